@@ -1,0 +1,91 @@
+// Context, error text and small queries of libtsrate.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void ts_set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+int ts_cuda_fail(cudaError_t e, const char *what)
+{
+    ts_set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+    return TS_E_CUDA;
+}
+
+extern "C" const char *ts_last_error(void) { return g_err; }
+
+extern "C" int ts_ctx_create(const ts_params *params, int device, ts_ctx **out)
+{
+    if (!params || !out) {
+        ts_set_error("ts_ctx_create: null argument");
+        return TS_E_ARG;
+    }
+    if (!(params->beta > 0.0) || !(params->tau >= 0.0)) {
+        ts_set_error("ts_ctx_create: beta must be > 0 and tau >= 0");
+        return TS_E_ARG;
+    }
+    int count = 0;
+    TS_CUDA(cudaGetDeviceCount(&count));
+    if (device < 0 || device >= count) {
+        ts_set_error("ts_ctx_create: device %d of %d", device, count);
+        return TS_E_ARG;
+    }
+    TS_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    TS_CUDA(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        ts_set_error("libtsrate is built for sm_100a (B200); device %d is sm_%d%d", device, prop.major, prop.minor);
+        return TS_E_UNSUPPORTED;
+    }
+    if (!prop.cooperativeLaunch) {
+        ts_set_error("device %d cannot launch cooperative kernels", device);
+        return TS_E_UNSUPPORTED;
+    }
+    ts_ctx *c = new ts_ctx();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    c->params = *params;
+    c->d_ctrl = nullptr;
+    cudaError_t e = cudaMalloc(&c->d_ctrl, CTRL_WORDS * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMemset(c->d_ctrl, 0, CTRL_WORDS * sizeof(unsigned long long));
+    if (e != cudaSuccess) {
+        delete c;
+        return ts_cuda_fail(e, "control words");
+    }
+    *out = c;
+    return 0;
+}
+
+extern "C" void ts_ctx_destroy(ts_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->d_ctrl);
+    delete ctx;
+}
+
+extern "C" int ts_sm_count(const ts_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
+
+extern "C" int64_t ts_error_count(ts_ctx *ctx, void *stream)
+{
+    if (!ctx) return TS_E_ARG;
+    unsigned long long v = 0;
+    TS_CUDA(cudaMemcpyAsync(&v, ctx->d_ctrl + CTRL_ERRORS, sizeof v, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    TS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return (int64_t)v;
+}
+
+extern "C" int ts_reset_errors(ts_ctx *ctx, void *stream)
+{
+    if (!ctx) return TS_E_ARG;
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_ERRORS, 0, sizeof(unsigned long long), (cudaStream_t)stream));
+    return 0;
+}

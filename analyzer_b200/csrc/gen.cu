@@ -1,0 +1,112 @@
+// Synthetic ladder generator (SURVEY.md 8d "Generator"): counter-based
+// splitmix64 hashing, integer-only decisions, so the CUDA output is
+// bit-identical to the host twin in oracle/ts_oracle.c.  Used by bench.py to
+// build BASELINE.json's configs directly in HBM.  No reference counterpart.
+#include "common.cuh"
+
+namespace {
+
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t z)
+{
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+__device__ __forceinline__ uint64_t rnd3(uint64_t seed, uint64_t a, uint64_t b, uint64_t c)
+{
+    return mix64(mix64(mix64(seed ^ a) + b * 0xD1342543DE82EF95ull) + c);
+}
+__device__ __forceinline__ int32_t four_u16(uint64_t h)
+{
+    return (int32_t)((h & 0xFFFF) + ((h >> 16) & 0xFFFF) + ((h >> 32) & 0xFFFF) + (h >> 48)) - 2 * 65535;
+}
+__device__ __forceinline__ int32_t latent_skill(uint64_t seed, uint64_t pid)
+{
+    return four_u16(mix64(mix64(seed ^ 0x5EEDFACE5EEDFACEull) + pid));
+}
+__device__ __forceinline__ uint32_t sample_player(const ts_gen &g, uint64_t x)
+{
+    if (!g.zipf) return (uint32_t)__umul64hi(x, g.n_players);
+    // inverse CDF of (rank + q)^-0.8 with explicitly rounded steps (no FMA contraction)
+    double u = __dmul_rn((double)(x >> 11), 0x1.0p-53);
+    double y = __dadd_rn(__dmul_rn(u, g.zipf_b), g.zipf_a);
+    double y2 = __dmul_rn(y, y);
+    double y4 = __dmul_rn(y2, y2);
+    double y5 = __dmul_rn(y4, y);
+    double r = __dadd_rn(y5, -g.zipf_q);
+    if (!(r >= 0.0)) r = 0.0;
+    uint64_t k = (uint64_t)r;
+    if (k >= g.n_players) k = g.n_players - 1;
+    return (uint32_t)k;
+}
+
+__global__ void __launch_bounds__(256) k_gen_matches(ts_gen g, int64_t first, int64_t count, uint32_t *ids, uint32_t *meta)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint64_t m = (uint64_t)(first + i);
+    const int P = g.slots, half = P / 2;
+    uint32_t pid[TS_MAX_SLOTS];
+    int64_t strength = 0;
+    for (int s = 0; s < P; ++s) {
+        uint64_t draw = 0;
+        for (;;) {
+            uint32_t p = sample_player(g, rnd3(g.seed, m, (uint64_t)s, draw));
+            bool dup = false;
+            for (int k = 0; k < s; ++k) dup |= (pid[k] == p);
+            if (!dup) { pid[s] = p; break; }
+            ++draw;
+        }
+        int32_t sk = latent_skill(g.seed, pid[s]);
+        strength += (s < half) ? sk : -sk;
+        ids[i * P + s] = pid[s];
+    }
+    uint64_t x = rnd3(g.seed, m, 0xFFFFull, 0);
+    long long thr = (1ll << 31) + strength * 11585ll;
+    const long long lo = 85899346ll, hi = 4209067950ll;
+    thr = thr < lo ? lo : (thr > hi ? hi : thr);
+    uint32_t bits = ((long long)(x >> 32) < thr) ? TS_META_WIN_A : TS_META_WIN_B;
+    uint64_t y = rnd3(g.seed, m, 0xFFFEull, 0);
+    if ((uint32_t)y < g.draw_thr) bits = 0;
+    if ((uint32_t)(y >> 32) < g.afk_thr) bits |= TS_META_AFK;
+    meta[i] = bits | ((uint32_t)g.mode << TS_META_MODE_SHIFT);
+}
+
+__global__ void __launch_bounds__(256) k_gen_table(uint64_t seed, int64_t first, int64_t count, double *table)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    uint64_t h = mix64(mix64(seed ^ 0x7AB1E7AB1E7AB1E5ull) + (uint64_t)(first + i));
+    double z = __dmul_rn((double)four_u16(h), 1.0 / 37837.0);
+    double mu = __dadd_rn(__dmul_rn(400.0, z), 1500.0);
+    reinterpret_cast<double2 *>(table)[i] = make_double2(mu, 500.0 * (2.0 / 3.0));
+}
+
+}  // namespace
+
+extern "C" int ts_gen_matches(const ts_gen *gen, int64_t first, int64_t count, uint32_t *ids, uint32_t *meta,
+                              void *stream)
+{
+    if (!gen || !ids || !meta || count < 0 || gen->slots < 2 || gen->slots > TS_MAX_SLOTS || (gen->slots & 1) ||
+        gen->n_players < (uint64_t)gen->slots) {
+        ts_set_error("ts_gen_matches: bad argument");
+        return TS_E_ARG;
+    }
+    if (count == 0) return 0;
+    k_gen_matches<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(*gen, first, count, ids, meta);
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int ts_gen_table(uint64_t seed, int64_t first, int64_t count, double *table, void *stream)
+{
+    if (!table || count < 0) {
+        ts_set_error("ts_gen_table: bad argument");
+        return TS_E_ARG;
+    }
+    if (count == 0) return 0;
+    k_gen_table<<<(unsigned)((count + 255) / 256), 256, 0, (cudaStream_t)stream>>>(seed, first, count, table);
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,499 @@
+// GPU dependency scheduler for sm_100a.
+//
+// Replaces the sequential, chronological per-match loop of worker.py:176-192
+// (state chains from one match to the next through the shared Player objects of
+// the SQLAlchemy identity map) with an explicit schedule:
+//
+//   1. radix-sort the (player_id, slot index) pairs of all rated matches by
+//      player id -- LSD, 8-bit digits, stable, so each player's slots stay in
+//      match_seq order;
+//   2. link each player's consecutive matches (successor per slot, number of
+//      predecessors per match);
+//   3. frontier relaxation: level-synchronous sweep in one persistent
+//      cooperative kernel; the frontier of iteration k is exactly the set of
+//      matches whose ASAP round is k (all predecessors resolved in k-1 sweeps);
+//   4. radix-sort (round, match_seq) so every round lists its matches in
+//      ascending match_seq, prefix-sum the level sizes into round_offsets, and
+//      permute the match records into that order for the rating kernel.
+//
+// Gated matches (unsupported mode, AFK, invalid roster count) never touch a
+// player (rater.py:83-85,102-106): they create no edges and land in bucket 0.
+// All integer work; the result is bit-exact against the sequential schedule
+// oracle by construction (Kahn levels == longest-path levels).
+#include "common.cuh"
+
+namespace {
+
+constexpr int kSortBlock = 256;
+constexpr int kSortItems = 16;
+constexpr int kSortTile = kSortBlock * kSortItems;   // 4096 elements per block
+constexpr int kWarps = kSortBlock / 32;
+
+struct KeySrc {
+    // pass 0 of the player sort reads match records directly: key = player id,
+    // or n_players for slots that take no part (empty slot / gated match)
+    const uint32_t *keys;
+    const uint32_t *meta;
+    ModeCols modes;
+    uint32_t slots;
+    uint32_t sentinel;
+    int from_ids;
+};
+
+__device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
+{
+    uint32_t k = __ldg(src.keys + idx);
+    if (src.from_ids) {
+        uint32_t m = __ldg(src.meta + idx / src.slots);
+        if (k == TS_EMPTY_SLOT || meta_is_gated(m, src.modes.col)) k = src.sentinel;
+    }
+    return k;
+}
+
+// per-block digit histogram, written digit-major: hist[d * n_blocks + block]
+__global__ void __launch_bounds__(kSortBlock) k_radix_hist(KeySrc src, uint32_t n, int shift,
+                                                           uint32_t *hist, uint32_t n_blocks)
+{
+    __shared__ uint32_t h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t base = blockIdx.x * kSortTile;
+#pragma unroll 4
+    for (int k = 0; k < kSortItems; ++k) {
+        uint32_t idx = base + k * kSortBlock + threadIdx.x;
+        if (idx < n) atomicAdd(&h[(load_key(src, idx) >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * n_blocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// exclusive scan of each digit's row of block counts (one block per digit)
+__global__ void __launch_bounds__(1024) k_radix_scan_rows(uint32_t *hist, uint32_t n_blocks, uint32_t *totals)
+{
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry;
+    uint32_t *row = hist + (size_t)blockIdx.x * n_blocks;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_blocks; base += 1024) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t x = i < n_blocks ? row[i] : 0u;
+        uint32_t incl = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if ((threadIdx.x & 31) >= o) incl += y;
+        }
+        if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_sums[threadIdx.x], wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t y = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+                if (threadIdx.x >= o) wi += y;
+            }
+            warp_sums[threadIdx.x] = wi - w;
+        }
+        __syncthreads();
+        uint32_t excl = carry + warp_sums[threadIdx.x >> 5] + incl - x;
+        if (i < n_blocks) row[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) totals[blockIdx.x] = carry;
+}
+
+// exclusive scan of the 256 digit totals (one block)
+__global__ void __launch_bounds__(256) k_radix_scan_totals(uint32_t *totals)
+{
+    __shared__ uint32_t s[256];
+    s[threadIdx.x] = totals[threadIdx.x];
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int d = 0; d < 256; ++d) { uint32_t c = s[d]; s[d] = run; run += c; }
+    }
+    __syncthreads();
+    totals[threadIdx.x] = s[threadIdx.x];
+}
+
+// stable scatter: warp w of a block owns WTILE consecutive elements and walks
+// them 32 at a time, so (step, lane) order is index order.
+__global__ void __launch_bounds__(kSortBlock)
+k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n, int shift,
+                const uint32_t *hist, const uint32_t *totals, uint32_t n_blocks,
+                uint32_t *keys_out, uint32_t *vals_out)
+{
+    __shared__ uint32_t wcount[kWarps][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < kWarps * 256; i += kSortBlock) (&wcount[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t wbase = blockIdx.x * kSortTile + warp * (kSortItems * 32);
+    uint32_t key[kSortItems], off[kSortItems];
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        uint32_t idx = wbase + k * 32 + lane;
+        bool ok = idx < n;
+        key[k] = ok ? load_key(src, idx) : 0u;
+        uint32_t d = ok ? ((key[k] >> shift) & 255u) : 256u;   // 256 = padding, matches only padding
+        uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
+        uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+        int leader = __ffs(peers) - 1;
+        uint32_t prev = 0;
+        if (ok && lane == leader) {
+            prev = wcount[warp][d];
+            wcount[warp][d] = prev + __popc(peers);
+        }
+        prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
+        off[k] = prev + rank;
+    }
+    __syncthreads();
+    {
+        // thread d: running start of digit d for each warp of this block
+        const uint32_t d = threadIdx.x;
+        uint32_t run = __ldg(totals + d) + __ldg(hist + (size_t)d * n_blocks + blockIdx.x);
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) {
+            uint32_t c = wcount[w][d];
+            wcount[w][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        uint32_t idx = wbase + k * 32 + lane;
+        if (idx < n) {
+            uint32_t pos = wcount[warp][(key[k] >> shift) & 255u] + off[k];
+            keys_out[pos] = key[k];
+            vals_out[pos] = ident_vals ? idx : __ldg(vals_in + idx);
+        }
+    }
+}
+
+// ---- chain linking --------------------------------------------------------
+// Sorted pairs (key = player, val = slot index i = m*P + s).  Runs of equal key
+// list one player's slots in match order.  The first entry of a (player, match)
+// run is its primary: it counts one predecessor for its match if an earlier
+// match of the same player exists, and carries the link to the next one.
+__global__ void __launch_bounds__(256)
+k_link(const uint32_t *keys, const uint32_t *vals, uint32_t n, uint32_t slots, uint32_t sentinel,
+       uint32_t *succ, uint32_t *pending)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t k = keys[i], v = vals[i];
+    if (k >= sentinel) { succ[v] = TS_NONE; return; }
+    uint32_t m = v / slots;
+    bool has_prev = i > 0 && keys[i - 1] == k;
+    if (has_prev && vals[i - 1] / slots == m) { succ[v] = TS_NONE; return; }   // duplicate of a player inside one match
+    if (has_prev) atomicAdd(&pending[m], 1u);
+    uint32_t nx = TS_NONE;
+    for (uint32_t j = i + 1; j < n && keys[j] == k; ++j) {
+        uint32_t mj = vals[j] / slots;
+        if (mj != m) { nx = mj; break; }
+    }
+    succ[v] = nx;
+}
+
+__global__ void __launch_bounds__(256)
+k_init_frontier(const uint32_t *meta, ModeCols modes, const uint32_t *pending, uint32_t n,
+                uint32_t *queue, unsigned long long *ctrl)
+{
+    uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+    bool ready = m < n && !meta_is_gated(__ldg(meta + m), modes.col) && pending[m] == 0u;
+    // warp-aggregated append
+    uint32_t mask = __ballot_sync(0xFFFFFFFFu, ready);
+    if (mask == 0u) return;
+    int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+    unsigned long long base = 0;
+    if (lane == leader) base = atomicAdd(&ctrl[CTRL_TAIL], (unsigned long long)__popc(mask));
+    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+    if (ready) queue[base + __popc(mask & ((1u << lane) - 1u))] = m;
+}
+
+// Level-synchronous frontier sweep.  queue holds level after level back to back;
+// the block that arrives last at the barrier snapshots the tail, which closes
+// the next level before anyone starts appending to the one after it.
+__global__ void __launch_bounds__(256)
+k_frontier(uint32_t *queue, const uint32_t *succ, uint32_t *pending, uint32_t *round, uint32_t slots,
+           uint32_t n_matches, uint32_t *level_sizes, uint32_t offsets_cap, ts_sched_info *info,
+           unsigned long long *ctrl)
+{
+    unsigned long long generation = 0;
+    uint32_t start = 0;
+    // every block must see the same first `end`: the host copied the tail into
+    // the snapshot word before launch, and it is rewritten only at a barrier
+    uint32_t end = (uint32_t)ld_acquire_u64(&ctrl[CTRL_TAIL + 1]);
+    uint32_t level = 1;
+    while (start < end) {
+        const uint32_t work = (end - start) * slots;
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < work; i += gridDim.x * blockDim.x) {
+            uint32_t m = __ldcg(queue + start + i / slots);
+            uint32_t s = i % slots;
+            if (s == 0) round[m] = level;
+            uint32_t nx = __ldg(succ + (size_t)m * slots + s);
+            if (nx != TS_NONE && atomicSub(&pending[nx], 1u) == 1u)
+                queue[atomicAdd(&ctrl[CTRL_TAIL], 1ull)] = nx;
+        }
+        const uint32_t lvl = level, cnt = end - start;
+        grid_barrier(ctrl, generation, [&]() {
+            if (lvl + 2 <= offsets_cap) level_sizes[lvl] = cnt;   // bucket lvl
+            ctrl[CTRL_TAIL + 1] = ld_acquire_u64(&ctrl[CTRL_TAIL]);
+        });
+        start = end;
+        end = (uint32_t)ld_acquire_u64(&ctrl[CTRL_TAIL + 1]);
+        level += 1;
+        // the snapshot word is rewritten only after every block has passed the
+        // NEXT barrier's arrive, i.e. after it has read this value
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        info->n_rounds = level - 1;
+        info->n_gated = n_matches - end;
+        info->overflow = (level - 1 + 2 > offsets_cap) ? 1u : 0u;
+        info->reserved = 0;
+        if (offsets_cap >= 1) level_sizes[0] = n_matches - end;
+    }
+}
+
+// in-place exclusive scan of bucket sizes -> round_offsets (single block; the
+// number of rounds is small next to the number of matches)
+__global__ void __launch_bounds__(1024) k_offsets(uint32_t *sizes, const ts_sched_info *info, uint32_t cap)
+{
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry;
+    uint32_t n = info->n_rounds + 1;           // buckets 0..n_rounds
+    if (n + 1 > cap) n = cap - 1;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n; base += 1024) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t x = i < n ? sizes[i] : 0u, incl = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if ((threadIdx.x & 31) >= o) incl += y;
+        }
+        if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_sums[threadIdx.x], wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                uint32_t y = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+                if (threadIdx.x >= o) wi += y;
+            }
+            warp_sums[threadIdx.x] = wi - w;
+        }
+        __syncthreads();
+        uint32_t excl = carry + warp_sums[threadIdx.x >> 5] + incl - x;
+        if (i < n) sizes[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) sizes[n] = carry;
+}
+
+__global__ void __launch_bounds__(256)
+k_permute(const uint32_t *ids, const uint32_t *meta, const uint32_t *order, uint32_t n, uint32_t slots,
+          uint32_t *ids_sorted, uint32_t *meta_sorted)
+{
+    // one thread per slot: contiguous writes, record-granular gathers
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)n * slots) return;
+    uint32_t j = (uint32_t)(i / slots), s = (uint32_t)(i % slots);
+    uint32_t m = __ldg(order + j);
+    ids_sorted[i] = __ldg(ids + (size_t)m * slots + s);
+    if (s == 0) meta_sorted[j] = __ldg(meta + m);
+}
+
+struct Workspace {
+    uint32_t *keys[2];
+    uint32_t *vals[2];
+    uint32_t *hist;
+    uint32_t *totals;
+    uint32_t *succ;
+    uint32_t *pending;
+    uint32_t *queue;
+    size_t bytes;
+};
+
+size_t align_up(size_t x) { return (x + 255) & ~(size_t)255; }
+
+Workspace carve(char *base, int64_t n_matches, int32_t slots)
+{
+    Workspace w;
+    size_t np = (size_t)n_matches * slots;
+    size_t n_blocks = (np + kSortTile - 1) / kSortTile;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { char *p = base ? base + off : nullptr; off += align_up(bytes); return (uint32_t *)p; };
+    for (int i = 0; i < 2; ++i) { w.keys[i] = take(np * 4); w.vals[i] = take(np * 4); }
+    w.hist = take((n_blocks * 256 + 256) * 4);
+    w.totals = take(256 * 4);
+    w.succ = take(np * 4);
+    w.pending = take((size_t)n_matches * 4);
+    w.queue = take((size_t)n_matches * 4);
+    w.bytes = off;
+    return w;
+}
+
+int bits_for(uint64_t max_value)
+{
+    int b = 1;
+    while (b < 32 && (max_value >> b) != 0) ++b;
+    return b;
+}
+
+// LSD radix sort of n (key, val) pairs on the low `bits` bits.  Pass 0 reads
+// `src` (with identity values); results ping-pong between the two buffers.
+// Returns the index of the buffer holding the result (or <0).
+int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream)
+{
+    const uint32_t n_blocks = (n + kSortTile - 1) / kSortTile;
+    const int passes = (bits + 7) / 8;
+    int cur = -1;
+    for (int p = 0; p < passes; ++p) {
+        KeySrc src = src0;
+        const uint32_t *vals_in = nullptr;
+        if (p > 0) { src.keys = w.keys[cur]; src.from_ids = 0; vals_in = w.vals[cur]; }
+        int dst = (cur + 1) & 1;
+        if (cur < 0) dst = 0;
+        k_radix_hist<<<n_blocks, kSortBlock, 0, stream>>>(src, n, p * 8, w.hist, n_blocks);
+        k_radix_scan_rows<<<256, 1024, 0, stream>>>(w.hist, n_blocks, w.totals);
+        k_radix_scan_totals<<<1, 256, 0, stream>>>(w.totals);
+        k_radix_scatter<<<n_blocks, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n, p * 8, w.hist,
+                                                             w.totals, n_blocks, w.keys[dst], w.vals[dst]);
+        cur = dst;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return ts_cuda_fail(e, "radix sort launch");
+    return cur;
+}
+
+}  // namespace
+
+extern "C" int64_t ts_schedule_workspace_bytes(int64_t n_matches, int32_t slots)
+{
+    if (n_matches < 0 || slots < 2 || slots > TS_MAX_SLOTS) return TS_E_ARG;
+    return (int64_t)carve(nullptr, n_matches, slots).bytes;
+}
+
+extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches,
+                           int32_t slots, int64_t n_players, const int8_t mode_col[16],
+                           uint32_t *round, uint32_t *order, uint32_t *round_offsets, int64_t offsets_cap,
+                           uint32_t *ids_sorted, uint32_t *meta_sorted, ts_sched_info *info,
+                           void *workspace, int64_t workspace_bytes, uint32_t *n_rounds_host, void *stream)
+{
+    if (!ctx || !mode_col || !round_offsets || !info ||
+        (n_matches > 0 && (!ids || !meta || !round || !order || !workspace))) {
+        ts_set_error("ts_schedule: null argument");
+        return TS_E_ARG;
+    }
+    if (slots < 2 || slots > TS_MAX_SLOTS || (slots & 1)) {
+        ts_set_error("ts_schedule: slots must be even and in [2, %d] (got %d)", TS_MAX_SLOTS, slots);
+        return TS_E_ARG;
+    }
+    if (n_matches < 0 || (uint64_t)n_matches * (uint64_t)slots >= 0xFFFF0000ull) {
+        ts_set_error("ts_schedule: n_matches * slots must stay below 2^32 - 2^16: schedule the ladder in windows");
+        return TS_E_ARG;
+    }
+    if (n_players < 1 || n_players >= 0xFFFFFFFFll) {
+        ts_set_error("ts_schedule: n_players outside [1, 2^32 - 1)");
+        return TS_E_ARG;
+    }
+    if (offsets_cap < 3) {
+        ts_set_error("ts_schedule: round_offsets needs at least 3 entries");
+        return TS_E_WORKSPACE;
+    }
+    TS_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n_matches == 0) {
+        ts_sched_info z = {0, 0, 0, 0};
+        TS_CUDA(cudaMemcpyAsync(info, &z, sizeof z, cudaMemcpyHostToDevice, s));
+        TS_CUDA(cudaMemsetAsync(round_offsets, 0, 3 * sizeof(uint32_t), s));
+        TS_CUDA(cudaStreamSynchronize(s));
+        if (n_rounds_host) *n_rounds_host = 0;
+        return 0;
+    }
+    Workspace w = carve((char *)workspace, n_matches, slots);
+    if ((int64_t)w.bytes > workspace_bytes) {
+        ts_set_error("ts_schedule: workspace too small (%lld < %lld bytes)", (long long)workspace_bytes, (long long)w.bytes);
+        return TS_E_WORKSPACE;
+    }
+    const uint32_t n = (uint32_t)n_matches;
+    const uint32_t np = n * (uint32_t)slots;
+    ModeCols modes;
+    for (int i = 0; i < 16; ++i) modes.col[i] = i < 6 ? mode_col[i] : (int8_t)-1;
+    const uint32_t cap = (uint32_t)(offsets_cap > 0xFFFFFFFFll ? 0xFFFFFFFFll : offsets_cap);
+
+    // 1. sort slots by player id
+    KeySrc src;
+    src.keys = ids;
+    src.meta = meta;
+    src.modes = modes;
+    src.slots = (uint32_t)slots;
+    src.sentinel = (uint32_t)n_players;
+    src.from_ids = 1;
+    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s);
+    if (buf < 0) return buf;
+
+    // 2. link chains
+    TS_CUDA(cudaMemsetAsync(w.pending, 0, (size_t)n * 4, s));
+    TS_CUDA(cudaMemsetAsync(round, 0, (size_t)n * 4, s));
+    // barrier words and queue tail/snapshot; the error counter (word 2) is left alone
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl, 0, 2 * sizeof(unsigned long long), s));
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_TAIL, 0, 2 * sizeof(unsigned long long), s));
+    k_link<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, (uint32_t)slots, (uint32_t)n_players,
+                                            w.succ, w.pending);
+    k_init_frontier<<<(n + 255) / 256, 256, 0, s>>>(meta, modes, w.pending, n, w.queue, ctx->d_ctrl);
+    // close level 1: the sweep reads its first `end` from the snapshot word
+    TS_CUDA(cudaMemcpyAsync(ctx->d_ctrl + CTRL_TAIL + 1, ctx->d_ctrl + CTRL_TAIL, sizeof(unsigned long long),
+                            cudaMemcpyDeviceToDevice, s));
+
+    // 3. frontier relaxation (persistent, cooperative)
+    {
+        int per_sm = 0;
+        TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_frontier, 256, 0));
+        if (per_sm < 1) { ts_set_error("frontier kernel does not fit"); return TS_E_CUDA; }
+        if (per_sm > 4) per_sm = 4;
+        dim3 grid(ctx->sm_count * per_sm), block(256);
+        uint32_t slots_u = (uint32_t)slots;
+        unsigned long long *ctrl = ctx->d_ctrl;
+        void *kargs[] = {&w.queue, &w.succ, &w.pending, &round, &slots_u, (void *)&n, &round_offsets,
+                         (void *)&cap, &info, &ctrl};
+        TS_CUDA(cudaLaunchCooperativeKernel((void *)k_frontier, grid, block, kargs, 0, s));
+    }
+    k_offsets<<<1, 1024, 0, s>>>(round_offsets, info, cap);
+
+    // 4. bucket by round, ascending match_seq inside a round
+    ts_sched_info h;
+    TS_CUDA(cudaMemcpyAsync(&h, info, sizeof h, cudaMemcpyDeviceToHost, s));
+    TS_CUDA(cudaStreamSynchronize(s));
+    // errors were reset together with the control words above: keep the count
+    if (h.overflow) {
+        ts_set_error("ts_schedule: %u rounds need offsets_cap >= %u (got %lld)", h.n_rounds, h.n_rounds + 2,
+                     (long long)offsets_cap);
+        return TS_E_WORKSPACE;
+    }
+    KeySrc rsrc;
+    rsrc.keys = round;
+    rsrc.meta = nullptr;
+    rsrc.modes = modes;
+    rsrc.slots = 1;
+    rsrc.sentinel = 0;
+    rsrc.from_ids = 0;
+    buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s);
+    if (buf < 0) return buf;
+    TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    if (ids_sorted && meta_sorted) {
+        size_t total = (size_t)n * slots;
+        k_permute<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(ids, meta, order, n, (uint32_t)slots, ids_sorted,
+                                                                  meta_sorted);
+    }
+    TS_CUDA(cudaGetLastError());
+    if (n_rounds_host) *n_rounds_host = h.n_rounds;
+    return 0;
+}

@@ -1,0 +1,304 @@
+"""Host side of the B200 rating path: environment, HBM player table, schedule
+and rate calls over the C ABI (include/tsrate.h).  torch is used for device
+memory and streams only; every kernel is in libtsrate.so.
+
+Mirrors, in columnar form, what rater.py:30-37 (env), worker.py:176-192 (the
+chronological per-match loop) and rater.py:69-169 (rate_match) do per object.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+N_MODES = 6
+MODE_NAMES = ("casual", "ranked", "blitz", "br", "5v5_casual", "5v5_ranked")   # rater.py:70-82
+
+
+# ---------------------------------------------------------------------------
+# draw margin, the way the trueskill package computes it:
+# ppf(y) = -sqrt(2) * erfcinv(2y), erfcinv = rational guess + 2 Newton steps
+# ---------------------------------------------------------------------------
+def _erfcinv(y):
+    if y >= 2:
+        return -100.0
+    if y <= 0:
+        return 100.0
+    lower = y < 1
+    if not lower:
+        y = 2 - y
+    t = math.sqrt(-2 * math.log(y / 2.0))
+    x = -0.70711 * ((2.30753 + t * 0.27061) / (1.0 + t * (0.99229 + t * 0.04481)) - t)
+    for _ in range(2):
+        err = math.erfc(x) - y
+        x += err / (1.12837916709551257 * math.exp(-(x ** 2)) - x * err)
+    return x if lower else -x
+
+
+def draw_margin(draw_probability, n_players, beta):
+    """calc_draw_margin(draw_probability, size, env); exactly 0 at
+    draw_probability == 0, where the kernel uses the analytic draw limit
+    (with the reference's 50-digit backend ppf(0.5) is ~1e-34, not 0)."""
+    if draw_probability == 0:
+        return 0.0
+    return -math.sqrt(2) * _erfcinv(draw_probability + 1.0) * math.sqrt(n_players) * beta
+
+
+class Env(object):
+    """rater.py:30-37 -- beta, tau, draw_probability of the TrueSkill environment."""
+
+    def __init__(self, beta=10.0 / 30 * 3000, tau=1000 / 100.0, draw_probability=0.0,
+                 mu=1500, sigma=1000):
+        self.mu, self.sigma = mu, sigma          # unused by the rating path (rater.py:121,132)
+        self.beta, self.tau, self.draw_probability = float(beta), float(tau), float(draw_probability)
+
+    def params(self):
+        p = L.TsParams()
+        p.beta, p.tau = self.beta, self.tau
+        for n in range(L.MAX_SLOTS + 1):
+            p.draw_margin[n] = draw_margin(self.draw_probability, n, self.beta) if n else 0.0
+        p.draw_is_zero = 1 if self.draw_probability == 0 else 0
+        return p
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+class PlayerTable(object):
+    """HBM-resident player table: float64 [n_players, row_pairs, 2], NaN = NULL.
+
+    layout "faithful": 8 pairs per row = one 128-byte line; col 0 shared
+    (player.trueskill_mu/_sigma), cols 1..6 the queue ratings in MODE_NAMES
+    order.  layout "ladder": one pair per row, no shared rating -- the single
+    (mu, sigma) ladder of BASELINE.json.  layout "pair": shared + one queue.
+    """
+
+    def __init__(self, data, shared_col, mode_cols, seed=None):
+        assert data.dtype == torch.float64 and data.dim() == 3 and data.shape[2] == 2
+        assert data.is_cuda and data.is_contiguous()
+        self.data, self.seed = data, seed
+        self.shared_col = int(shared_col)
+        self.mode_cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
+        if seed is not None:
+            assert seed.dtype == torch.float64 and seed.shape == (data.shape[0], 2) and seed.is_cuda
+
+    @property
+    def n_players(self):
+        return self.data.shape[0]
+
+    @classmethod
+    def faithful(cls, n_players, device, seed=None):
+        data = torch.full((n_players, 8, 2), float("nan"), dtype=torch.float64, device=device)
+        return cls(data, 0, [1, 2, 3, 4, 5, 6], seed)
+
+    @classmethod
+    def ladder(cls, data, mode=1, seed=None):
+        cols = [-1] * N_MODES
+        cols[mode] = 0
+        return cls(data.view(-1, 1, 2), -1, cols, seed)
+
+    def mode_col_array(self):
+        return (C.c_int8 * 16)(*self.mode_cols)
+
+    def desc(self):
+        t = L.TsTable()
+        t.data = self.data.data_ptr()
+        t.seed = self.seed.data_ptr() if self.seed is not None else None
+        t.n_players = self.n_players
+        t.row_pairs = self.data.shape[1]
+        t.shared_col = self.shared_col
+        for i in range(16):
+            t.mode_col[i] = self.mode_cols[i]
+        return t
+
+
+class Schedule(object):
+    """Result of Rater.schedule: device tensors in tsrate.h's terms."""
+
+    def __init__(self, n_matches, slots):
+        self.n_matches, self.slots = n_matches, slots
+        self.round = self.order = self.round_offsets = None
+        self.ids_sorted = self.meta_sorted = self.info = None
+        self.n_rounds = 0
+
+
+class Rater(object):
+    """One context per device (ts_ctx)."""
+
+    def __init__(self, env=None, device=0):
+        if not torch.cuda.is_available():
+            raise RuntimeError("analyzer_b200 needs a CUDA device (B200); there is no CPU fallback")
+        self.env = env or Env()
+        self.device = torch.device("cuda", device) if not isinstance(device, torch.device) else device
+        self._lib = L.lib()
+        self._ctx = C.c_void_p()
+        prm = self.env.params()
+        L.check(self._lib.ts_ctx_create(C.byref(prm), self.device.index or 0, C.byref(self._ctx)))
+        self._ws = None
+
+    def close(self):
+        if self._ctx:
+            self._lib.ts_ctx_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def sm_count(self):
+        return self._lib.ts_sm_count(self._ctx)
+
+    def _workspace(self, nbytes):
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = None
+            self._ws = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def schedule(self, ids, meta, n_players, mode_cols, offsets_cap=None):
+        """ids: uint32-as-int32 [N, P] device tensor (torch has no uint32 math;
+        the bits are what matter), meta: [N].  Returns a Schedule."""
+        assert ids.is_cuda and ids.is_contiguous() and meta.is_contiguous()
+        assert ids.element_size() == 4 and meta.element_size() == 4
+        n, p = ids.shape
+        sch = Schedule(n, p)
+        dev = ids.device
+        cap = int(offsets_cap if offsets_cap is not None else n + 2)
+        sch.round = torch.empty(n, dtype=torch.int32, device=dev)
+        sch.order = torch.empty(n, dtype=torch.int32, device=dev)
+        sch.round_offsets = torch.empty(max(cap, 3), dtype=torch.int32, device=dev)
+        sch.ids_sorted = torch.empty_like(ids)
+        sch.meta_sorted = torch.empty_like(meta)
+        sch.info = torch.zeros(4, dtype=torch.int32, device=dev)
+        nbytes = self._lib.ts_schedule_workspace_bytes(n, p)
+        L.check(nbytes)
+        ws = self._workspace(nbytes)
+        cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
+        n_rounds = C.c_uint32(0)
+        with torch.cuda.device(dev):
+            L.check(self._lib.ts_schedule(
+                self._ctx, _ptr(ids), _ptr(meta), n, p, int(n_players), (C.c_int8 * 16)(*cols),
+                _ptr(sch.round), _ptr(sch.order), _ptr(sch.round_offsets), cap,
+                _ptr(sch.ids_sorted), _ptr(sch.meta_sorted), _ptr(sch.info),
+                _ptr(ws), ws.numel(), C.byref(n_rounds), _stream_ptr()))
+        sch.n_rounds = int(n_rounds.value)
+        return sch
+
+    def rate(self, table, sch, outputs=None, lanes_per_match=0):
+        """Run every round of `sch` against `table` (in place).  outputs: dict
+        with any of quality/out_shared/out_delta/out_queue/status device tensors."""
+        out = L.TsOutputs()
+        if outputs:
+            for k in ("quality", "out_shared", "out_delta", "out_queue", "status"):
+                t = outputs.get(k)
+                setattr(out, k, t.data_ptr() if t is not None else None)
+        desc = table.desc()
+        with torch.cuda.device(table.data.device):
+            L.check(self._lib.ts_rate(
+                self._ctx, C.byref(desc), _ptr(sch.ids_sorted), _ptr(sch.meta_sorted), _ptr(sch.order),
+                _ptr(sch.round_offsets), _ptr(sch.info), sch.n_matches, sch.slots, C.byref(out),
+                int(lanes_per_match), _stream_ptr()))
+
+    def error_count(self):
+        return L.check(self._lib.ts_error_count(self._ctx, _stream_ptr()))
+
+    def reset_errors(self):
+        L.check(self._lib.ts_reset_errors(self._ctx, _stream_ptr()))
+
+    def alloc_outputs(self, n, p, device=None):
+        dev = device or self.device
+        nan = float("nan")
+        return dict(
+            quality=torch.full((n,), nan, dtype=torch.float64, device=dev),
+            out_shared=torch.full((n, p, 2), nan, dtype=torch.float64, device=dev),
+            out_delta=torch.full((n, p), nan, dtype=torch.float64, device=dev),
+            out_queue=torch.full((n, p, 2), nan, dtype=torch.float64, device=dev),
+            status=torch.zeros((n,), dtype=torch.uint8, device=dev))
+
+    # ------------------------------------------------------------------
+    def rate_batch(self, ids, meta, table, seed=None, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6),
+                   want_outputs=True, lanes_per_match=0, table_out=None):
+        """The reference-facing batch call with HOST buffers: numpy ids
+        [N, P] uint32, meta [N] uint32, table [U, C, 2] float64 (NaN = NULL),
+        optional seed [U, 2].  Copies in, schedules, rates, copies back.
+        Returns dict(table=..., n_rounds=..., quality=..., out_*=..., status=...).
+        Raises FloatingPointError / ValueError like the reference would for the
+        batch (worker.py:195-197) -- the returned table is then not produced."""
+        dev = self.device
+
+        def host(a, as_i32=False):
+            if a is None or isinstance(a, torch.Tensor):
+                return a                      # torch CPU tensors (e.g. pinned) pass through
+            a = np.ascontiguousarray(a)
+            return torch.from_numpy(a.view(np.int32) if as_i32 else a)
+
+        ids_t, meta_t, tab_t, seed_t = host(ids, True), host(meta, True), host(table), host(seed)
+        ids_d = ids_t.to(dev, non_blocking=True)
+        meta_d = meta_t.to(dev, non_blocking=True)
+        tab_d = tab_t.to(dev, non_blocking=True)
+        seed_d = seed_t.to(dev, non_blocking=True) if seed_t is not None else None
+        ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
+        n, p = ids_d.shape
+        self.reset_errors()
+        sch = self.schedule(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
+        outs = self.alloc_outputs(n, p) if want_outputs else None
+        self.rate(ptab, sch, outs, lanes_per_match)
+        bad = self.error_count()
+        result = dict(n_rounds=sch.n_rounds, errors=bad)
+        if outs is not None:
+            for k, t in outs.items():
+                result[k] = t.cpu().numpy()
+        if bad:
+            st = result.get("status")
+            if st is not None and np.any(st == L.ST_VALUE_ERROR):
+                raise ValueError("sigma**2 should be greater than 0 / player without rating or seed "
+                                 "(%d matches)" % int(np.sum(st == L.ST_VALUE_ERROR)))
+            raise FloatingPointError("%d matches outside the truncated-Gaussian domain" % bad)
+        if table_out is not None:             # caller-provided (pinned) host tensor
+            table_out.copy_(tab_d, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            result["table"] = table_out
+        else:
+            result["table"] = tab_d.cpu().numpy()
+        return result
+
+
+# ---------------------------------------------------------------------------
+# synthetic ladders (BASELINE.json configs) generated in HBM
+# ---------------------------------------------------------------------------
+def make_gen(seed, n_players, slots=6, mode=1, p_draw=0.0, p_afk=0.0, zipf=False, zipf_q=1000.0):
+    g = L.TsGen()
+    g.seed, g.n_players, g.slots, g.mode = seed, n_players, slots, mode
+    g.draw_thr = min(int(p_draw * 2 ** 32), 2 ** 32 - 1)
+    g.afk_thr = min(int(p_afk * 2 ** 32), 2 ** 32 - 1)
+    g.zipf = 1 if zipf else 0
+    g.zipf_q = zipf_q
+    g.zipf_a = zipf_q ** 0.2
+    g.zipf_b = (n_players + zipf_q) ** 0.2 - zipf_q ** 0.2
+    return g
+
+
+def gen_matches(gen, first, count, device):
+    ids = torch.empty((count, gen.slots), dtype=torch.int32, device=device)
+    meta = torch.empty((count,), dtype=torch.int32, device=device)
+    with torch.cuda.device(device):
+        L.check(L.lib().ts_gen_matches(C.byref(gen), first, count, _ptr(ids), _ptr(meta), _stream_ptr()))
+    return ids, meta
+
+
+def gen_table(seed, first, count, device):
+    t = torch.empty((count, 1, 2), dtype=torch.float64, device=device)
+    with torch.cuda.device(device):
+        L.check(L.lib().ts_gen_table(seed, first, count, _ptr(t), _stream_ptr()))
+    return t

@@ -1,0 +1,242 @@
+"""Drop-in for the reference's `rater` module (rater.py) on the B200 path.
+
+Same names and behaviour at the module boundary:
+
+    rate_match(match)          rater.py:69-169   mutate one match's object graph
+    get_trueskill_seed(player) rater.py:42-62
+    vst_points                 rater.py:13-27
+    env, TAU, UNKNOWN_PLAYER_SIGMA   rater.py:10-11,30-37
+
+plus the batch forms the GPU wants:
+
+    rate_matches(matches)      worker.py:176-192's loop in ONE call: columnar
+                               ingest of the object graphs (shared Player
+                               objects keep their identity, like the SQLAlchemy
+                               session's identity map), GPU schedule + rate,
+                               attribute write-back
+    rate_batch(ids, meta, table, ...)   columns in, columns out (engine.Rater)
+
+`worker.py` keeps working unchanged (`rater.rate_match(match)` per match), but
+a worker that wants the throughput calls `rater.rate_matches(list_of_matches)`
+once per batch instead of looping.
+
+Everything numeric runs in libtsrate.so on the GPU.  There is no CPU fallback:
+without the library or a CUDA device these functions raise.
+"""
+from __future__ import annotations
+
+import logging
+import os
+import sys
+
+import numpy as np
+
+from . import _lib as L
+from .engine import Env, Rater, MODE_NAMES
+
+UNKNOWN_PLAYER_SIGMA = int(os.environ.get("UNKNOWN_PLAYER_SIGMA") or 500)   # rater.py:10
+TAU = float(os.environ.get("TAU") or 1000 / 100.0)                          # rater.py:11
+
+
+def _build_vst_points():
+    """Tier (-1..29) -> average skill-tier points, piecewise linear in the
+    tier with slopes 109 1/11, 50, 66 2/3, 133 1/3 and 200 (rater.py:13-27)."""
+    pts = {-1: 1, 0: 1}
+    anchor = 0
+    for count, slope in ((11, 109 + 1 / 11), (4, 50), (9, 66 + 2 / 3), (3, 133 + 1 / 3), (2, 200)):
+        base = pts[anchor] if anchor else 0
+        for c in range(1, count + 1):
+            pts[anchor + c] = base + slope * (c + 0.5)
+        anchor += count
+    return pts
+
+
+vst_points = _build_vst_points()
+
+env = Env(beta=10.0 / 30 * 3000, tau=TAU, draw_probability=0)   # rater.py:30-37
+
+_MODE_INDEX = {name: i for i, name in enumerate(MODE_NAMES)}
+_MODE_COLUMN = {name: "trueskill_" + name for name in MODE_NAMES}      # rater.py:70-82
+
+logger = logging.getLogger("__name__")   # sic: the reference names its logger "__name__" (rater.py:177)
+if not logger.handlers:
+    logger.setLevel(logging.INFO)
+
+    class _InfoFilter(logging.Filter):
+        def filter(self, record):
+            return record.levelno in (logging.DEBUG, logging.INFO)
+
+    _h1 = logging.StreamHandler(sys.stdout)
+    _h1.setLevel(logging.INFO)
+    _h1.addFilter(_InfoFilter())
+    logger.addHandler(_h1)
+    _h2 = logging.StreamHandler(sys.stderr)
+    _h2.setLevel(logging.WARNING)
+    logger.addHandler(_h2)
+
+
+def get_trueskill_seed(player):
+    """First-touch (mu, sigma) of a player (rater.py:42-62)."""
+    best = None
+    for pts in (player.rank_points_ranked, player.rank_points_blitz):
+        if pts is not None and pts != 0 and (best is None or pts > best):
+            best = pts
+    if best is not None:
+        sigma = UNKNOWN_PLAYER_SIGMA * (2.0 / 3.0)
+        return float(best) + sigma, sigma
+    sigma = UNKNOWN_PLAYER_SIGMA
+    return vst_points[player.skill_tier] + sigma, sigma   # KeyError outside -1..29, like the reference
+
+
+_raters = {}
+
+
+def _rater(device=0):
+    r = _raters.get(device)
+    if r is None or r.env is not env:
+        r = Rater(env, device)
+        _raters[device] = r
+    return r
+
+
+# ---------------------------------------------------------------------------
+# columnar ingest of object graphs (replaces the per-match Python loop)
+# ---------------------------------------------------------------------------
+class _Batch(object):
+    __slots__ = ("ids", "meta", "table", "seed", "players", "slot_parts", "matches", "index", "slots")
+
+
+def ingest(matches):
+    """Object graphs -> columns.  Every distinct Player object gets a row of the
+    batch-local table (NaN = attribute is None).  Mirrors the reads of
+    rater.py:70-130 without touching the objects."""
+    b = _Batch()
+    b.matches = list(matches)
+    index, players = {}, []
+    n = len(b.matches)
+    widest = 3
+    for match in b.matches:
+        for roster in match.rosters[:2]:
+            widest = max(widest, len(roster.participants))
+    if widest > 5:
+        raise ValueError("rosters of more than 5 participants are not supported by the kernel")
+    slots = 6 if widest <= 3 else 10
+    half = slots // 2
+    ids = np.full((n, slots), L.EMPTY_SLOT, dtype=np.uint32)
+    meta = np.zeros(n, dtype=np.uint32)
+    slot_parts = [None] * n
+    need_seed = set()
+    for m, match in enumerate(b.matches):
+        mode = _MODE_INDEX.get(match.game_mode, L.MODE_UNSUPPORTED)
+        bits = mode << L.META_MODE_SHIFT
+        if mode == L.MODE_UNSUPPORTED:
+            meta[m] = bits
+            continue
+        if len(match.rosters) != 2:
+            bits |= L.META_INVALID
+        for part in match.participants:          # rater.py:95-100 (stops at the first AFK)
+            if part.went_afk == 1:
+                bits |= L.META_AFK
+                break
+        gated = bits & (L.META_AFK | L.META_INVALID)
+        parts = []
+        if not gated:
+            for t, roster in enumerate(match.rosters):
+                if roster.winner:
+                    bits |= (L.META_WIN_A << t)
+                for k, part in enumerate(roster.participants):
+                    player = part.player[0]
+                    row = index.get(id(player))
+                    if row is None:
+                        row = index[id(player)] = len(players)
+                        players.append(player)
+                    ids[m, t * half + k] = row
+                    parts.append((t * half + k, part))
+                    if player.trueskill_mu is None:
+                        need_seed.add(row)
+        meta[m] = bits
+        slot_parts[m] = parts
+    u = max(len(players), 1)
+    table = np.full((u, 8, 2), np.nan)
+    seed = np.full((u, 2), np.nan)
+    for row, player in enumerate(players):
+        if player.trueskill_mu is not None:
+            table[row, 0] = (float(player.trueskill_mu), float(player.trueskill_sigma))
+        for mi, name in enumerate(MODE_NAMES):
+            mu = getattr(player, _MODE_COLUMN[name] + "_mu", None)
+            if mu is not None:
+                table[row, 1 + mi] = (float(mu), float(getattr(player, _MODE_COLUMN[name] + "_sigma")))
+        if row in need_seed:
+            seed[row] = get_trueskill_seed(player)
+    b.ids, b.meta, b.table, b.seed = ids, meta, table, seed
+    b.players, b.slot_parts, b.index, b.slots = players, slot_parts, index, slots
+    return b
+
+
+def _write_back(b, res):
+    """Columns -> attributes, exactly the stores of rater.py:96-106,141,151-169."""
+    status = res["status"]
+    for m, match in enumerate(b.matches):
+        st = int(status[m])
+        if st == L.ST_SKIP_MODE:
+            logger.info("got unsupported game mode %s", match.game_mode)
+            continue
+        if st in (L.ST_AFK, L.ST_INVALID):
+            if st == L.ST_INVALID or len(match.rosters) != 2:
+                logger.error("got an invalid matchup %s", match.api_id)
+            if int(b.meta[m]) & L.META_AFK:
+                logger.info("got an afk matchup %s", match.api_id)
+            match.trueskill_quality = 0
+            for part in match.participants:
+                part.participant_items[0].any_afk = True
+            continue
+        logger.info("got a valid matchup %s", match.api_id)
+        col = _MODE_COLUMN[match.game_mode]
+        match.trueskill_quality = float(res["quality"][m])
+        for part in match.participants:
+            part.participant_items[0].any_afk = False
+        seen = set()
+        for s, part in b.slot_parts[m]:
+            player = part.player[0]
+            mu, sg = float(res["out_shared"][m, s, 0]), float(res["out_shared"][m, s, 1])
+            # a player listed twice in one match (worker_test.py:130-131) has already
+            # been updated when the reference reaches the second listing: delta 0
+            part.trueskill_delta = float(res["out_delta"][m, s]) if id(player) not in seen else 0.0
+            if player.trueskill_mu is None:
+                part.trueskill_delta = 0
+            seen.add(id(player))
+            player.trueskill_mu = part.trueskill_mu = mu
+            player.trueskill_sigma = part.trueskill_sigma = sg
+        for s, part in b.slot_parts[m]:
+            player, items = part.player[0], part.participant_items[0]
+            mu, sg = float(res["out_queue"][m, s, 0]), float(res["out_queue"][m, s, 1])
+            setattr(player, col + "_mu", mu)
+            setattr(items, col + "_mu", mu)
+            setattr(player, col + "_sigma", sg)
+            setattr(items, col + "_sigma", sg)
+
+
+def rate_matches(matches, device=0):
+    """Rate a chronologically ordered batch of match object graphs in one GPU
+    pass (the loop of worker.py:176-192).  Mutates the objects; returns None.
+    Raises before any object is touched if the reference would have raised for
+    the batch (FloatingPointError / ValueError / KeyError)."""
+    b = ingest(matches)
+    if not b.matches:
+        return None
+    res = _rater(device).rate_batch(b.ids, b.meta, b.table, seed=b.seed, shared_col=0,
+                                    mode_cols=(1, 2, 3, 4, 5, 6), want_outputs=True)
+    _write_back(b, res)
+    return None
+
+
+def rate_match(match):
+    """Mutate a match structure by updating TrueSkill values (rater.py:69).
+    Returns None like the reference (worker.py:192 discards the result)."""
+    return rate_matches([match])
+
+
+def rate_batch(ids, meta, table, seed=None, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6), device=0, **kw):
+    """Columns in, columns out: see engine.Rater.rate_batch."""
+    return _rater(device).rate_batch(ids, meta, table, seed=seed, shared_col=shared_col,
+                                     mode_cols=mode_cols, **kw)

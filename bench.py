@@ -1,0 +1,416 @@
+#!/usr/bin/env python
+"""bench.py -- matches rated/sec (fp64 TrueSkill) on B200, one process per GPU.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+A step is one pass of the hot path over one batch: schedule (radix sort, chain
+link, frontier relaxation, round bucketing) + rate (all rounds) of the
+workload -- BASELINE.json configs[1]: 10M synthetic 3v3 ranked matches over 1M
+players, single (mu, sigma) ladder -- on inputs already resident in HBM.  With
+N GPUs every rank rates its own independent ladder of that size (BASELINE.json
+configs[3]: ladders shard by game mode x region; no data-path collective), so
+scaling is weak and `value` is the sum over ranks / max-over-ranks time.
+
+`e2e` is the same workload through the reference-facing call
+(analyzer_b200.engine.Rater.rate_batch) with pinned HOST buffers: H2D of ids,
+meta and the player table, schedule, rate, D2H of the table, every step.
+
+`--impl reference` times the reference's CPU implementation of the path on the
+host cores: oracle/rater_port.py (the restated rater.py policy) on the
+trueskill-API shim at 50 digits -- the pinned trueskill==0.4.4 is not
+installable (no network) and /root/reference cannot travel to the GPU box.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "matches rated/sec (fp64 TrueSkill)"
+UNIT = "matches/s"
+SEED = 0xA11CE002
+FALLBACK_HBM_GBS = 6650.0     # /opt/skills/guides/B200_PROFILING.md, used only without MEASURED_PEAKS.json
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--matches", type=int, default=10_000_000)
+    ap.add_argument("--players", type=int, default=1_000_000)
+    ap.add_argument("--slots", type=int, default=6)
+    ap.add_argument("--lanes", type=int, default=0, help="lanes per match of the rating kernel (0 = default)")
+    ap.add_argument("--zipf", action="store_true")
+    ap.add_argument("--p-draw", type=float, default=0.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0)
+    ap.add_argument("--skip-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    return "%s synthetic %s matches over %s players, single ladder (K=1 pair per player)%s%s" % (
+        _si(a.matches), "3v3 ranked" if a.slots == 6 else "5v5 ranked", _si(a.players),
+        ", Zipf activity" if a.zipf else "", ", %.0f%% draws" % (100 * a.p_draw) if a.p_draw else "")
+
+
+def _si(n):
+    for div, suf in ((10 ** 9, "B"), (10 ** 6, "M"), (10 ** 3, "k")):
+        if n >= div and n % (div // 10 if div >= 10 else 1) == 0:
+            return ("%g" % (n / div)) + suf
+    return str(n)
+
+
+def rate_bytes_per_match(slots, k=1):
+    """record (4P ids + 4 meta) + gather and scatter of P pairs of 16 B, K pairs each."""
+    return (4 * slots + 4) + 2 * slots * 16 * k
+
+
+def sched_bytes_per_match(slots, n_players):
+    bits = max(1, (n_players).bit_length())
+    return slots * 16 * ((bits + 7) // 8) + 4 * slots + 8
+
+
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+# ---------------------------------------------------------------------------
+# CPU side (oracle/ is executed only here: cpu_baseline leg and --impl reference)
+# ---------------------------------------------------------------------------
+def cpu_reference_rate(ids, meta, table, seconds, draw_probability=0.0):
+    """Single-rate port (one env.rate per match, like the K=1 GPU workload) on a
+    prefix of the stream sized to run for about `seconds`; 1 core, because the
+    reference is one process with one thread (worker.py:219-221)."""
+    import numpy as np
+    from oracle import rater_port as rp
+    env = rp.make_env(draw_probability=draw_probability)
+    probe = min(64, len(ids))
+    ratings = {int(i): (float(table[int(i), 0, 0]), float(table[int(i), 0, 1])) for i in np.unique(ids[:probe])}
+    t0 = time.perf_counter()
+    rp.rate_ladder(ids[:probe], meta[:probe], ratings, env)
+    per = (time.perf_counter() - t0) / probe
+    n = int(max(probe, min(len(ids), seconds / per)))
+    ratings = {int(i): (float(table[int(i), 0, 0]), float(table[int(i), 0, 1])) for i in np.unique(ids[:n])}
+    t0 = time.perf_counter()
+    rp.rate_ladder(ids[:n], meta[:n], ratings, env)
+    dt = time.perf_counter() - t0
+    return n / dt, n, dt
+
+
+def cpu_rate_match_rate(ids, meta, seconds):
+    """The full rate_match (shared + queue rate() + quality) of the port, for context."""
+    import numpy as np
+    from oracle import rater_port as rp
+    n = min(len(ids), 256)
+    players = {int(i): rp.new_player(skill_tier=int(i) % 30) for i in np.unique(ids[:n])}
+    matches = rp.matches_from_columns(ids[:n], meta[:n], players)
+    t0 = time.perf_counter()
+    done = 0
+    for m in matches:
+        rp.rate_match(m)
+        done += 1
+        if time.perf_counter() - t0 > seconds:
+            break
+    return done / (time.perf_counter() - t0), done
+
+
+def cpu_c_baselines(ids, meta, table, n_players):
+    """the closed form in C, fp64, 1 core sequential and
+    round-parallel OpenMP on all host cores (reported, not the target)."""
+    import numpy as np
+    from oracle import c_oracle as co
+    prm = co.make_params()
+    cols = [-1, 0]
+    t = table.copy()
+    t0 = time.perf_counter()
+    co.rate_sequential(prm, ids, meta, t, -1, cols, quad=False)
+    seq = len(ids) / (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    rnd, order, offs, R = co.schedule(ids, meta, cols, n_players)
+    sched_s = time.perf_counter() - t0
+    t = table.copy()
+    t0 = time.perf_counter()
+    co.rate_rounds_omp(prm, ids, meta, t, -1, cols, order, offs, R)
+    omp = len(ids) / (time.perf_counter() - t0)
+    return dict(c_fp64_1core=seq, c_fp64_omp=omp, omp_threads=co.max_threads(),
+                c_schedule_matches_per_s=len(ids) / sched_s, sample_matches=len(ids), rounds=R)
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import numpy as np
+    from oracle import c_oracle as co
+    co.build()
+    gen = co.make_gen(SEED, a.players, slots=a.slots, mode=1, p_draw=a.p_draw, zipf=a.zipf)
+    budget = 90.0 / max(1, a.steps + a.warmup)          # whole run ~1.5 min of CPU work
+    sample = max(64, int(budget * 300))
+    ids, meta = co.gen_matches(gen, 0, sample)
+    table = co.gen_table(SEED, 0, a.players)
+    times = []
+    n_done = 0
+    for step in range(a.warmup + a.steps):
+        rate, n_done, dt = cpu_reference_rate(ids, meta, table, budget, a.p_draw)
+        if step >= a.warmup:
+            times.append(dt / n_done)
+    per_match = sum(times) / len(times)
+    value = 1.0 / per_match
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1e3 * per_match * n_done,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "mpmath-50-digit",
+        "data": "synthetic", "config": {"workload": workload_name(a), "seed": hex(SEED)},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
+                         "sample": "first %d matches of the workload's stream per step; oracle/rater_port.py "
+                                   "rate_ladder (one env.rate per match) on the trueskill-API shim, mpmath 50 "
+                                   "digits; 1 core because the reference is single-process/single-thread "
+                                   "(worker.py:219-221)" % n_done},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------
+# clocks during the timed region (NVML, sampled from a thread)
+# ---------------------------------------------------------------------------
+class ClockSampler(object):
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+                util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+                bits = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                self.samples.append((mhz, util))
+                for b, name in self.REASONS.items():
+                    if bits & b and name != "gpu_idle":
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def start(self):
+        if self.nv:
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thread:
+            self._thread.join()
+        mhz = sorted(m for m, _ in self.samples)
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(mhz)}
+
+
+# ---------------------------------------------------------------------------
+def run_b200(a):
+    import numpy as np
+    import torch
+    from analyzer_b200 import engine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the rating path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    n, u, p = a.matches, a.players, a.slots
+    seed = SEED + rank                      # an independent ladder per GPU
+    rater = engine.Rater(engine.Env(draw_probability=a.p_draw), local)
+    gen = engine.make_gen(seed, u, slots=p, mode=1, p_draw=a.p_draw, zipf=a.zipf)
+    ids_d, meta_d = engine.gen_matches(gen, 0, n, dev)
+    table0 = engine.gen_table(seed, 0, u, dev)
+    table = table0.clone()
+    ptab = engine.PlayerTable.ladder(table, mode=1)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    sched_ms, rate_ms = [], []
+    n_rounds = 0
+
+    def step(timed):
+        nonlocal n_rounds
+        table.copy_(table0)
+        flush.fill_(1)                       # evict ids/table from L2 between steps
+        e0, e1, e2 = ev(), ev(), ev()
+        e0.record()
+        sch = rater.schedule(ids_d, meta_d, u, ptab.mode_cols)
+        e1.record()
+        rater.rate(ptab, sch, None, a.lanes)
+        e2.record()
+        n_rounds = sch.n_rounds
+        if timed:
+            torch.cuda.synchronize()
+            sched_ms.append(e0.elapsed_time(e1))
+            rate_ms.append(e1.elapsed_time(e2))
+        return sch
+
+    for _ in range(a.warmup):
+        step(False)
+    sampler = ClockSampler(local)
+    barrier()
+    sampler.start()
+    t_wall = time.perf_counter()
+    for _ in range(a.steps):
+        step(True)
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    clocks = sampler.stop()
+    assert rater.error_count() == 0
+
+    ms_sched = sum(sched_ms) / len(sched_ms)
+    ms_rate = sum(rate_ms) / len(rate_ms)
+    ms_step = ms_sched + ms_rate
+    if dist is not None:
+        t = torch.tensor([ms_step, ms_sched, ms_rate], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_step, ms_sched, ms_rate = (float(x) for x in t.cpu())
+
+    # ---- e2e: the reference-facing call with pinned host buffers -----------
+    e2e = None
+    if not a.skip_e2e:
+        ids_h = ids_d.cpu().pin_memory()
+        meta_h = meta_d.cpu().pin_memory()
+        tab_h = table0.cpu().pin_memory()
+        out_h = torch.empty_like(tab_h).pin_memory()
+        k_e2e = max(1, min(a.steps, 5))
+        res = None
+        for it in range(1 + k_e2e):          # 1 warm-up
+            if it == 1:
+                barrier()
+                t0 = time.perf_counter()
+            res = rater.rate_batch(ids_h, meta_h, tab_h, shared_col=-1, mode_cols=ptab.mode_cols[:6],
+                                   want_outputs=False, lanes_per_match=a.lanes, table_out=out_h)
+        barrier()
+        dt = (time.perf_counter() - t0) / k_e2e
+        if dist is not None:
+            t = torch.tensor([dt], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.cpu()[0])
+        # the e2e result must be the same table the device-resident path produced
+        assert torch.equal(out_h, table.cpu()), "e2e table differs from the HBM-resident run"
+        h2d = ids_h.numel() * 4 + meta_h.numel() * 4 + tab_h.numel() * 8
+        e2e = {"value": n * world / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": out_h.numel() * 8 + 8 + 16, "ms_per_step": dt * 1e3, "steps": k_e2e}
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = hbm_peak()
+    b_rate = rate_bytes_per_match(p, 1)
+    achieved = b_rate * n / (ms_rate * 1e-3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "rate_kernel_traffic.json")
+    if os.path.exists(tp):
+        try:
+            tj = json.load(open(tp))
+            if tj.get("matches") == n and tj.get("slots") == p:
+                traffic = tj.get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    b_sched = sched_bytes_per_match(p, u)
+    passes_p = (max(1, u.bit_length()) + 7) // 8
+    passes_r = (max(1, n_rounds.bit_length()) + 7) // 8
+    launches = 4 * passes_p + 2 + 1 + 1 + 4 * passes_r + 1 + 1   # sort, link+init, frontier, offsets, sort, permute, rate
+    line = {
+        "metric": METRIC, "value": n * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_name(a), "seed": hex(SEED), "rounds": n_rounds,
+                   "per_gpu": "one independent ladder per GPU, no data-path collective" if world > 1 else "single GPU",
+                   "l2": "256 MiB flush between steps; ids+meta (%d MB) exceed the 126 MB L2; the %d MB player "
+                         "table is L2-resident by nature" % ((n * p * 4 + n * 4) >> 20, (u * 16) >> 20),
+                   "lanes_per_match": a.lanes or 2},
+        "phases": {"schedule_ms": ms_sched, "rate_ms": ms_rate,
+                   "rate_only_matches_per_s": n * world / (ms_rate * 1e-3),
+                   "schedule_only_matches_per_s": n * world / (ms_sched * 1e-3)},
+        "roofline": {"kernel": "k_rate", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_match": b_rate,
+                     "note": "one launch per step; duration = CUDA events around ts_rate on its stream"},
+        "roofline_schedule": {"bound": "hbm", "achieved": b_sched * n / (ms_sched * 1e-3) / 1e9, "peak": peak,
+                              "unit": "GB/s", "frac": b_sched * n / (ms_sched * 1e-3) / 1e9 / peak,
+                              "algorithmic_bytes_per_match": b_sched},
+        "gpu_launches": launches * a.steps,
+        "clocks": clocks,
+        "wall_s_timed_region": t_wall,
+    }
+    if e2e:
+        line["e2e"] = e2e
+    if world == 1 and not a.no_cpu_baseline:
+        sample = min(n, 200_000)
+        ids = ids_d[:sample].cpu().numpy().view(np.uint32)
+        meta = meta_d[:sample].cpu().numpy().view(np.uint32)
+        tab = table0.cpu().numpy()
+        value, n_done, dt = cpu_reference_rate(ids, meta, tab, a.cpu_seconds, a.p_draw)
+        full, n_full = cpu_rate_match_rate(ids, meta, 3.0)
+        cb = {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
+              "sample": "first %d matches of the same stream (%.1f s); oracle/rater_port.py rate_ladder (one "
+                        "env.rate per match, like the GPU workload) on the restated trueskill API at 50 digits; "
+                        "the pinned trueskill==0.4.4 is not installable here" % (n_done, dt),
+              "rate_match_value": full,
+              "rate_match_note": "full rate_match (2 x rate + quality) on %d matches" % n_full}
+        try:
+            cb.update(cpu_c_baselines(ids, meta, tab, u))
+        except Exception as exc:   # the C oracle is optional context, never the product
+            cb["c_error"] = repr(exc)
+        line["cpu_baseline"] = cb
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    args = parse()
+    sys.exit(run_reference(args) if args.impl == "reference" else run_b200(args))

@@ -1,0 +1,161 @@
+/* tsrate.h -- C ABI of libtsrate.so, the B200 (sm_100a) TrueSkill rating hot path
+ * of vainglorygame/analyzer.
+ *
+ * The reference is pure Python and has no FFI of its own; each entry point
+ * below names the reference code (file:line under the analyzer tree) whose
+ * work it takes over.  All pointers marked "device" are CUDA device pointers
+ * owned by the caller (the Python host passes torch tensors' data_ptr()); the
+ * library allocates nothing but the few hundred bytes of control words held
+ * by a ts_ctx.  Every call enqueues on the caller's stream (a cudaStream_t
+ * passed as void*) and returns 0 on success or a negative TS_E_* code;
+ * ts_last_error() gives the text.  Nothing throws.
+ */
+#ifndef TSRATE_H
+#define TSRATE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TS_MAX_SLOTS 16          /* match record width limit (teams of up to 8) */
+#define TS_EMPTY_SLOT 0xFFFFFFFFu /* id of an unused slot in a match record   */
+#define TS_NONE 0xFFFFFFFFu
+
+/* match meta word (one uint32 per match) */
+#define TS_META_WIN_A 1u    /* roster 0 .winner           (rater.py:144)        */
+#define TS_META_WIN_B 2u    /* roster 1 .winner                                 */
+#define TS_META_AFK 4u      /* some participant.went_afk  (rater.py:95-100)     */
+#define TS_META_INVALID 8u  /* len(rosters) != 2          (rater.py:91-93)      */
+#define TS_META_MODE_SHIFT 4 /* bits 4..7: game mode 0..5 (rater.py:70-82), 15 = unsupported */
+
+/* per-match status byte */
+enum {
+    TS_ST_OK = 0,
+    TS_ST_SKIP_MODE = 1,   /* unsupported game mode: untouched (rater.py:83-85)          */
+    TS_ST_AFK = 2,         /* AFK gate: quality 0, no rating change (rater.py:102-106)    */
+    TS_ST_INVALID = 3,     /* roster-count gate, same effect                              */
+    TS_ST_FP_ERROR = 4,    /* trueskill raises FloatingPointError (w outside (0,1), zero mass) */
+    TS_ST_VALUE_ERROR = 5  /* trueskill raises ValueError (sigma == 0, empty team) or a
+                              player has neither a stored rating nor a seed            */
+};
+
+enum {
+    TS_E_ARG = -1,      /* bad argument                                  */
+    TS_E_CUDA = -2,     /* a CUDA runtime call failed                    */
+    TS_E_WORKSPACE = -3,/* workspace / offsets capacity too small        */
+    TS_E_UNSUPPORTED = -4
+};
+
+/* Environment of rater.py:30-37 (beta, tau, draw_probability), with the draw
+ * margin calc_draw_margin() would give for a match of n players precomputed
+ * by the host (n = index).  draw_is_zero selects the analytic draw limit
+ * (v = -t, w = 1) that the reference reaches at draw_probability = 0. */
+typedef struct ts_params {
+    double beta;
+    double tau;
+    double draw_margin[TS_MAX_SLOTS + 1];
+    int32_t draw_is_zero;
+    int32_t reserved;
+} ts_params;
+
+/* The HBM-resident player table: n_players rows of row_pairs (mu, sigma)
+ * pairs of doubles, NaN mu = SQL NULL.  Replaces the player columns
+ * worker.py:184-190 loads: trueskill_mu/_sigma (shared_col) and the six
+ * trueskill_<mode>_mu/_sigma pairs (mode_col[mode]).  shared_col = -1 gives
+ * the single-pair ladder of BASELINE.json (one rate() per match).
+ * seed (optional) holds get_trueskill_seed() per player (rater.py:42-62). */
+typedef struct ts_table {
+    double *data;          /* device, [n_players][row_pairs][2] */
+    const double *seed;    /* device, [n_players][2] or NULL    */
+    int64_t n_players;
+    int32_t row_pairs;
+    int32_t shared_col;
+    int8_t mode_col[16];   /* column of each game mode, -1 = mode not rated */
+} ts_table;
+
+/* Result of ts_schedule, written to device memory so ts_rate can follow on
+ * the same stream. */
+typedef struct ts_sched_info {
+    uint32_t n_rounds;     /* largest round; rounds 1..n_rounds are rated  */
+    uint32_t n_gated;      /* matches in bucket 0 (they touch no player)    */
+    uint32_t overflow;     /* 1 if round_offsets capacity was too small     */
+    uint32_t reserved;
+} ts_sched_info;
+
+/* Optional per-match / per-participant outputs of rate_match, indexed by the
+ * ORIGINAL match index (not schedule order).  Any pointer may be NULL. */
+typedef struct ts_outputs {
+    double *quality;     /* device [N]       match.trueskill_quality        (rater.py:103,141) */
+    double *out_shared;  /* device [N][P][2] participant.trueskill_mu/sigma (rater.py:155,157) */
+    double *out_delta;   /* device [N][P]    participant.trueskill_delta    (rater.py:150-153) */
+    double *out_queue;   /* device [N][P][2] participant_items <mode>_mu/sigma (rater.py:167,169) */
+    uint8_t *status;     /* device [N]       TS_ST_*                                          */
+} ts_outputs;
+
+typedef struct ts_ctx ts_ctx;
+
+/* rater.py:30-37 `env = trueskill.TrueSkill(...)` -- one context per device. */
+int ts_ctx_create(const ts_params *params, int device, ts_ctx **out);
+void ts_ctx_destroy(ts_ctx *ctx);
+const char *ts_last_error(void);
+int ts_sm_count(const ts_ctx *ctx);
+
+/* Bytes of device workspace ts_schedule needs for N matches of P slots. */
+int64_t ts_schedule_workspace_bytes(int64_t n_matches, int32_t slots);
+
+/* Replaces the ORDER BY created_at loop of worker.py:176-192: gives every
+ * match the earliest conflict-free round that keeps each player's matches in
+ * stream order.  ids: device [N][P] player ids in match_seq order (first P/2
+ * slots roster 0, rest roster 1, TS_EMPTY_SLOT = unused); meta: device [N].
+ * Outputs (device): round[N]; order[N] = match indices sorted by (round,
+ * match_seq); round_offsets[offsets_cap] with bucket r at
+ * [round_offsets[r], round_offsets[r+1]), r = 0 (gated) .. n_rounds;
+ * ids_sorted[N][P] / meta_sorted[N] = the records permuted into that order;
+ * info.  Synchronises the stream once (to size the final sort).
+ * On success *n_rounds_host (optional) receives n_rounds. */
+int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches,
+                int32_t slots, int64_t n_players, const int8_t mode_col[16],
+                uint32_t *round, uint32_t *order, uint32_t *round_offsets, int64_t offsets_cap,
+                uint32_t *ids_sorted, uint32_t *meta_sorted, ts_sched_info *info,
+                void *workspace, int64_t workspace_bytes, uint32_t *n_rounds_host, void *stream);
+
+/* Replaces rater.py:108-169 for every match of the batch: gather the players'
+ * pairs, quality, rate(shared), delta, rate(queue), scatter -- one persistent
+ * kernel walking the rounds of a schedule.  lanes_per_match: 0 = default, or
+ * one of 1,2,4,8,16,32 (how many lanes of a warp share one match). */
+int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_sorted,
+            const uint32_t *meta_sorted, const uint32_t *order, const uint32_t *round_offsets,
+            const ts_sched_info *info, int64_t n_matches, int32_t slots,
+            const ts_outputs *outputs, int32_t lanes_per_match, void *stream);
+
+/* Number of matches that ended in TS_ST_FP_ERROR / TS_ST_VALUE_ERROR since the
+ * last ts_reset_errors (the reference raises and fails the whole batch,
+ * worker.py:108-120,195-197).  Synchronises the stream. */
+int64_t ts_error_count(ts_ctx *ctx, void *stream);
+int ts_reset_errors(ts_ctx *ctx, void *stream);
+
+/* Synthetic ladders of BASELINE.json's configs (SURVEY.md 8d "Generator"):
+ * counter-based, so any window [first, first+count) can be produced on its
+ * own.  No counterpart in the reference (it has no benchmark input). */
+typedef struct ts_gen {
+    uint64_t seed;
+    uint64_t n_players;
+    int32_t slots;
+    int32_t mode;
+    uint32_t draw_thr;   /* P(draw) * 2^32     */
+    uint32_t afk_thr;    /* P(AFK gate) * 2^32 */
+    int32_t zipf;        /* 0 uniform, 1 Zipf-Mandelbrot (rank + q)^-0.8 */
+    double zipf_a;       /* q^0.2               */
+    double zipf_b;       /* (U + q)^0.2 - q^0.2 */
+    double zipf_q;
+} ts_gen;
+int ts_gen_matches(const ts_gen *gen, int64_t first, int64_t count, uint32_t *ids, uint32_t *meta,
+                   void *stream);
+int ts_gen_table(uint64_t seed, int64_t first, int64_t count, double *table, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TSRATE_H */

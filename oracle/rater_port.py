@@ -235,3 +235,31 @@ def matches_from_columns(ids, meta, players):
             teams.append((False, []))
         out.append(new_match(name, teams, api_id=str(m)))
     return out
+
+
+def rate_ladder(ids, meta, ratings, env=env, mode_cols=None):
+    """The single-ladder form of the path (BASELINE.json configs[1..4]): one
+    (mu, sigma) per player and ONE env.rate per match -- rater.py:108-169 with
+    only the queue-specific rating kept.  `ratings` maps player id -> (mu,
+    sigma) floats and is updated in place, match after match in stream order
+    (worker.py:192).  Gated matches are skipped (rater.py:83-85,102-106)."""
+    n, p = ids.shape
+    half = p // 2
+    for m in range(n):
+        bits = int(meta[m])
+        mode = (bits >> MODE_SHIFT) & MODE_MASK
+        if mode >= 6 or (mode_cols is not None and mode_cols[mode] < 0):
+            continue
+        if bits & (META_AFK | META_INVALID):
+            continue
+        teams, who = [], []
+        for t in range(2):
+            row = [int(x) for x in ids[m, t * half:(t + 1) * half] if x != EMPTY]
+            who.append(row)
+            teams.append([env.create_rating(float(ratings[i][0]), float(ratings[i][1])) for i in row])
+        ranks = [int(not (bits & META_WIN_A)), int(not (bits & META_WIN_B))]
+        new = env.rate(teams, ranks=ranks)
+        for row, team in zip(who, new):
+            for i, r in zip(row, team):
+                ratings[i] = (r.mu, r.sigma)
+    return ratings

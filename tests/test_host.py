@@ -1,0 +1,101 @@
+"""Host-side logic that needs no GPU: seed policy, columnar ingest, draw margin,
+and that libtsrate.so loads and exports every symbol include/tsrate.h declares."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from analyzer_b200 import _lib as L
+from analyzer_b200 import engine
+from oracle import rater_port as rp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def rater_mod():
+    from analyzer_b200 import rater
+    return rater
+
+
+def test_library_exports_every_declared_symbol():
+    L.build()
+    header = open(os.path.join(ROOT, "include", "tsrate.h")).read()
+    declared = set(re.findall(r"\b(ts_[a-z_0-9]+)\s*\(", header))
+    assert declared and declared == set(L.EXPORTS)
+    lib = ctypes.CDLL(L.LIB_PATH)
+    for name in declared:
+        assert getattr(lib, name) is not None
+    # struct sizes the ctypes mirrors must agree with (checked again on the GPU box by use)
+    assert ctypes.sizeof(L.TsParams) == 8 * 2 + 8 * 17 + 8
+    assert ctypes.sizeof(L.TsTable) == 8 + 8 + 8 + 4 + 4 + 16
+    assert ctypes.sizeof(L.TsSchedInfo) == 16 and ctypes.sizeof(L.TsOutputs) == 40
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(RuntimeError):
+        engine.Rater(engine.Env(), 0)
+    from analyzer_b200 import rater
+    m = rp.new_match("ranked", [(True, [rp.new_participant(rp.new_player(skill_tier=3))]),
+                                (False, [rp.new_participant(rp.new_player(skill_tier=4))])])
+    with pytest.raises(RuntimeError):
+        rater.rate_match(m)
+
+
+def test_vst_points_and_seed_match_reference_policy(rater_mod):
+    assert rater_mod.vst_points == rp.vst_points          # port is checked against rater.py:13-27 live
+    assert rater_mod.env.beta == 1000.0 and rater_mod.env.tau == 10.0 and rater_mod.env.draw_probability == 0
+    cases = [(None, None, 15), (2500, None, 0), (2500, 100, 0), (100, 2500, 0), (None, 2500, 0),
+             (0, 0, 7), (0, 1200, -1), (3000.5, 2999, 29)]
+    for ranked, blitz, tier in cases:
+        p = rp.new_player(skill_tier=tier, rank_points_ranked=ranked, rank_points_blitz=blitz)
+        assert rater_mod.get_trueskill_seed(p) == rp.seed_from_fields(ranked, blitz, tier)
+    for ranked, blitz in [(2500, None), (2500, 100), (100, 2500), (None, 2500)]:   # worker_test.py:86-113
+        mu, sigma = rater_mod.get_trueskill_seed(rp.new_player(skill_tier=0, rank_points_ranked=ranked,
+                                                               rank_points_blitz=blitz))
+        assert mu - sigma == 2500
+    with pytest.raises(KeyError):
+        rater_mod.get_trueskill_seed(rp.new_player(skill_tier=30))
+
+
+def test_draw_margin_matches_package_formula(c_oracle):
+    for p in (0.0, 0.02, 0.10):
+        want = c_oracle.draw_margins(1000.0, p)     # 50-digit ppf through the shim
+        for n in (2, 6, 10):
+            got = engine.draw_margin(p, n, 1000.0)
+            assert abs(got - want[n]) <= 1e-9 * max(1.0, abs(want[n]))
+    prm = engine.Env(draw_probability=0.02).params()
+    assert prm.draw_is_zero == 0 and prm.draw_margin[10] > prm.draw_margin[6] > 0
+    assert engine.Env().params().draw_is_zero == 1
+
+
+def test_ingest_columns(rater_mod):
+    a, b, c = (rp.new_player(skill_tier=t) for t in (3, 4, 5))
+    d = rp.new_player(trueskill_mu=2000, trueskill_sigma=100, trueskill_ranked_mu=1900, trueskill_ranked_sigma=90)
+    mk = rp.new_participant
+    m0 = rp.new_match("ranked", [(True, [mk(a), mk(b)]), (False, [mk(c), mk(d)])])
+    m1 = rp.new_match("aral", [(True, [mk(a)]), (False, [mk(b)])])                       # unsupported
+    m2 = rp.new_match("casual", [(False, [mk(a), mk(b, went_afk=1)]), (True, [mk(c)])])   # AFK
+    m3 = rp.new_match("blitz", [(False, [mk(d)]), (False, [mk(a)]), (True, [mk(b)])])    # 3 rosters
+    m4 = rp.new_match("5v5_ranked", [(False, [mk(d), mk(a), mk(b), mk(c)]), (True, [mk(a)])])
+    bt = rater_mod.ingest([m0, m1, m2, m3, m4])
+    assert bt.slots == 10 and bt.ids.shape == (5, 10)
+    E = L.EMPTY_SLOT
+    assert list(bt.ids[0]) == [0, 1, E, E, E, 2, 3, E, E, E]
+    assert list(bt.ids[4]) == [3, 0, 1, 2, E, 0, E, E, E, E]
+    assert np.all(bt.ids[1:4] == E)
+    assert list(bt.meta) == [1 | (1 << 4), 15 << 4, 4 | (0 << 4), 8 | (2 << 4), 2 | (5 << 4)]
+    assert bt.table.shape == (4, 8, 2)
+    assert np.isnan(bt.table[0]).all() and list(bt.table[3, 0]) == [2000.0, 100.0]
+    assert list(bt.table[3, 2]) == [1900.0, 90.0] and np.isnan(bt.table[3, 1]).all()
+    assert tuple(bt.seed[0]) == rp.seed_from_fields(None, None, 3) and np.isnan(bt.seed[3]).all()
+    with pytest.raises(ValueError):
+        rater_mod.ingest([rp.new_match("ranked", [(True, [mk(a)] * 6), (False, [mk(b)])])])
+    bad = rp.new_player(skill_tier=None)
+    with pytest.raises(KeyError):
+        rater_mod.ingest([rp.new_match("ranked", [(True, [mk(bad)]), (False, [mk(b)])])])
