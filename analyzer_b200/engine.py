@@ -174,10 +174,10 @@ class Rater(object):
         n, p = ids.shape
         sch = Schedule(n, p)
         dev = ids.device
-        cap = int(offsets_cap if offsets_cap is not None else n + 2)
+        cap = max(3, int(offsets_cap if offsets_cap is not None else n + 2))
         sch.round = torch.empty(n, dtype=torch.int32, device=dev)
         sch.order = torch.empty(n, dtype=torch.int32, device=dev)
-        sch.round_offsets = torch.empty(max(cap, 3), dtype=torch.int32, device=dev)
+        sch.round_offsets = torch.empty(cap, dtype=torch.int32, device=dev)
         sch.ids_sorted = torch.empty_like(ids)
         sch.meta_sorted = torch.empty_like(meta)
         sch.info = torch.zeros(4, dtype=torch.int32, device=dev)
