@@ -10,7 +10,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libtsrate.so")
-SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu"]
+SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "static_sched.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-shared", "-Xcompiler", "-fPIC"]
 
@@ -23,7 +23,8 @@ ST_OK, ST_SKIP_MODE, ST_AFK, ST_INVALID, ST_FP_ERROR, ST_VALUE_ERROR = range(6)
 
 EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_workspace_bytes", "ts_schedule", "ts_rate", "ts_error_count",
-           "ts_reset_errors", "ts_gen_matches", "ts_gen_table"]
+           "ts_reset_errors", "ts_gen_matches", "ts_gen_table",
+           "ts_schedule_static", "ts_schedule_static_max_slot_entries"]
 
 
 class TsParams(C.Structure):
@@ -98,6 +99,10 @@ def lib():
                                   C.POINTER(C.c_int8), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
                                   C.POINTER(C.c_uint32), C.c_void_p]
+        L.ts_schedule_static.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
+                                         C.POINTER(C.c_int8), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint32), C.c_void_p]
+        L.ts_schedule_static_max_slot_entries.restype = C.c_int64
         L.ts_rate.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.POINTER(TsOutputs),
                               C.c_int32, C.c_void_p]

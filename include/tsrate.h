@@ -121,6 +121,31 @@ int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t 
                 uint32_t *ids_sorted, uint32_t *meta_sorted, ts_sched_info *info,
                 void *workspace, int64_t workspace_bytes, uint32_t *n_rounds_host, void *stream);
 
+/* ts_schedule without any allocation.  No counterpart in the reference: it is
+ * for hosts that embed this library where device memory is not theirs to
+ * allocate -- a plugin inside a service that hands out device memory from its
+ * own pool, a process whose HBM is already reserved by another framework -- and
+ * that therefore can call neither cudaMalloc (for a workspace) nor
+ * ts_ctx_create (which allocates its control words).  Inputs and outputs are
+ * still the caller's; the scratch is a 2 MiB array built into the library image
+ * on every GPU that loads it.  Same arguments and results as ts_schedule, minus
+ * ctx / workspace, plus the device ordinal.
+ *   - n_matches * slots must not exceed TS_STATIC_MAX_SLOT_ENTRIES, else
+ *     TS_E_WORKSPACE (ts_last_error says so);
+ *   - the first call on a device resolves the array's device address and caches
+ *     it: make that call before any stream capture;
+ *   - all calls share the array; it is not cleared between calls except for what
+ *     the scheduler needs zeroed, which each call clears on `stream` itself;
+ *     calls whose GPU work can overlap race -- serialise them;
+ *   - performs no cudaMalloc / cudaFree / allocating library call. */
+#define TS_STATIC_MAX_SLOT_ENTRIES 65536
+int ts_schedule_static(int device, const uint32_t *ids, const uint32_t *meta, int64_t n_matches,
+                       int32_t slots, int64_t n_players, const int8_t mode_col[16],
+                       uint32_t *round, uint32_t *order, uint32_t *round_offsets, int64_t offsets_cap,
+                       uint32_t *ids_sorted, uint32_t *meta_sorted, ts_sched_info *info,
+                       uint32_t *n_rounds_host, void *stream);
+int64_t ts_schedule_static_max_slot_entries(void);
+
 /* Replaces rater.py:108-169 for every match of the batch: gather the players'
  * pairs, quality, rate(shared), delta, rate(queue), scatter -- one persistent
  * kernel walking the rounds of a schedule.  lanes_per_match: 0 = default, or
