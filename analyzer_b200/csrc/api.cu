@@ -22,6 +22,12 @@ int ts_cuda_fail(cudaError_t e, const char *what)
 
 extern "C" const char *ts_last_error(void) { return g_err; }
 
+int ts_reset_barrier(unsigned long long *d_ctrl, cudaStream_t stream)
+{
+    TS_CUDA(cudaMemsetAsync(d_ctrl, 0, 2 * sizeof(unsigned long long), stream));
+    return 0;
+}
+
 extern "C" int ts_ctx_create(const ts_params *params, int device, ts_ctx **out)
 {
     if (!params || !out) {
@@ -54,8 +60,8 @@ extern "C" int ts_ctx_create(const ts_params *params, int device, ts_ctx **out)
     c->sm_count = prop.multiProcessorCount;
     c->params = *params;
     c->d_ctrl = nullptr;
-    cudaError_t e = cudaMalloc(&c->d_ctrl, CTRL_WORDS * sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMemset(c->d_ctrl, 0, CTRL_WORDS * sizeof(unsigned long long));
+    cudaError_t e = cudaMalloc(&c->d_ctrl, TS_CTRL_BYTES);
+    if (e == cudaSuccess) e = cudaMemset(c->d_ctrl, 0, TS_CTRL_BYTES);
     if (e != cudaSuccess) {
         delete c;
         return ts_cuda_fail(e, "control words");

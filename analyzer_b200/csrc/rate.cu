@@ -20,6 +20,8 @@
 // read with ld.global.cg / written with st.global.cg (L2 is the coherence
 // point across SMs; L1 is not coherent), as 16-byte vectors.  Match records of
 // a tile are staged through shared memory with coalesced loads.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace {
@@ -106,13 +108,50 @@ __device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, boo
     return true;
 }
 
+// ---- asynchronous staging of match records (cp.async = LDGSTS) -------------
+__device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)
+{
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(void *smem, const void *gmem)
+{
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+template <int P, int G>
+struct RecordStage {
+    uint32_t ids[2][G * P];
+    uint32_t meta[2][G];
+    uint32_t order[2][G];
+};
+
+// Start copying the records of tile `tile` of the round [lo, hi) into buffer b.
+// Records do not depend on the player table, so this runs ahead of the grid
+// barrier that orders the table accesses of consecutive rounds.
+template <int P, int G>
+__device__ __forceinline__ void stage_tile(RecordStage<P, G> &st, int b, const RateArgs &a, uint32_t lo,
+                                           uint32_t hi, uint32_t tile, bool want_order)
+{
+    const uint32_t base = lo + tile * G;
+    const uint32_t cnt = min((uint32_t)G, hi - base);
+    const uint32_t *src = a.ids_sorted + (size_t)base * P;   // base * P * 4 bytes: 8-byte aligned (P even)
+    for (uint32_t i = threadIdx.x; i < cnt * (P / 2); i += blockDim.x) cp_async_8(&st.ids[b][2 * i], src + 2 * i);
+    for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) {
+        cp_async_4(&st.meta[b][i], a.meta_sorted + base + i);
+        if (want_order) cp_async_4(&st.order[b][i], a.order + base + i);
+    }
+}
+
 template <int P, int L, bool SHARED>
 __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
 {
     constexpr int G = kBlock / L;               // matches per tile
     constexpr int SPL = (P + L - 1) / L;        // slots per lane
     constexpr int HALF = P / 2;
-    __shared__ uint32_t sm_ids[G * P];
+    __shared__ __align__(16) RecordStage<P, G> stage;
 
     const int tid = threadIdx.x;
     const int lane = tid % L;
@@ -121,35 +160,43 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
     const double beta2 = a.prm.beta * a.prm.beta;
     const double tb2 = tau2 + beta2;
     const uint32_t n_rounds = __ldcg(&a.info->n_rounds);
+    const bool want_order = a.out.quality || a.out.out_shared || a.out.out_delta || a.out.out_queue || a.out.status;
     unsigned long long generation = 0;
 
-    for (uint32_t r = 0; r <= n_rounds; ++r) {
-        const uint32_t lo = __ldg(a.round_offsets + r), hi = __ldg(a.round_offsets + r + 1);
-        const uint32_t n_tiles = (hi - lo + G - 1) / G;
-        if (r == 0) {
-            // bucket 0: gated matches (rater.py:83-85, 102-106) -- outputs only
-            if (a.out.status != nullptr || a.out.quality != nullptr) {
-                for (uint32_t j = lo + blockIdx.x * kBlock + tid; j < hi; j += gridDim.x * kBlock) {
-                    uint32_t meta = __ldg(a.meta_sorted + j), m = __ldg(a.order + j);
-                    uint32_t mode = (meta >> TS_META_MODE_SHIFT) & 15u;
-                    bool skip = mode >= 6u || a.modes.col[mode] < 0;
-                    uint8_t st = skip ? TS_ST_SKIP_MODE : ((meta & TS_META_INVALID) ? TS_ST_INVALID : TS_ST_AFK);
-                    if (a.out.status) a.out.status[m] = st;
-                    if (!skip && a.out.quality) a.out.quality[m] = 0.0;
-                }
-            }
-            continue;   // nothing in bucket 0 touches the table: no barrier needed
+    // bucket 0: gated matches (rater.py:83-85, 102-106) -- outputs only; nothing
+    // here touches the table, so no barrier is needed before round 1
+    if (a.out.status != nullptr || a.out.quality != nullptr) {
+        const uint32_t lo = __ldg(a.round_offsets), hi = __ldg(a.round_offsets + 1);
+        for (uint32_t j = lo + blockIdx.x * kBlock + tid; j < hi; j += gridDim.x * kBlock) {
+            uint32_t meta = __ldg(a.meta_sorted + j), m = __ldg(a.order + j);
+            uint32_t mode = (meta >> TS_META_MODE_SHIFT) & 15u;
+            bool skip = mode >= 6u || a.modes.col[mode] < 0;
+            uint8_t st = skip ? TS_ST_SKIP_MODE : ((meta & TS_META_INVALID) ? TS_ST_INVALID : TS_ST_AFK);
+            if (a.out.status) a.out.status[m] = st;
+            if (!skip && a.out.quality) a.out.quality[m] = 0.0;
         }
+    }
+    if (n_rounds == 0) return;
+
+    // round bounds travel one round ahead in registers: lo/hi of the current
+    // round and hi of the next, so nothing on the post-barrier path waits for them
+    uint32_t lo = __ldg(a.round_offsets + 1), hi = __ldg(a.round_offsets + 2);
+    uint32_t hi_next = n_rounds >= 2 ? __ldg(a.round_offsets + 3) : hi;
+    int pf = 0;   // staging buffer that holds / will hold the next tile of this block
+    if (blockIdx.x < (hi - lo + G - 1) / G) stage_tile<P, G>(stage, pf, a, lo, hi, blockIdx.x, want_order);
+
+    for (uint32_t r = 1; r <= n_rounds; ++r) {
+        const uint32_t n_tiles = (hi - lo + G - 1) / G;
         for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            cp_async_wait_all();
+            __syncthreads();               // tile's records landed; everyone is done with the other buffer
+            const int cur = pf;
+            pf ^= 1;
+            if (tile + gridDim.x < n_tiles) stage_tile<P, G>(stage, pf, a, lo, hi, tile + gridDim.x, want_order);
             const uint32_t base = lo + tile * G;
             const uint32_t cnt = min((uint32_t)G, hi - base);
-            __syncthreads();   // previous tile's readers are done with sm_ids
-            for (uint32_t i = tid; i < cnt * P; i += kBlock)
-                sm_ids[i] = __ldg(a.ids_sorted + (size_t)base * P + i);
-            __syncthreads();
             const bool live = (uint32_t)grp < cnt;
-            const uint32_t j = base + grp;
-            const uint32_t meta = live ? __ldg(a.meta_sorted + j) : 0u;
+            const uint32_t meta = live ? stage.meta[cur][grp] : 0u;
             const uint32_t mode = (meta >> TS_META_MODE_SHIFT) & 15u;
             const int qcol = live ? a.modes.col[mode & 7u] : 0;
             // winner first, stable (rater.py:144: rank = int(not winner))
@@ -168,7 +215,7 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
 #pragma unroll
             for (int k = 0; k < SPL; ++k) {
                 const int s = lane + k * L;
-                pid[k] = (live && s < P) ? sm_ids[grp * P + s] : TS_EMPTY_SLOT;
+                pid[k] = (live && s < P) ? stage.ids[cur][grp * P + s] : TS_EMPTY_SLOT;
                 used[k] = pid[k] != TS_EMPTY_SLOT;
                 raw_s[k] = make_double2(0.0, 1.0);
                 raw_q[k] = make_double2(0.0, 1.0);
@@ -236,9 +283,7 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
             if (!trunc_vw(d_q * rc_q, margin * rc_q, is_draw, a.prm.draw_is_zero != 0, v_q, w_q))
                 status = status ? status : TS_ST_FP_ERROR;
 
-            const uint32_t m = (live && (a.out.quality || a.out.out_shared || a.out.out_delta ||
-                                         a.out.out_queue || a.out.status))
-                                   ? __ldg(a.order + j) : 0u;
+            const uint32_t m = (live && want_order) ? stage.order[cur][grp] : 0u;
             if (live && lane == 0) {
                 if (a.out.status) a.out.status[m] = (uint8_t)status;
                 if (status != TS_ST_OK) atomicAdd(&a.ctrl[CTRL_ERRORS], 1ull);
@@ -274,8 +319,28 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
                 if (a.out.out_queue) st_pair(a.out.out_queue + o * 2, mu2, sg2);
             }
         }
-        if (r < n_rounds) grid_barrier(a.ctrl, generation, NoSerial());
+        if (r == n_rounds) break;
+        // run ahead of the barrier: bounds and first tile of the next round
+        lo = hi;
+        hi = hi_next;
+        if (r + 2 <= n_rounds) hi_next = __ldg(a.round_offsets + r + 3);
+        if (blockIdx.x < (hi - lo + G - 1) / G) stage_tile<P, G>(stage, pf, a, lo, hi, blockIdx.x, want_order);
+        grid_barrier(a.ctrl, generation);
     }
+}
+
+// Fewer resident blocks make the per-round grid barrier cheaper (fewer arrivals
+// on one L2 word); more blocks give more gathers in flight for fat rounds.
+// TSRATE_BLOCKS_PER_SM overrides the default for experiments.
+int rate_blocks_per_sm_cap()
+{
+    static int cap = -1;
+    if (cap < 0) {
+        const char *e = getenv("TSRATE_BLOCKS_PER_SM");
+        cap = e ? atoi(e) : 2;
+        if (cap < 1) cap = 1;
+    }
+    return cap;
 }
 
 template <int P, int L, bool SHARED>
@@ -284,9 +349,10 @@ int launch_rate(ts_ctx *ctx, const RateArgs &args, cudaStream_t stream)
     int per_sm = 0;
     TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rate<P, L, SHARED>, kBlock, 0));
     if (per_sm < 1) { ts_set_error("rate kernel does not fit on an SM"); return TS_E_CUDA; }
+    per_sm = min(per_sm, rate_blocks_per_sm_cap());
     dim3 grid(ctx->sm_count * per_sm), block(kBlock);
     void *kargs[] = {(void *)&args};
-    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl, 0, 2 * sizeof(unsigned long long), stream));
+    if (int rc = ts_reset_barrier(ctx->d_ctrl, stream)) return rc;
     TS_CUDA(cudaLaunchCooperativeKernel((void *)k_rate<P, L, SHARED>, grid, block, kargs, 0, stream));
     return 0;
 }

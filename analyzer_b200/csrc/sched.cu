@@ -20,6 +20,10 @@
 // player (rater.py:83-85,102-106): they create no edges and land in bucket 0.
 // All integer work; the result is bit-exact against the sequential schedule
 // oracle by construction (Kahn levels == longest-path levels).
+#include <stdlib.h>
+
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace {
@@ -119,18 +123,25 @@ __global__ void __launch_bounds__(256) k_radix_scan_totals(uint32_t *totals)
     totals[threadIdx.x] = s[threadIdx.x];
 }
 
-// stable scatter: warp w of a block owns WTILE consecutive elements and walks
-// them 32 at a time, so (step, lane) order is index order.
+// stable scatter: warp w of a block owns kSortItems*32 consecutive elements and
+// walks them 32 at a time, so (step, lane) order is index order.  The tile is
+// first put in digit order in shared memory, then written out with consecutive
+// threads on consecutive addresses of each digit's run.
 __global__ void __launch_bounds__(kSortBlock)
 k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n, int shift,
                 const uint32_t *hist, const uint32_t *totals, uint32_t n_blocks,
                 uint32_t *keys_out, uint32_t *vals_out)
 {
     __shared__ uint32_t wcount[kWarps][256];
+    __shared__ uint32_t gbase[256];       // global start of the digit's run for this block, minus its tile-local start
+    __shared__ uint32_t warp_tot[kWarps];
+    __shared__ uint32_t skey[kSortTile];
+    __shared__ uint32_t sval[kSortTile];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < kWarps * 256; i += kSortBlock) (&wcount[0][0])[i] = 0;
     __syncthreads();
-    const uint32_t wbase = blockIdx.x * kSortTile + warp * (kSortItems * 32);
+    const uint32_t tile_base = blockIdx.x * kSortTile;
+    const uint32_t wbase = tile_base + warp * (kSortItems * 32);
     uint32_t key[kSortItems], off[kSortItems];
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
@@ -151,15 +162,30 @@ k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n,
     }
     __syncthreads();
     {
-        // thread d: running start of digit d for each warp of this block
+        // thread d: per-warp starts inside digit d's run, then the run's tile-local start
         const uint32_t d = threadIdx.x;
-        uint32_t run = __ldg(totals + d) + __ldg(hist + (size_t)d * n_blocks + blockIdx.x);
+        uint32_t run = 0;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) {
             uint32_t c = wcount[w][d];
             wcount[w][d] = run;
             run += c;
         }
+        uint32_t incl = run;   // exclusive scan of the 256 digit totals across the block
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        uint32_t before = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) before += (w < warp) ? warp_tot[w] : 0u;
+        const uint32_t dstart = before + incl - run;
+        gbase[d] = __ldg(totals + d) + __ldg(hist + (size_t)d * n_blocks + blockIdx.x) - dstart;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) wcount[w][d] += dstart;
     }
     __syncthreads();
 #pragma unroll
@@ -167,43 +193,59 @@ k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n,
         uint32_t idx = wbase + k * 32 + lane;
         if (idx < n) {
             uint32_t pos = wcount[warp][(key[k] >> shift) & 255u] + off[k];
-            keys_out[pos] = key[k];
-            vals_out[pos] = ident_vals ? idx : __ldg(vals_in + idx);
+            skey[pos] = key[k];
+            sval[pos] = ident_vals ? idx : __ldg(vals_in + idx);
         }
+    }
+    __syncthreads();
+    const uint32_t cnt = min((uint32_t)kSortTile, n - tile_base);
+    for (uint32_t i = threadIdx.x; i < cnt; i += kSortBlock) {
+        uint32_t k = skey[i];
+        uint32_t pos = gbase[(k >> shift) & 255u] + i;
+        keys_out[pos] = k;
+        vals_out[pos] = sval[i];
     }
 }
 
 // ---- chain linking --------------------------------------------------------
 // Sorted pairs (key = player, val = slot index i = m*P + s).  Runs of equal key
 // list one player's slots in match order.  The first entry of a (player, match)
-// run is its primary: it counts one predecessor for its match if an earlier
-// match of the same player exists, and carries the link to the next one.
+// run is its primary: it records whether an earlier match of the same player
+// exists (bit 31) and carries the link to the player's next match (bits 0..30).
+constexpr uint32_t kLinkNone = 0x7FFFFFFFu;
+constexpr uint32_t kLinkHasPred = 0x80000000u;
+
 __global__ void __launch_bounds__(256)
-k_link(const uint32_t *keys, const uint32_t *vals, uint32_t n, uint32_t slots, uint32_t sentinel,
-       uint32_t *succ, uint32_t *pending)
+k_link(const uint32_t *keys, const uint32_t *vals, uint32_t n, uint32_t slots, uint32_t sentinel, uint32_t *succ)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     uint32_t k = keys[i], v = vals[i];
-    if (k >= sentinel) { succ[v] = TS_NONE; return; }
+    if (k >= sentinel) { succ[v] = kLinkNone; return; }
     uint32_t m = v / slots;
     bool has_prev = i > 0 && keys[i - 1] == k;
-    if (has_prev && vals[i - 1] / slots == m) { succ[v] = TS_NONE; return; }   // duplicate of a player inside one match
-    if (has_prev) atomicAdd(&pending[m], 1u);
-    uint32_t nx = TS_NONE;
+    if (has_prev && vals[i - 1] / slots == m) { succ[v] = kLinkNone; return; }   // duplicate of a player inside one match
+    uint32_t nx = kLinkNone;
     for (uint32_t j = i + 1; j < n && keys[j] == k; ++j) {
         uint32_t mj = vals[j] / slots;
         if (mj != m) { nx = mj; break; }
     }
-    succ[v] = nx;
+    succ[v] = nx | (has_prev ? kLinkHasPred : 0u);
 }
 
+// pending[m] = number of slots with a predecessor; matches with none start the sweep
 __global__ void __launch_bounds__(256)
-k_init_frontier(const uint32_t *meta, ModeCols modes, const uint32_t *pending, uint32_t n,
-                uint32_t *queue, unsigned long long *ctrl)
+k_init_frontier(const uint32_t *meta, ModeCols modes, const uint32_t *succ, uint32_t slots, uint32_t n,
+                uint32_t *pending, uint32_t *queue, unsigned long long *ctrl)
 {
     uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
-    bool ready = m < n && !meta_is_gated(__ldg(meta + m), modes.col) && pending[m] == 0u;
+    bool ready = false;
+    if (m < n) {
+        uint32_t cnt = 0;
+        for (uint32_t s = 0; s < slots; ++s) cnt += succ[(size_t)m * slots + s] >> 31;
+        pending[m] = cnt;
+        ready = cnt == 0u && !meta_is_gated(__ldg(meta + m), modes.col);
+    }
     // warp-aggregated append
     uint32_t mask = __ballot_sync(0xFFFFFFFFu, ready);
     if (mask == 0u) return;
@@ -214,40 +256,73 @@ k_init_frontier(const uint32_t *meta, ModeCols modes, const uint32_t *pending, u
     if (ready) queue[base + __popc(mask & ((1u << lane) - 1u))] = m;
 }
 
-// Level-synchronous frontier sweep.  queue holds level after level back to back;
-// the block that arrives last at the barrier snapshots the tail, which closes
-// the next level before anyone starts appending to the one after it.
+// Level-synchronous frontier sweep.  queue holds level after level back to back.
+// Level L+1's entries are claimed through a per-level word whose low half counts
+// the appended matches and whose high half counts the blocks that have finished
+// level L; a block polls that one word until the whole grid has arrived and
+// reads the size of the next level from the same load.  Three words rotate.
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 __global__ void __launch_bounds__(256)
 k_frontier(uint32_t *queue, const uint32_t *succ, uint32_t *pending, uint32_t *round, uint32_t slots,
            uint32_t n_matches, uint32_t *level_sizes, uint32_t offsets_cap, ts_sched_info *info,
            unsigned long long *ctrl)
 {
-    unsigned long long generation = 0;
+    __shared__ uint32_t s_cnt;
     uint32_t start = 0;
-    // every block must see the same first `end`: the host copied the tail into
-    // the snapshot word before launch, and it is rewritten only at a barrier
+    // the host copied the tail after k_init_frontier into the snapshot word
     uint32_t end = (uint32_t)ld_acquire_u64(&ctrl[CTRL_TAIL + 1]);
     uint32_t level = 1;
+    const int lane = threadIdx.x & 31;
     while (start < end) {
+        unsigned long long *word = &ctrl[CTRL_LEVEL + level % 3];      // collects level + 1
         const uint32_t work = (end - start) * slots;
-        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < work; i += gridDim.x * blockDim.x) {
-            uint32_t m = __ldcg(queue + start + i / slots);
-            uint32_t s = i % slots;
-            if (s == 0) round[m] = level;
-            uint32_t nx = __ldg(succ + (size_t)m * slots + s);
-            if (nx != TS_NONE && atomicSub(&pending[nx], 1u) == 1u)
-                queue[atomicAdd(&ctrl[CTRL_TAIL], 1ull)] = nx;
+        const uint32_t stride = gridDim.x * blockDim.x;
+        // whole warps iterate together so the appends can be warp-aggregated
+        for (uint32_t i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < work; i0 += stride) {
+            const uint32_t i = i0 + lane;
+            bool push = false;
+            uint32_t nx = kLinkNone;
+            if (i < work) {
+                uint32_t m = __ldcg(queue + start + i / slots);
+                uint32_t s = i % slots;
+                if (s == 0) round[m] = level;
+                nx = __ldg(succ + (size_t)m * slots + s) & kLinkNone;
+                push = nx != kLinkNone && atomicSub(&pending[nx], 1u) == 1u;
+            }
+            uint32_t mask = __ballot_sync(0xFFFFFFFFu, push);
+            if (mask) {
+                int leader = __ffs(mask) - 1;
+                unsigned long long base = 0;
+                if (lane == leader) base = atomicAdd(word, (unsigned long long)__popc(mask));
+                base = __shfl_sync(0xFFFFFFFFu, base, leader);
+                if (push) {
+                    queue[end + (uint32_t)base + __popc(mask & ((1u << lane) - 1u))] = nx;
+                    // next level reads this match's links right after the barrier
+                    prefetch_l2(succ + (size_t)nx * slots);
+                    prefetch_l2(succ + (size_t)nx * slots + slots - 1);
+                }
+            }
         }
-        const uint32_t lvl = level, cnt = end - start;
-        grid_barrier(ctrl, generation, [&]() {
-            if (lvl + 2 <= offsets_cap) level_sizes[lvl] = cnt;   // bucket lvl
-            ctrl[CTRL_TAIL + 1] = ld_acquire_u64(&ctrl[CTRL_TAIL]);
-        });
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            __threadfence();
+            red_add_u64(word, 1ull << 32);
+            unsigned long long w;
+            while (((w = ld_relaxed_u64(word)) >> 32) < gridDim.x) {
+            }
+            __threadfence();
+            s_cnt = (uint32_t)w;
+            if (blockIdx.x == 0) {
+                if (level + 2 <= offsets_cap) level_sizes[level] = end - start;
+                // the word of two levels ago is idle: everyone polled it before arriving here
+                ctrl[CTRL_LEVEL + (level + 2) % 3] = 0ull;
+            }
+        }
+        __syncthreads();
         start = end;
-        end = (uint32_t)ld_acquire_u64(&ctrl[CTRL_TAIL + 1]);
+        end = start + s_cnt;
         level += 1;
-        // the snapshot word is rewritten only after every block has passed the
-        // NEXT barrier's arrive, i.e. after it has read this value
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         info->n_rounds = level - 1;
@@ -340,6 +415,17 @@ Workspace carve(char *base, int64_t n_matches, int32_t slots)
     return w;
 }
 
+int frontier_blocks_per_sm_cap()
+{
+    static int cap = -1;
+    if (cap < 0) {
+        const char *e = getenv("TSRATE_FRONTIER_BLOCKS_PER_SM");
+        cap = e ? atoi(e) : 2;
+        if (cap < 1) cap = 1;
+    }
+    return cap;
+}
+
 int bits_for(uint64_t max_value)
 {
     int b = 1;
@@ -400,6 +486,10 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
         ts_set_error("ts_schedule: n_matches * slots must stay below 2^32 - 2^16: schedule the ladder in windows");
         return TS_E_ARG;
     }
+    if (n_matches >= 0x7FFFFFFFll) {
+        ts_set_error("ts_schedule: n_matches must stay below 2^31 - 1");
+        return TS_E_ARG;
+    }
     if (n_players < 1 || n_players >= 0xFFFFFFFFll) {
         ts_set_error("ts_schedule: n_players outside [1, 2^32 - 1)");
         return TS_E_ARG;
@@ -441,14 +531,14 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     if (buf < 0) return buf;
 
     // 2. link chains
-    TS_CUDA(cudaMemsetAsync(w.pending, 0, (size_t)n * 4, s));
     TS_CUDA(cudaMemsetAsync(round, 0, (size_t)n * 4, s));
     // barrier words and queue tail/snapshot; the error counter (word 2) is left alone
-    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl, 0, 2 * sizeof(unsigned long long), s));
-    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_TAIL, 0, 2 * sizeof(unsigned long long), s));
+    if (int rc = ts_reset_barrier(ctx->d_ctrl, s)) return rc;
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_TAIL, 0, (CTRL_WORDS - CTRL_TAIL) * sizeof(unsigned long long), s));
     k_link<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, (uint32_t)slots, (uint32_t)n_players,
-                                            w.succ, w.pending);
-    k_init_frontier<<<(n + 255) / 256, 256, 0, s>>>(meta, modes, w.pending, n, w.queue, ctx->d_ctrl);
+                                            w.succ);
+    k_init_frontier<<<(n + 255) / 256, 256, 0, s>>>(meta, modes, w.succ, (uint32_t)slots, n, w.pending, w.queue,
+                                                    ctx->d_ctrl);
     // close level 1: the sweep reads its first `end` from the snapshot word
     TS_CUDA(cudaMemcpyAsync(ctx->d_ctrl + CTRL_TAIL + 1, ctx->d_ctrl + CTRL_TAIL, sizeof(unsigned long long),
                             cudaMemcpyDeviceToDevice, s));
@@ -458,7 +548,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
         int per_sm = 0;
         TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_frontier, 256, 0));
         if (per_sm < 1) { ts_set_error("frontier kernel does not fit"); return TS_E_CUDA; }
-        if (per_sm > 4) per_sm = 4;
+        per_sm = std::min(per_sm, frontier_blocks_per_sm_cap());
         dim3 grid(ctx->sm_count * per_sm), block(256);
         uint32_t slots_u = (uint32_t)slots;
         unsigned long long *ctrl = ctx->d_ctrl;

@@ -34,7 +34,7 @@
 // ---------------------------------------------------------------------------
 namespace {
 
-constexpr size_t kStaticCtrlBytes = 256;   // CTRL_WORDS * 8 = 128, padded to the alignment
+constexpr size_t kStaticCtrlBytes = (TS_CTRL_BYTES + 255) & ~(size_t)255;   // control words first, then the workspace
 constexpr size_t kStaticScratchBytes = 2u << 20;
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
