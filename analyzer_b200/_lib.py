@@ -10,7 +10,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libtsrate.so")
-SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "static_sched.cu"]
+SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "static_sched.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-shared", "-Xcompiler", "-fPIC"]
 
@@ -24,7 +24,8 @@ ST_OK, ST_SKIP_MODE, ST_AFK, ST_INVALID, ST_FP_ERROR, ST_VALUE_ERROR = range(6)
 EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_workspace_bytes", "ts_schedule", "ts_rate", "ts_error_count",
            "ts_reset_errors", "ts_gen_matches", "ts_gen_table",
-           "ts_schedule_static", "ts_schedule_static_max_slot_entries"]
+           "ts_schedule_static", "ts_schedule_static_max_slot_entries",
+           "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream"]
 
 
 class TsParams(C.Structure):
@@ -106,6 +107,15 @@ def lib():
         L.ts_rate.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.POINTER(TsOutputs),
                               C.c_int32, C.c_void_p]
+        L.ts_link_workspace_bytes.restype = C.c_int64
+        L.ts_link_workspace_bytes.argtypes = [C.c_int64, C.c_int32]
+        L.ts_link_pred.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
+                                   C.POINTER(C.c_int8), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        L.ts_rate_stream_workspace_bytes.restype = C.c_int64
+        L.ts_rate_stream_workspace_bytes.argtypes = [C.c_int64]
+        L.ts_rate_stream.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p,
+                                     C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32, C.c_void_p,
+                                     C.c_int64, C.c_void_p]
         L.ts_gen_matches.argtypes = [C.POINTER(TsGen), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                      C.c_void_p]
         L.ts_gen_table.argtypes = [C.c_uint64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]

@@ -42,13 +42,14 @@ struct KeySrc {
     uint32_t slots;
     uint32_t sentinel;
     int from_ids;
+    unsigned long long slots_magic;   // floor(2^40 / slots) + 1: idx / slots == (idx * magic) >> 40 for idx < 2^32
 };
 
 __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
 {
     uint32_t k = __ldg(src.keys + idx);
     if (src.from_ids) {
-        uint32_t m = __ldg(src.meta + idx / src.slots);
+        uint32_t m = __ldg(src.meta + (uint32_t)(((unsigned long long)idx * src.slots_magic) >> 40));
         if (k == TS_EMPTY_SLOT || meta_is_gated(m, src.modes.col)) k = src.sentinel;
     }
     return k;
@@ -127,7 +128,7 @@ __global__ void __launch_bounds__(256) k_radix_scan_totals(uint32_t *totals)
 // walks them 32 at a time, so (step, lane) order is index order.  The tile is
 // first put in digit order in shared memory, then written out with consecutive
 // threads on consecutive addresses of each digit's run.
-__global__ void __launch_bounds__(kSortBlock)
+__global__ void __launch_bounds__(kSortBlock, 4)
 k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n, int shift,
                 const uint32_t *hist, const uint32_t *totals, uint32_t n_blocks,
                 uint32_t *keys_out, uint32_t *vals_out)
@@ -143,22 +144,26 @@ k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n,
     const uint32_t tile_base = blockIdx.x * kSortTile;
     const uint32_t wbase = tile_base + warp * (kSortItems * 32);
     uint32_t key[kSortItems], off[kSortItems];
+    // all loads first (16 independent requests per thread in flight) ...
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        uint32_t idx = wbase + k * 32 + lane;
+        key[k] = idx < n ? load_key(src, idx) : 0u;
+    }
+    // ... then the ranks: lanes with equal digits find each other with match.any;
+    // the lowest such lane bumps the warp's counter of that digit with a shared-
+    // memory atomic (same-address atomics of one warp retire in program order, so
+    // later steps rank behind earlier ones: stable)
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
         bool ok = idx < n;
-        key[k] = ok ? load_key(src, idx) : 0u;
         uint32_t d = ok ? ((key[k] >> shift) & 255u) : 256u;   // 256 = padding, matches only padding
         uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
-        uint32_t rank = __popc(peers & ((1u << lane) - 1u));
         int leader = __ffs(peers) - 1;
         uint32_t prev = 0;
-        if (ok && lane == leader) {
-            prev = wcount[warp][d];
-            wcount[warp][d] = prev + __popc(peers);
-        }
-        prev = __shfl_sync(0xFFFFFFFFu, prev, leader);
-        off[k] = prev + rank;
+        if (ok && lane == leader) prev = atomicAdd(&wcount[warp][d], (uint32_t)__popc(peers));
+        off[k] = __shfl_sync(0xFFFFFFFFu, prev, leader) + __popc(peers & ((1u << lane) - 1u));
     }
     __syncthreads();
     {
@@ -385,6 +390,37 @@ k_permute(const uint32_t *ids, const uint32_t *meta, const uint32_t *order, uint
     if (s == 0) meta_sorted[j] = __ldg(meta + m);
 }
 
+// Predecessor links for the streaming (dataflow) rating kernel: pred[v] = index of
+// the previous rated match of the player in slot v, or TS_NONE.  The scatter by
+// slot index is random; it is done in passes over destination ranges small
+// enough to stay in L2, so every 32-byte sector of pred is written back to HBM
+// once, complete, instead of being read-modified-written eight times.
+__global__ void __launch_bounds__(256)
+k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long long slots_magic, uint32_t sentinel,
+       uint32_t v_lo, uint32_t v_hi, uint32_t *pred)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    // all four loads are issued up front (coalesced; the i-1 ones hit L1): one
+    // memory latency per thread instead of a chain of three
+    const uint32_t v = __ldcs(vals + i), k = __ldcs(keys + i);
+    const uint32_t kp = i > 0 ? __ldcs(keys + i - 1) : ~k, vp = i > 0 ? __ldcs(vals + i - 1) : 0u;
+    if (v < v_lo || v >= v_hi || k >= sentinel) return;   // other pass / empty slot / gated match
+    const uint32_t m = (uint32_t)(((unsigned long long)v * slots_magic) >> 40);
+    uint32_t pm = TS_NONE;
+    if (kp == k) {
+        pm = (uint32_t)(((unsigned long long)vp * slots_magic) >> 40);
+        if (pm == m) {          // the player is listed twice in this match: walk back to a different match
+            pm = TS_NONE;
+            for (uint32_t j = i - 1; j > 0 && __ldcs(keys + j - 1) == k; --j) {
+                uint32_t mj = (uint32_t)(((unsigned long long)__ldcs(vals + j - 1) * slots_magic) >> 40);
+                if (mj != m) { pm = mj; break; }
+            }
+        }
+    }
+    pred[v] = pm;
+}
+
 struct Workspace {
     uint32_t *keys[2];
     uint32_t *vals[2];
@@ -527,6 +563,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     src.slots = (uint32_t)slots;
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
+    src.slots_magic = ((1ull << 40) / (unsigned long long)slots) + 1ull;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s);
     if (buf < 0) return buf;
 
@@ -575,6 +612,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     rsrc.slots = 1;
     rsrc.sentinel = 0;
     rsrc.from_ids = 0;
+    rsrc.slots_magic = (1ull << 40) + 1ull;
     buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s);
     if (buf < 0) return buf;
     TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
@@ -585,5 +623,67 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     }
     TS_CUDA(cudaGetLastError());
     if (n_rounds_host) *n_rounds_host = h.n_rounds;
+    return 0;
+}
+
+
+extern "C" int64_t ts_link_workspace_bytes(int64_t n_matches, int32_t slots)
+{
+    if (n_matches < 0 || slots < 2 || slots > TS_MAX_SLOTS) return TS_E_ARG;
+    size_t np = (size_t)n_matches * slots;
+    size_t n_blocks = (np + kSortTile - 1) / kSortTile;
+    return (int64_t)(4 * align_up(np * 4) + align_up((n_blocks * 256 + 256) * 4) + align_up(256 * 4));
+}
+
+extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
+                            int64_t n_players, const int8_t mode_col[16], uint32_t *pred, void *workspace,
+                            int64_t workspace_bytes, void *stream)
+{
+    if (!ctx || !mode_col || (n_matches > 0 && (!ids || !meta || !pred || !workspace))) {
+        ts_set_error("ts_link_pred: null argument");
+        return TS_E_ARG;
+    }
+    if (slots < 2 || slots > TS_MAX_SLOTS || (slots & 1) || n_matches < 0 ||
+        (uint64_t)n_matches * (uint64_t)slots >= 0xFFFF0000ull || n_players < 1 || n_players >= 0xFFFFFFFFll) {
+        ts_set_error("ts_link_pred: bad sizes (n_matches * slots must stay below 2^32 - 2^16)");
+        return TS_E_ARG;
+    }
+    if (n_matches == 0) return 0;
+    if (workspace_bytes < ts_link_workspace_bytes(n_matches, slots)) {
+        ts_set_error("ts_link_pred: workspace too small");
+        return TS_E_WORKSPACE;
+    }
+    TS_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t np = (uint32_t)n_matches * (uint32_t)slots;
+    Workspace w;
+    {
+        char *base = (char *)workspace;
+        size_t off = 0, n_blocks = ((size_t)np + kSortTile - 1) / kSortTile;
+        auto take = [&](size_t bytes) { char *p = base + off; off += align_up(bytes); return (uint32_t *)p; };
+        for (int i = 0; i < 2; ++i) { w.keys[i] = take((size_t)np * 4); w.vals[i] = take((size_t)np * 4); }
+        w.hist = take((n_blocks * 256 + 256) * 4);
+        w.totals = take(256 * 4);
+        w.succ = w.pending = w.queue = nullptr;
+        w.bytes = off;
+    }
+    KeySrc src;
+    src.keys = ids;
+    src.meta = meta;
+    for (int i = 0; i < 16; ++i) src.modes.col[i] = i < 6 ? mode_col[i] : (int8_t)-1;
+    src.slots = (uint32_t)slots;
+    src.sentinel = (uint32_t)n_players;
+    src.from_ids = 1;
+    src.slots_magic = ((1ull << 40) / (unsigned long long)slots) + 1ull;
+    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s);
+    if (buf < 0) return buf;
+    // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2
+    const uint32_t range = 16u << 20;
+    for (uint64_t lo = 0; lo < np; lo += range) {
+        uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);
+        k_pred<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, src.slots_magic, (uint32_t)n_players,
+                                                (uint32_t)lo, hi, pred);
+    }
+    TS_CUDA(cudaGetLastError());
     return 0;
 }

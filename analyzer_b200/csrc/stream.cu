@@ -1,0 +1,418 @@
+// Streaming (dataflow) form of the fp64 rating kernel for sm_100a.
+//
+// Same arithmetic and same result as ts_rate, but no rounds and no grid
+// barriers: matches are rated in stream order (worker.py:192's order, which is
+// a topological order of the dependency graph), and a match simply waits until
+// the rows of its players carry the version it expects -- the index of that
+// player's previous match, from ts_link_pred -- before it reads them.  On B200
+// a coherent L2 round trip costs ~0.6 us, so a barrier per round puts several
+// of them on the critical path of each of the R rounds (R = 888 for 10M
+// matches over 1M players); here the only chained latency is one poll per hop
+// of the longest dependency chain.
+//
+// Row format (workspace, 32 bytes = one sector per player): four 64-bit words
+//   [mu.lo | ver<<32] [mu.hi | ver<<32] [sigma.lo | ver<<32] [sigma.hi | ver<<32]
+// Every 8-byte word validates itself (64-bit accesses are single-copy atomic),
+// so neither writer nor reader needs a fence: a reader accepts a row when all
+// four version fields equal the version it waits for.  Same idea as the
+// low-latency flag protocols of collective libraries.
+//
+// Progress: blocks take tiles of consecutive matches round-robin in increasing
+// order and the grid is co-resident (cooperative launch), so the oldest
+// unfinished match never waits on unstarted work.  Inside a warp the wait loop
+// is warp-uniform and ready groups finish whole matches inside an iteration, so
+// a match may depend on another match of the same warp.
+//
+// Single-pair ladders only (table.row_pairs == 1, shared_col == -1): the
+// faithful shared + queue layout keeps using ts_rate.
+#include <stdlib.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int kBlock = 256;
+
+struct StreamArgs {
+    ts_params prm;
+    unsigned long long *vt;       // versioned rows, 4 words per player
+    const double *seed;
+    ModeCols modes;
+    const uint32_t *ids;
+    const uint32_t *meta;
+    const uint32_t *pred;
+    uint32_t n_matches;
+    ts_outputs out;
+    unsigned long long *ctrl;
+};
+
+__device__ __forceinline__ void ld_row(const unsigned long long *row, unsigned long long (&w)[4])
+{
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(row) : "memory");
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(row + 2) : "memory");
+}
+__device__ __forceinline__ void st_row(unsigned long long *row, double mu, double sigma, uint32_t ver)
+{
+    const unsigned long long v = (unsigned long long)ver << 32;
+    const unsigned long long m = (unsigned long long)__double_as_longlong(mu);
+    const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
+    unsigned long long w0 = (m & 0xFFFFFFFFull) | v, w1 = (m >> 32) | v;
+    unsigned long long w2 = (s & 0xFFFFFFFFull) | v, w3 = (s >> 32) | v;
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"(w0), "l"(w1) : "memory");
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"(w2), "l"(w3) : "memory");
+}
+__device__ __forceinline__ bool row_has_version(const unsigned long long (&w)[4], uint32_t ver)
+{
+    return (uint32_t)(w[0] >> 32) == ver && (uint32_t)(w[1] >> 32) == ver && (uint32_t)(w[2] >> 32) == ver &&
+           (uint32_t)(w[3] >> 32) == ver;
+}
+__device__ __forceinline__ double row_mu(const unsigned long long (&w)[4])
+{
+    return __longlong_as_double((long long)((w[0] & 0xFFFFFFFFull) | (w[1] << 32)));
+}
+__device__ __forceinline__ double row_sigma(const unsigned long long (&w)[4])
+{
+    return __longlong_as_double((long long)((w[2] & 0xFFFFFFFFull) | (w[3] << 32)));
+}
+
+constexpr double kInvSqrt2 = 0.70710678118654752440;
+constexpr double kSqrt2OverPi = 0.79788456080286535588;
+constexpr double kInvSqrt2Pi = 0.39894228040143267794;
+__device__ __forceinline__ double npdf(double x) { return kInvSqrt2Pi * exp(-0.5 * x * x); }
+__device__ __forceinline__ double ncdf(double x) { return 0.5 * erfc(-x * kInvSqrt2); }
+
+// identical to rate.cu's trunc_vw (kept textually in step with it)
+__device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, bool draw_is_zero, double &v, double &w)
+{
+    if (!is_draw) {
+        double x = t - eps;
+        double e = erfcx(-x * kInvSqrt2);
+        v = kSqrt2OverPi / e;
+        w = v * (v + x);
+        if (w > 0.0 && w < 1.0) return true;
+        if (x > 30.0 && w >= 0.0) { v = 0.0; w = 0.0; return true; }
+        return false;
+    }
+    if (draw_is_zero) { v = -t; w = 1.0; return true; }
+    double at = fabs(t);
+    double a = eps - at, b = -eps - at;
+    double mass = ncdf(a) - ncdf(b);
+    if (mass == 0.0) return false;
+    double pa = npdf(a), pb = npdf(b);
+    double vv = (pb - pa) / mass;
+    w = vv * vv + (a * pa - b * pb) / mass;
+    v = t < 0.0 ? -vv : vv;
+    return true;
+}
+
+__device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)
+{
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_4(void *smem, const void *gmem)
+{
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// per-warp staging buffers: a warp owns W = 32 / L consecutive matches at a time
+template <int P, int W>
+struct WarpStage {
+    uint32_t ids[2][W * P];
+    uint32_t pred[2][W * P];
+    uint32_t meta[2][W];
+};
+
+template <int P, int W>
+__device__ __forceinline__ void stage_warp_tile(WarpStage<P, W> &st, int b, const StreamArgs &a, uint32_t tile, int wl)
+{
+    const uint32_t base = tile * W;
+    const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
+    const uint32_t *src_i = a.ids + (size_t)base * P, *src_p = a.pred + (size_t)base * P;
+    for (uint32_t i = wl; i < cnt * (P / 2); i += 32) {
+        cp_async_8(&st.ids[b][2 * i], src_i + 2 * i);
+        cp_async_8(&st.pred[b][2 * i], src_p + 2 * i);
+    }
+    for (uint32_t i = wl; i < cnt; i += 32) cp_async_4(&st.meta[b][i], a.meta + base + i);
+}
+
+template <int L>
+__device__ __forceinline__ double group_sum(double x, uint32_t gmask)
+{
+#pragma unroll
+    for (int o = L / 2; o > 0; o >>= 1) x += __shfl_xor_sync(gmask, x, o, L);
+    return x;
+}
+template <int L>
+__device__ __forceinline__ uint32_t group_sum_u32(uint32_t x, uint32_t gmask)
+{
+#pragma unroll
+    for (int o = L / 2; o > 0; o >>= 1) x += __shfl_xor_sync(gmask, x, o, L);
+    return x;
+}
+
+// Warps are the unit of work: warp w of the grid takes the tiles w, w + n_warps,
+// ... of W consecutive matches, in increasing order, and never synchronises
+// with the other warps of its block -- a warp that has to wait for a dependency
+// holds up nothing but its own W matches.
+template <int P, int L>
+__global__ void __launch_bounds__(kBlock) k_rate_stream(const StreamArgs a)
+{
+    constexpr int W = 32 / L;
+    constexpr int SPL = (P + L - 1) / L;
+    constexpr int HALF = P / 2;
+    constexpr int kWarps = kBlock / 32;
+    __shared__ __align__(16) WarpStage<P, W> stage_all[kWarps];
+
+    const int wl = threadIdx.x & 31;            // lane in warp
+    const int lane = wl % L;                    // lane in match group
+    const int grp = wl / L;                     // match of the warp tile
+    WarpStage<P, W> &stage = stage_all[threadIdx.x >> 5];
+    const uint32_t gmask = L == 32 ? 0xFFFFFFFFu : (((1u << L) - 1u) << (grp * L));
+    const double tau2 = a.prm.tau * a.prm.tau;
+    const double beta2 = a.prm.beta * a.prm.beta;
+    const double tb2 = tau2 + beta2;
+    const uint32_t n_tiles = (a.n_matches + W - 1) / W;
+    const uint32_t n_warps = gridDim.x * kWarps;
+    const uint32_t warp_id = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;   // neighbouring tiles on different SMs
+
+    int pf = 0;
+    if (warp_id < n_tiles) stage_warp_tile<P, W>(stage, pf, a, warp_id, wl);
+    for (uint32_t tile = warp_id; tile < n_tiles; tile += n_warps) {
+        cp_async_wait_all();
+        __syncwarp();
+        const int cur = pf;
+        pf ^= 1;
+        if (tile + n_warps < n_tiles) stage_warp_tile<P, W>(stage, pf, a, tile + n_warps, wl);
+        const uint32_t base = tile * W;
+        const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
+        const uint32_t m = base + grp;
+        const uint32_t meta = (uint32_t)grp < cnt ? stage.meta[cur][grp] : (15u << TS_META_MODE_SHIFT);
+        const uint32_t mode = (meta >> TS_META_MODE_SHIFT) & 15u;
+        const bool skip_mode = mode >= 6u || a.modes.col[mode & 7u] < 0;
+        const bool gated = skip_mode || (meta & (TS_META_AFK | TS_META_INVALID)) != 0u;
+        const bool live = (uint32_t)grp < cnt && !gated;
+        if ((uint32_t)grp < cnt && gated && lane == 0) {     // rater.py:83-85,102-106: outputs only
+            if (a.out.status) a.out.status[m] = skip_mode ? TS_ST_SKIP_MODE : ((meta & TS_META_INVALID) ? TS_ST_INVALID : TS_ST_AFK);
+            if (!skip_mode && a.out.quality) a.out.quality[m] = 0.0;
+        }
+        const int rank0 = (meta & TS_META_WIN_A) ? 0 : 1, rank1 = (meta & TS_META_WIN_B) ? 0 : 1;
+        const int first = rank1 < rank0 ? 1 : 0;
+        const bool is_draw = rank0 == rank1;
+
+        uint32_t pid[SPL], want[SPL];
+        bool used[SPL], have[SPL];
+        double q_mu[SPL], q_sg[SPL];
+#pragma unroll
+        for (int k = 0; k < SPL; ++k) {
+            const int s = lane + k * L;
+            pid[k] = (live && s < P) ? stage.ids[cur][grp * P + s] : TS_EMPTY_SLOT;
+            used[k] = pid[k] != TS_EMPTY_SLOT;
+            want[k] = used[k] ? stage.pred[cur][grp * P + s] : TS_NONE;
+            have[k] = !used[k];
+            q_mu[k] = 0.0; q_sg[k] = 1.0;
+        }
+        bool done = !live;
+        // warp-uniform wait loop: a group that finds all its rows at the expected
+        // version rates its match inside the iteration
+        while (!__all_sync(0xFFFFFFFFu, done)) {
+            if (!done) {
+                bool ready = true;
+                unsigned long long w[SPL][4];
+#pragma unroll
+                for (int k = 0; k < SPL; ++k)
+                    if (!have[k]) ld_row(a.vt + (size_t)pid[k] * 4, w[k]);
+#pragma unroll
+                for (int k = 0; k < SPL; ++k) {
+                    if (!have[k] && row_has_version(w[k], want[k])) {
+                        have[k] = true;
+                        q_mu[k] = row_mu(w[k]);
+                        q_sg[k] = row_sigma(w[k]);
+                    }
+                    ready &= have[k];
+                }
+                if (__all_sync(gmask, ready)) {
+                    double sgn[SPL], r_mu[SPL], r_sg[SPL];
+                    double d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
+                    uint32_t cnts = 0;
+#pragma unroll
+                    for (int k = 0; k < SPL; ++k) {
+                        const int s = lane + k * L;
+                        sgn[k] = ((s >= HALF ? 1 : 0) == first) ? 1.0 : -1.0;
+                        r_mu[k] = q_mu[k]; r_sg[k] = q_sg[k];      // the row as read (kept for a failed match)
+                        if (!used[k]) continue;
+                        bool bad = false;
+                        if (isnan(q_mu[k])) {            // first touch: seed (rater.py:118-119)
+                            double2 sd = make_double2(q_mu[k], q_sg[k]);
+                            if (a.seed) sd = __ldg(reinterpret_cast<const double2 *>(a.seed) + pid[k]);
+                            bad |= isnan(sd.x);
+                            if (!bad) { q_mu[k] = sd.x; q_sg[k] = sd.y; }
+                        }
+                        bad |= q_sg[k] == 0.0;
+                        d_q = fma(sgn[k], q_mu[k], d_q);
+                        c2_q += fma(q_sg[k], q_sg[k], tb2);
+                        ss_q = fma(q_sg[k], q_sg[k], ss_q);
+                        cnts += (sgn[k] > 0.0 ? 1u : 256u) + (bad ? 65536u : 0u);
+                    }
+                    if (L > 1) {
+                        d_q = group_sum<L>(d_q, gmask);
+                        c2_q = group_sum<L>(c2_q, gmask);
+                        ss_q = group_sum<L>(ss_q, gmask);
+                        cnts = group_sum_u32<L>(cnts, gmask);
+                    }
+                    const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
+                    int status = TS_ST_OK;
+                    if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
+                    const double margin = a.prm.draw_margin[n];
+                    double v_q = 0.0, w_q = 0.0;
+                    const double rc_q = rsqrt(c2_q);
+                    if (status == TS_ST_OK &&
+                        !trunc_vw(d_q * rc_q, margin * rc_q, is_draw, a.prm.draw_is_zero != 0, v_q, w_q))
+                        status = TS_ST_FP_ERROR;
+#pragma unroll
+                    for (int k = 0; k < SPL; ++k) {
+                        if (!used[k]) continue;
+                        const int s = lane + k * L;
+                        // a failed match writes nothing in the reference; here it republishes the
+                        // row it read under its own version so that successors can go on
+                        double mu2 = r_mu[k], sg2 = r_sg[k];
+                        if (status == TS_ST_OK) {
+                            const double si = fma(q_sg[k], q_sg[k], tau2);
+                            const double g = si * rc_q;
+                            mu2 = fma(sgn[k] * g, v_q, q_mu[k]);
+                            sg2 = sqrt(si * (1.0 - (g * rc_q) * w_q));
+                        }
+                        st_row(a.vt + (size_t)pid[k] * 4, mu2, sg2, m);      // first: successors are waiting
+                        if (status == TS_ST_OK && a.out.out_queue)
+                            __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + (size_t)m * P + s, make_double2(mu2, sg2));
+                    }
+                    if (lane == 0) {
+                        if (a.out.status) a.out.status[m] = (uint8_t)status;
+                        if (status != TS_ST_OK) atomicAdd(&a.ctrl[CTRL_ERRORS], 1ull);
+                        else if (a.out.quality) {
+                            const double nb2 = (double)n * beta2;
+                            const double den = nb2 + ss_q;
+                            a.out.quality[m] = exp(-0.5 * d_q * d_q / den) * sqrt(nb2 / den);
+                        }
+                    }
+                    done = true;
+                } else {
+                    __nanosleep(20);
+                }
+            }
+        }
+    }
+}
+
+// user table (mu, sigma) <-> versioned rows
+__global__ void __launch_bounds__(256) k_vt_load(const double *table, unsigned long long *vt, int64_t n)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double2 r = reinterpret_cast<const double2 *>(table)[i];
+    st_row(vt + i * 4, r.x, r.y, TS_NONE);
+}
+__global__ void __launch_bounds__(256) k_vt_store(const unsigned long long *vt, double *table, int64_t n)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned long long w[4];
+    ld_row(vt + i * 4, w);
+    reinterpret_cast<double2 *>(table)[i] = make_double2(row_mu(w), row_sigma(w));
+}
+
+int stream_blocks_per_sm_cap()
+{
+    static int cap = -1;
+    if (cap < 0) {
+        const char *e = getenv("TSRATE_STREAM_BLOCKS_PER_SM");
+        cap = e ? atoi(e) : 4;
+        if (cap < 1) cap = 1;
+    }
+    return cap;
+}
+
+template <int P, int L>
+int launch_stream(ts_ctx *ctx, const StreamArgs &args, cudaStream_t stream)
+{
+    int per_sm = 0;
+    TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rate_stream<P, L>, kBlock, 0));
+    if (per_sm < 1) { ts_set_error("stream kernel does not fit on an SM"); return TS_E_CUDA; }
+    per_sm = per_sm < stream_blocks_per_sm_cap() ? per_sm : stream_blocks_per_sm_cap();
+    dim3 grid(ctx->sm_count * per_sm), block(kBlock);
+    void *kargs[] = {(void *)&args};
+    // cooperative launch only for its guarantee that the whole grid is resident
+    TS_CUDA(cudaLaunchCooperativeKernel((void *)k_rate_stream<P, L>, grid, block, kargs, 0, stream));
+    return 0;
+}
+
+template <int P>
+int dispatch_l(ts_ctx *ctx, const StreamArgs &a, int lanes, cudaStream_t s)
+{
+    switch (lanes) {
+    case 1: return launch_stream<P, 1>(ctx, a, s);
+    case 2: return launch_stream<P, 2>(ctx, a, s);
+    case 4: return launch_stream<P, 4>(ctx, a, s);
+    case 8: return launch_stream<P, 8>(ctx, a, s);
+    case 16: return launch_stream<P, 16>(ctx, a, s);
+    case 32: return launch_stream<P, 32>(ctx, a, s);
+    }
+    ts_set_error("lanes_per_match must be 0,1,2,4,8,16 or 32 (got %d)", lanes);
+    return TS_E_ARG;
+}
+
+}  // namespace
+
+extern "C" int64_t ts_rate_stream_workspace_bytes(int64_t n_players) { return n_players < 0 ? TS_E_ARG : n_players * 32; }
+
+extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
+                              const uint32_t *pred, int64_t n_matches, int32_t slots, const ts_outputs *outputs,
+                              int32_t lanes_per_match, void *workspace, int64_t workspace_bytes, void *stream)
+{
+    if (!ctx || !table || !table->data || (n_matches > 0 && (!ids || !meta || !pred || !workspace))) {
+        ts_set_error("ts_rate_stream: null argument");
+        return TS_E_ARG;
+    }
+    if (table->row_pairs != 1 || table->shared_col >= 0) {
+        ts_set_error("ts_rate_stream: single-pair ladder tables only (row_pairs == 1, shared_col == -1); use ts_rate");
+        return TS_E_UNSUPPORTED;
+    }
+    if (slots != 6 && slots != 10) {
+        ts_set_error("ts_rate_stream: slots must be 6 or 10 (got %d)", slots);
+        return TS_E_UNSUPPORTED;
+    }
+    if (n_matches < 0 || n_matches >= 0xFFFFFFFFll) {
+        ts_set_error("ts_rate_stream: n_matches outside [0, 2^32 - 1)");
+        return TS_E_ARG;
+    }
+    if (workspace_bytes < table->n_players * 32) {
+        ts_set_error("ts_rate_stream: workspace too small (%lld < %lld bytes)", (long long)workspace_bytes,
+                     (long long)table->n_players * 32);
+        return TS_E_WORKSPACE;
+    }
+    if (n_matches == 0) return 0;
+    TS_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    StreamArgs a;
+    a.prm = ctx->params;
+    a.vt = (unsigned long long *)workspace;
+    a.seed = table->seed;
+    for (int i = 0; i < 16; ++i) a.modes.col[i] = i < 6 ? table->mode_col[i] : (int8_t)-1;
+    a.ids = ids;
+    a.meta = meta;
+    a.pred = pred;
+    a.n_matches = (uint32_t)n_matches;
+    if (outputs) a.out = *outputs;
+    else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
+    a.ctrl = ctx->d_ctrl;
+    const int64_t u = table->n_players;
+    k_vt_load<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, a.vt, u);
+    int lanes = lanes_per_match ? lanes_per_match : 2;
+    int rc = slots == 6 ? dispatch_l<6>(ctx, a, lanes, s) : dispatch_l<10>(ctx, a, lanes, s);
+    if (rc) return rc;
+    k_vt_store<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(a.vt, table->data, u);
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -144,6 +144,7 @@ class Rater(object):
         prm = self.env.params()
         L.check(self._lib.ts_ctx_create(C.byref(prm), self.device.index or 0, C.byref(self._ctx)))
         self._ws = None
+        self._vt = None
 
     def close(self):
         if self._ctx:
@@ -210,6 +211,38 @@ class Rater(object):
                 _ptr(sch.round_offsets), _ptr(sch.info), sch.n_matches, sch.slots, C.byref(out),
                 int(lanes_per_match), _stream_ptr()))
 
+    def link_pred(self, ids, meta, n_players, mode_cols):
+        """First half of the scheduler only: pred[N, P] (previous rated match of
+        each slot's player) for the streaming rating kernel."""
+        assert ids.is_cuda and ids.is_contiguous() and meta.is_contiguous()
+        n, p = ids.shape
+        pred = torch.empty_like(ids)
+        nbytes = L.check(self._lib.ts_link_workspace_bytes(n, p))
+        ws = self._workspace(nbytes)
+        cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
+        with torch.cuda.device(ids.device):
+            L.check(self._lib.ts_link_pred(self._ctx, _ptr(ids), _ptr(meta), n, p, int(n_players),
+                                           (C.c_int8 * 16)(*cols), _ptr(pred), _ptr(ws), ws.numel(),
+                                           _stream_ptr()))
+        return pred
+
+    def rate_stream(self, table, ids, meta, pred, outputs=None, lanes_per_match=0):
+        """Dataflow rating in stream order (single-pair ladder tables only)."""
+        out = L.TsOutputs()
+        if outputs:
+            for k in ("quality", "out_shared", "out_delta", "out_queue", "status"):
+                t = outputs.get(k)
+                setattr(out, k, t.data_ptr() if t is not None else None)
+        desc = table.desc()
+        n, p = ids.shape
+        nbytes = L.check(self._lib.ts_rate_stream_workspace_bytes(table.n_players))
+        if self._vt is None or self._vt.numel() < nbytes:
+            self._vt = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(table.data.device):
+            L.check(self._lib.ts_rate_stream(self._ctx, C.byref(desc), _ptr(ids), _ptr(meta), _ptr(pred), n, p,
+                                             C.byref(out), int(lanes_per_match), _ptr(self._vt),
+                                             self._vt.numel(), _stream_ptr()))
+
     def error_count(self):
         return L.check(self._lib.ts_error_count(self._ctx, _stream_ptr()))
 
@@ -228,7 +261,7 @@ class Rater(object):
 
     # ------------------------------------------------------------------
     def rate_batch(self, ids, meta, table, seed=None, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6),
-                   want_outputs=True, lanes_per_match=0, table_out=None):
+                   want_outputs=True, lanes_per_match=0, table_out=None, path="auto"):
         """The reference-facing batch call with HOST buffers: numpy ids
         [N, P] uint32, meta [N] uint32, table [U, C, 2] float64 (NaN = NULL),
         optional seed [U, 2].  Copies in, schedules, rates, copies back.
@@ -251,11 +284,20 @@ class Rater(object):
         ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
         n, p = ids_d.shape
         self.reset_errors()
-        sch = self.schedule(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
         outs = self.alloc_outputs(n, p) if want_outputs else None
-        self.rate(ptab, sch, outs, lanes_per_match)
+        # single-pair ladders take the streaming (dataflow) path unless told otherwise
+        stream = path == "stream" or (path == "auto" and ptab.shared_col < 0 and tab_d.shape[1] == 1
+                                       and p in (6, 10) and n > 0)
+        if stream:
+            pred = self.link_pred(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
+            self.rate_stream(ptab, ids_d, meta_d, pred, outs, lanes_per_match)
+            n_rounds = None
+        else:
+            sch = self.schedule(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
+            self.rate(ptab, sch, outs, lanes_per_match)
+            n_rounds = sch.n_rounds
         bad = self.error_count()
-        result = dict(n_rounds=sch.n_rounds, errors=bad)
+        result = dict(n_rounds=n_rounds, errors=bad)
         if outs is not None:
             for k, t in outs.items():
                 result[k] = t.cpu().numpy()

@@ -42,13 +42,17 @@ FALLBACK_HBM_GBS = 6650.0     # /opt/skills/guides/B200_PROFILING.md, used only 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--matches", type=int, default=10_000_000)
     ap.add_argument("--players", type=int, default=1_000_000)
     ap.add_argument("--slots", type=int, default=6)
     ap.add_argument("--lanes", type=int, default=0, help="lanes per match of the rating kernel (0 = default)")
+    ap.add_argument("--path", default="stream", choices=["rounds", "stream"],
+                    help="headline path. stream: ts_link_pred + ts_rate_stream (sort, link, dataflow rating in stream "
+                         "order); rounds: ts_schedule + ts_rate (sort, link, frontier relaxation, round buckets, one "
+                         "grid barrier per round).  Both are timed every run; the other one is reported under 'paths'.")
     ap.add_argument("--zipf", action="store_true")
     ap.add_argument("--p-draw", type=float, default=0.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -273,46 +277,66 @@ def run_b200(a):
         torch.cuda.synchronize()
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
-    sched_ms, rate_ms = [], []
+    timings = {"stream": ([], []), "rounds": ([], [])}
     n_rounds = 0
+    final = {}
 
-    def step(timed):
+    def step(path, timed):
         nonlocal n_rounds
         table.copy_(table0)
         flush.fill_(1)                       # evict ids/table from L2 between steps
         e0, e1, e2 = ev(), ev(), ev()
         e0.record()
-        sch = rater.schedule(ids_d, meta_d, u, ptab.mode_cols)
-        e1.record()
-        rater.rate(ptab, sch, None, a.lanes)
+        if path == "stream":
+            pred = rater.link_pred(ids_d, meta_d, u, ptab.mode_cols)
+            e1.record()
+            rater.rate_stream(ptab, ids_d, meta_d, pred, None, a.lanes)
+        else:
+            sch = rater.schedule(ids_d, meta_d, u, ptab.mode_cols)
+            e1.record()
+            rater.rate(ptab, sch, None, a.lanes)
+            n_rounds = sch.n_rounds
         e2.record()
-        n_rounds = sch.n_rounds
         if timed:
             torch.cuda.synchronize()
-            sched_ms.append(e0.elapsed_time(e1))
-            rate_ms.append(e1.elapsed_time(e2))
-        return sch
+            timings[path][0].append(e0.elapsed_time(e1))
+            timings[path][1].append(e1.elapsed_time(e2))
 
-    for _ in range(a.warmup):
-        step(False)
+    other = "rounds" if a.path == "stream" else "stream"
+    for path in (other, a.path):
+        for _ in range(a.warmup):
+            step(path, False)
+    # the secondary path first (outside the contract's timed region, device-timed all the same) ...
+    barrier()
+    for _ in range(a.steps):
+        step(other, True)
+    final[other] = table.clone()
+    # ... then the headline path inside the contract's timed region
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
     t_wall = time.perf_counter()
     for _ in range(a.steps):
-        step(True)
+        step(a.path, True)
     barrier()
     t_wall = time.perf_counter() - t_wall
     clocks = sampler.stop()
+    final[a.path] = table.clone()
     assert rater.error_count() == 0
+    # both paths rate the same ladder: their tables must agree to rounding
+    assert float((final["stream"] - final["rounds"]).abs().max()) < 1e-9, "stream and rounds paths disagree"
 
-    ms_sched = sum(sched_ms) / len(sched_ms)
-    ms_rate = sum(rate_ms) / len(rate_ms)
+    def mean_ms(path):
+        sc, rt = timings[path]
+        return sum(sc) / len(sc), sum(rt) / len(rt)
+
+    ms_sched, ms_rate = mean_ms(a.path)
+    ms_sched2, ms_rate2 = mean_ms(other)
     ms_step = ms_sched + ms_rate
     if dist is not None:
-        t = torch.tensor([ms_step, ms_sched, ms_rate], dtype=torch.float64, device=dev)
+        t = torch.tensor([ms_step, ms_sched, ms_rate, ms_sched2, ms_rate2], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_step, ms_sched, ms_rate = (float(x) for x in t.cpu())
+        ms_step, ms_sched, ms_rate, ms_sched2, ms_rate2 = (float(x) for x in t.cpu())
 
     # ---- e2e: the reference-facing call with pinned host buffers -----------
     e2e = None
@@ -328,7 +352,7 @@ def run_b200(a):
                 barrier()
                 t0 = time.perf_counter()
             res = rater.rate_batch(ids_h, meta_h, tab_h, shared_col=-1, mode_cols=ptab.mode_cols[:6],
-                                   want_outputs=False, lanes_per_match=a.lanes, table_out=out_h)
+                                   want_outputs=False, lanes_per_match=a.lanes, table_out=out_h, path=a.path)
         barrier()
         dt = (time.perf_counter() - t0) / k_e2e
         if dist is not None:
@@ -336,7 +360,7 @@ def run_b200(a):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.cpu()[0])
         # the e2e result must be the same table the device-resident path produced
-        assert torch.equal(out_h, table.cpu()), "e2e table differs from the HBM-resident run"
+        assert torch.equal(out_h, final[a.path].cpu()), "e2e table differs from the HBM-resident run"
         h2d = ids_h.numel() * 4 + meta_h.numel() * 4 + tab_h.numel() * 8
         e2e = {"value": n * world / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": out_h.numel() * 8 + 8 + 16, "ms_per_step": dt * 1e3, "steps": k_e2e}
@@ -353,7 +377,7 @@ def run_b200(a):
     tp = os.path.join(ROOT, "profiles", "rate_kernel_traffic.json")
     if os.path.exists(tp):
         try:
-            tj = json.load(open(tp))
+            tj = json.load(open(tp)).get(kernel, {})
             if tj.get("matches") == n and tj.get("slots") == p:
                 traffic = tj.get("dram_bytes_per_launch")
         except Exception:
@@ -361,12 +385,15 @@ def run_b200(a):
     b_sched = sched_bytes_per_match(p, u)
     passes_p = (max(1, u.bit_length()) + 7) // 8
     passes_r = (max(1, n_rounds.bit_length()) + 7) // 8
-    launches = 4 * passes_p + 2 + 1 + 1 + 4 * passes_r + 1 + 1   # sort, link+init, frontier, offsets, sort, permute, rate
+    pred_passes = -(-(n * p) // (16 << 20))
+    launches = {"stream": 4 * passes_p + pred_passes + 3,      # sort, pred passes, vt load, rate_stream, vt store
+                "rounds": 4 * passes_p + 2 + 1 + 1 + 4 * passes_r + 1 + 1}   # sort, link+init, frontier, offsets, sort, permute, rate
+    kernel = "k_rate_stream" if a.path == "stream" else "k_rate"
     line = {
         "metric": METRIC, "value": n * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(a), "seed": hex(SEED), "rounds": n_rounds,
+        "config": {"workload": workload_name(a), "seed": hex(SEED), "rounds": n_rounds, "path": a.path,
                    "per_gpu": "one independent ladder per GPU, no data-path collective" if world > 1 else "single GPU",
                    "l2": "256 MiB flush between steps; ids+meta (%d MB) exceed the 126 MB L2; the %d MB player "
                          "table is L2-resident by nature" % ((n * p * 4 + n * 4) >> 20, (u * 16) >> 20),
@@ -374,14 +401,19 @@ def run_b200(a):
         "phases": {"schedule_ms": ms_sched, "rate_ms": ms_rate,
                    "rate_only_matches_per_s": n * world / (ms_rate * 1e-3),
                    "schedule_only_matches_per_s": n * world / (ms_sched * 1e-3)},
-        "roofline": {"kernel": "k_rate", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "paths": {a.path: {"schedule_ms": ms_sched, "rate_ms": ms_rate, "matches_per_s": n * world / (ms_step * 1e-3)},
+                  other: {"schedule_ms": ms_sched2, "rate_ms": ms_rate2,
+                          "matches_per_s": n * world / ((ms_sched2 + ms_rate2) * 1e-3)},
+                  "note": "stream = sort + link + dataflow rating in stream order; rounds = sort + link + frontier "
+                          "relaxation + round buckets + one grid barrier per round; same ratings (checked)"},
+        "roofline": {"kernel": kernel, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_match": b_rate,
                      "note": "one launch per step; duration = CUDA events around ts_rate on its stream"},
         "roofline_schedule": {"bound": "hbm", "achieved": b_sched * n / (ms_sched * 1e-3) / 1e9, "peak": peak,
                               "unit": "GB/s", "frac": b_sched * n / (ms_sched * 1e-3) / 1e9 / peak,
                               "algorithmic_bytes_per_match": b_sched},
-        "gpu_launches": launches * a.steps,
+        "gpu_launches": launches[a.path] * a.steps,
         "clocks": clocks,
         "wall_s_timed_region": t_wall,
     }

@@ -155,6 +155,25 @@ int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_sorted,
             const ts_sched_info *info, int64_t n_matches, int32_t slots,
             const ts_outputs *outputs, int32_t lanes_per_match, void *stream);
 
+/* Streaming (dataflow) form of the same path for single-pair ladders
+ * (table.row_pairs == 1, shared_col == -1): no rounds, no barriers.
+ * ts_link_pred does the first half of the scheduler only -- radix sort by
+ * player id and chain linking -- and writes pred[N][P]: for every slot the
+ * index of that player's previous rated match in the stream (TS_NONE if none;
+ * undefined for empty slots and gated matches).  ts_rate_stream then rates
+ * the matches in stream order (worker.py:192), each match waiting until its
+ * players' rows carry the version pred names.  Results are identical to
+ * ts_schedule + ts_rate.  ids / meta are in ORIGINAL order; outputs (quality,
+ * out_queue, status) too.  workspace: ts_rate_stream_workspace_bytes(U). */
+int64_t ts_link_workspace_bytes(int64_t n_matches, int32_t slots);
+int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
+                 int64_t n_players, const int8_t mode_col[16], uint32_t *pred, void *workspace,
+                 int64_t workspace_bytes, void *stream);
+int64_t ts_rate_stream_workspace_bytes(int64_t n_players);
+int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
+                   const uint32_t *pred, int64_t n_matches, int32_t slots, const ts_outputs *outputs,
+                   int32_t lanes_per_match, void *workspace, int64_t workspace_bytes, void *stream);
+
 /* Number of matches that ended in TS_ST_FP_ERROR / TS_ST_VALUE_ERROR since the
  * last ts_reset_errors (the reference raises and fails the whole batch,
  * worker.py:108-120,195-197).  Synchronises the stream. */

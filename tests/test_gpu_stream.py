@@ -1,0 +1,138 @@
+"""The streaming (dataflow) rating path: ts_link_pred + ts_rate_stream through
+the C ABI, against the sequential oracles.  pred is integer work and must be
+bit-exact; ratings within 1e-9 (north-star tolerance) and equal to what the
+round-based path gives."""
+import numpy as np
+import pytest
+import torch
+
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-9
+
+
+def _u32(t):
+    return t.cpu().numpy().view(np.uint32)
+
+
+def _dev(a):
+    if a.dtype == np.uint32:
+        a = a.view(np.int32)
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def _pred_oracle(ids, meta, mode_cols):
+    """Sequential definition: previous rated match of each slot's player."""
+    n, p = ids.shape
+    last = {}
+    pred = np.full((n, p), 0xFFFFFFFF, dtype=np.uint32)
+    live = np.zeros((n, p), dtype=bool)
+    for m in range(n):
+        bits = int(meta[m])
+        mode = (bits >> 4) & 15
+        if mode >= 6 or mode_cols[mode] < 0 or bits & 12:
+            continue
+        row = [int(x) for x in ids[m]]
+        for s, pl in enumerate(row):
+            if pl == H.EMPTY:
+                continue
+            live[m, s] = True
+            pred[m, s] = last.get(pl, 0xFFFFFFFF)
+        for pl in row:
+            if pl != H.EMPTY:
+                last[pl] = m
+    return pred, live
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from analyzer_b200 import engine
+    return engine
+
+
+def test_link_pred_bit_exact(eng):
+    rater = eng.Rater(eng.Env(), 0)
+    rng = np.random.default_rng(5)
+    ids, meta = H.small_ladder(rng, 20000, 900, slots=10, modes=(1,), p_afk=0.1, p_unsupported=0.05, ragged=True)
+    ids[7, 4] = ids[7, 0]                      # a player listed twice in one match
+    ids[8, 1] = ids[7, 0]
+    cols = [-1, 0]
+    pred = _u32(rater.link_pred(_dev(ids), _dev(meta), 900, cols))
+    want, live = _pred_oracle(ids, meta, cols + [-1] * 14)
+    assert np.array_equal(pred[live], want[live])
+    rater.close()
+
+
+@pytest.mark.parametrize("slots,lanes,p_draw,env_draw,zipf", [
+    (6, 1, 0.0, 0.0, False), (6, 2, 0.05, 0.0, False), (6, 8, 0.0, 0.0, True),
+    (10, 2, 0.02, 0.02, True), (10, 16, 0.02, 0.02, False), (6, 32, 0.0, 0.0, False)])
+def test_stream_vs_oracle_and_rounds(eng, c_oracle, slots, lanes, p_draw, env_draw, zipf):
+    """Deep chains (~400 matches per player): every dependency is exercised."""
+    dev = torch.device("cuda", 0)
+    n, n_players, seed = 200_000, 3_000, 0xA11CE0E0 + slots + lanes
+    r = eng.Rater(eng.Env(draw_probability=env_draw), 0)
+    gd = eng.make_gen(seed, n_players, slots=slots, mode=1, p_draw=p_draw, p_afk=0.03, zipf=zipf)
+    ids_d, meta_d = eng.gen_matches(gd, 0, n, dev)
+    tab_a = eng.gen_table(seed, 0, n_players, dev)
+    tab_b = tab_a.clone()
+    want = tab_a.cpu().numpy()
+    pa, pb = eng.PlayerTable.ladder(tab_a, mode=1), eng.PlayerTable.ladder(tab_b, mode=1)
+    outs_a, outs_b = r.alloc_outputs(n, slots), r.alloc_outputs(n, slots)
+    pred = r.link_pred(ids_d, meta_d, n_players, pa.mode_cols)
+    r.rate_stream(pa, ids_d, meta_d, pred, outs_a, lanes)
+    sch = r.schedule(ids_d, meta_d, n_players, pb.mode_cols)
+    r.rate(pb, sch, outs_b, lanes)
+    assert r.error_count() == 0
+    prm = c_oracle.make_params(1000.0, 10.0, env_draw)
+    out = c_oracle.rate_sequential(prm, _u32(ids_d), _u32(meta_d), want, -1, pa.mode_cols[:6], quad=True,
+                                   want_outputs=True)
+    assert out["errors"] == 0
+    got = tab_a.cpu().numpy()
+    assert np.abs(got - want).max() < TOL
+    assert np.abs(got - tab_b.cpu().numpy()).max() < TOL
+    st = outs_a["status"].cpu().numpy()
+    assert np.array_equal(st, out["status"]) and np.array_equal(st, outs_b["status"].cpu().numpy())
+    rated = st == 0
+    q = outs_a["quality"].cpu().numpy()
+    assert np.abs(q[rated] - out["quality"][rated]).max() < 1e-12 and np.all(q[st == 2] == 0)
+    oq, wq = outs_a["out_queue"].cpu().numpy()[rated], out["out_queue"][rated]
+    assert np.array_equal(np.isnan(oq), np.isnan(wq))
+    assert np.nanmax(np.abs(oq - wq)) < TOL
+    r.close()
+
+
+def test_stream_errors_do_not_stall_successors(eng, c_oracle):
+    """A match the reference would raise on writes nothing but still releases
+    the players' next matches (no deadlock), and is counted."""
+    ids = np.array([[0, 1, 2, 3, 4, 5], [0, 6, 7, 8, 9, 10], [0, 1, 2, 6, 7, 8]], dtype=np.uint32)
+    meta = np.full(3, 1 | (1 << 4), dtype=np.uint32)
+    table = np.full((11, 1, 2), np.nan)
+    table[:, 0] = (1500.0, 300.0)
+    table[3, 0, 1] = 0.0                            # sigma == 0: ValueError for match 0
+    r = eng.Rater(eng.Env(), 0)
+    tab_d = _dev(table)
+    ptab = eng.PlayerTable(tab_d, -1, [-1, 0])
+    outs = r.alloc_outputs(3, 6)
+    r.reset_errors()
+    pred = r.link_pred(_dev(ids), _dev(meta), 11, ptab.mode_cols)
+    r.rate_stream(ptab, _dev(ids), _dev(meta), pred, outs)
+    want = table.copy()
+    o = c_oracle.rate_sequential(c_oracle.make_params(), ids, meta, want, -1, [-1, 0], want_outputs=True)
+    assert list(outs["status"].cpu().numpy()) == list(o["status"]) == [5, 0, 0]
+    assert r.error_count() == 1
+    got = tab_d.cpu().numpy()
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and np.nanmax(np.abs(got - want)) < TOL
+    r.reset_errors()
+    r.close()
+
+
+def test_stream_rejects_faithful_layout(eng):
+    from analyzer_b200._lib import TsError
+    r = eng.Rater(eng.Env(), 0)
+    ptab = eng.PlayerTable.faithful(8, torch.device("cuda", 0))
+    ids = torch.zeros((1, 6), dtype=torch.int32, device="cuda")
+    meta = torch.zeros((1,), dtype=torch.int32, device="cuda")
+    with pytest.raises(TsError, match="single-pair ladder"):
+        r.rate_stream(ptab, ids, meta, ids.clone())
+    r.close()
