@@ -150,7 +150,7 @@ k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n,
         uint32_t idx = wbase + k * 32 + lane;
         key[k] = idx < n ? load_key(src, idx) : 0u;
     }
-    // ... then the ranks: lanes with equal digits find each other with match.any;
+    // ... then the ranks: lanes with equal digits find each other (ballots, below);
     // the lowest such lane bumps the warp's counter of that digit with a shared-
     // memory atomic (same-address atomics of one warp retire in program order, so
     // later steps rank behind earlier ones: stable)
@@ -158,8 +158,17 @@ k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n,
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
         bool ok = idx < n;
-        uint32_t d = ok ? ((key[k] >> shift) & 255u) : 256u;   // 256 = padding, matches only padding
-        uint32_t peers = __match_any_sync(0xFFFFFFFFu, d);
+        const uint32_t d = (key[k] >> shift) & 255u;
+        // lanes holding the same digit: one ballot per digit bit (match.any walks the
+        // distinct values of the warp one by one and is several times slower here)
+        uint32_t peers = __ballot_sync(0xFFFFFFFFu, ok);
+        peers = ok ? peers : ~peers;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            const bool bit = (d >> b) & 1u;
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, bit);
+            peers &= bit ? bal : ~bal;
+        }
         int leader = __ffs(peers) - 1;
         uint32_t prev = 0;
         if (ok && lane == leader) prev = atomicAdd(&wcount[warp][d], (uint32_t)__popc(peers));
