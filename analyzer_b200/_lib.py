@@ -63,7 +63,7 @@ def sources():
 def build(force=False, verbose=False):
     """Compile the CUDA library in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
     srcs = sources()
-    deps = srcs + [os.path.join(CSRC, "common.cuh"),
+    deps = srcs + [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "vw.cuh"), os.path.join(CSRC, "vtable.inc"),
                    os.path.join(os.path.dirname(_HERE), "include", "tsrate.h")]
     if not force and os.path.exists(LIB_PATH) and \
             all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):

@@ -23,6 +23,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "vw.cuh"
 
 namespace {
 
@@ -68,45 +69,7 @@ __device__ __forceinline__ uint32_t group_sum_u32(uint32_t x)
     return x;
 }
 
-constexpr double kInvSqrt2 = 0.70710678118654752440;
-constexpr double kSqrt2OverPi = 0.79788456080286535588;   // sqrt(2/pi) = pdf(0) * 2
-constexpr double kInvSqrt2Pi = 0.39894228040143267794;
-
-__device__ __forceinline__ double npdf(double x) { return kInvSqrt2Pi * exp(-0.5 * x * x); }
-__device__ __forceinline__ double ncdf(double x) { return 0.5 * erfc(-x * kInvSqrt2); }
-
-// v and w of the truncate factor at (t, eps); returns false where the trueskill
-// package raises FloatingPointError.
-__device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, bool draw_is_zero,
-                                         double &v, double &w)
-{
-    if (!is_draw) {
-        // v = pdf(x)/cdf(x) = sqrt(2/pi) / erfcx(-x/sqrt2): no cancellation in either tail
-        double x = t - eps;
-        double e = erfcx(-x * kInvSqrt2);
-        v = kSqrt2OverPi / e;
-        w = v * (v + x);
-        if (w > 0.0 && w < 1.0) return true;
-        // far favourite-wins tail: erfcx overflows where the 50-digit reference
-        // still sees 0 < w << 1e-300; the update is then the tau-only one.
-        if (x > 30.0 && w >= 0.0) { v = 0.0; w = 0.0; return true; }
-        return false;
-    }
-    if (draw_is_zero) {   // draw_probability = 0: limit of v_draw/w_draw for eps -> 0
-        v = -t;
-        w = 1.0;
-        return true;
-    }
-    double at = fabs(t);
-    double a = eps - at, b = -eps - at;
-    double mass = ncdf(a) - ncdf(b);
-    if (mass == 0.0) return false;
-    double pa = npdf(a), pb = npdf(b);
-    double vv = (pb - pa) / mass;
-    w = vv * vv + (a * pa - b * pb) / mass;
-    v = t < 0.0 ? -vv : vv;
-    return true;
-}
+using tsvw::trunc_vw;
 
 // ---- asynchronous staging of match records (cp.async = LDGSTS) -------------
 __device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)

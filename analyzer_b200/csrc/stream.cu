@@ -28,6 +28,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "vw.cuh"
 
 namespace {
 
@@ -75,35 +76,7 @@ __device__ __forceinline__ double row_sigma(const unsigned long long (&w)[4])
     return __longlong_as_double((long long)((w[2] & 0xFFFFFFFFull) | (w[3] << 32)));
 }
 
-constexpr double kInvSqrt2 = 0.70710678118654752440;
-constexpr double kSqrt2OverPi = 0.79788456080286535588;
-constexpr double kInvSqrt2Pi = 0.39894228040143267794;
-__device__ __forceinline__ double npdf(double x) { return kInvSqrt2Pi * exp(-0.5 * x * x); }
-__device__ __forceinline__ double ncdf(double x) { return 0.5 * erfc(-x * kInvSqrt2); }
-
-// identical to rate.cu's trunc_vw (kept textually in step with it)
-__device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, bool draw_is_zero, double &v, double &w)
-{
-    if (!is_draw) {
-        double x = t - eps;
-        double e = erfcx(-x * kInvSqrt2);
-        v = kSqrt2OverPi / e;
-        w = v * (v + x);
-        if (w > 0.0 && w < 1.0) return true;
-        if (x > 30.0 && w >= 0.0) { v = 0.0; w = 0.0; return true; }
-        return false;
-    }
-    if (draw_is_zero) { v = -t; w = 1.0; return true; }
-    double at = fabs(t);
-    double a = eps - at, b = -eps - at;
-    double mass = ncdf(a) - ncdf(b);
-    if (mass == 0.0) return false;
-    double pa = npdf(a), pb = npdf(b);
-    double vv = (pb - pa) / mass;
-    w = vv * vv + (a * pa - b * pb) / mass;
-    v = t < 0.0 ? -vv : vv;
-    return true;
-}
+using tsvw::trunc_vw;
 
 __device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)
 {
