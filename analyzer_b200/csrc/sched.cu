@@ -42,14 +42,14 @@ struct KeySrc {
     uint32_t slots;
     uint32_t sentinel;
     int from_ids;
-    unsigned long long slots_magic;   // floor(2^40 / slots) + 1: idx / slots == (idx * magic) >> 40 for idx < 2^32
+    unsigned long long slots_magic;   // floor(2^64 / slots) + 1: idx / slots == umul64hi(idx, magic) for idx < 2^32
 };
 
 __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
 {
     uint32_t k = __ldg(src.keys + idx);
     if (src.from_ids) {
-        uint32_t m = __ldg(src.meta + (uint32_t)(((unsigned long long)idx * src.slots_magic) >> 40));
+        uint32_t m = __ldg(src.meta + (uint32_t)__umul64hi((unsigned long long)idx, src.slots_magic));
         if (k == TS_EMPTY_SLOT || meta_is_gated(m, src.modes.col)) k = src.sentinel;
     }
     return k;
@@ -415,14 +415,14 @@ k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long lon
     const uint32_t v = __ldcs(vals + i), k = __ldcs(keys + i);
     const uint32_t kp = i > 0 ? __ldcs(keys + i - 1) : ~k, vp = i > 0 ? __ldcs(vals + i - 1) : 0u;
     if (v < v_lo || v >= v_hi || k >= sentinel) return;   // other pass / empty slot / gated match
-    const uint32_t m = (uint32_t)(((unsigned long long)v * slots_magic) >> 40);
+    const uint32_t m = (uint32_t)__umul64hi((unsigned long long)v, slots_magic);
     uint32_t pm = TS_NONE;
     if (kp == k) {
-        pm = (uint32_t)(((unsigned long long)vp * slots_magic) >> 40);
+        pm = (uint32_t)__umul64hi((unsigned long long)vp, slots_magic);
         if (pm == m) {          // the player is listed twice in this match: walk back to a different match
             pm = TS_NONE;
             for (uint32_t j = i - 1; j > 0 && __ldcs(keys + j - 1) == k; --j) {
-                uint32_t mj = (uint32_t)(((unsigned long long)__ldcs(vals + j - 1) * slots_magic) >> 40);
+                uint32_t mj = (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + j - 1), slots_magic);
                 if (mj != m) { pm = mj; break; }
             }
         }
@@ -572,7 +572,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     src.slots = (uint32_t)slots;
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
-    src.slots_magic = ((1ull << 40) / (unsigned long long)slots) + 1ull;
+    src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s);
     if (buf < 0) return buf;
 
@@ -621,7 +621,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     rsrc.slots = 1;
     rsrc.sentinel = 0;
     rsrc.from_ids = 0;
-    rsrc.slots_magic = (1ull << 40) + 1ull;
+    rsrc.slots_magic = 0ull;   // unused: keys are read as they are
     buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s);
     if (buf < 0) return buf;
     TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
@@ -683,7 +683,7 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
     src.slots = (uint32_t)slots;
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
-    src.slots_magic = ((1ull << 40) / (unsigned long long)slots) + 1ull;
+    src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s);
     if (buf < 0) return buf;
     // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2

@@ -136,3 +136,40 @@ def test_stream_rejects_faithful_layout(eng):
     with pytest.raises(TsError, match="single-pair ladder"):
         r.rate_stream(ptab, ids, meta, ids.clone())
     r.close()
+
+
+def test_large_index_range(eng):
+    """300M slot entries (5v5, 30M matches, Zipf): index arithmetic beyond 2^28
+    (a 64-bit overflow in the divide-by-slots multiplication once broke exactly
+    this).  Checked on the device: every pred is an earlier match containing the
+    same player, first appearances carry TS_NONE, and the streaming and
+    round-based paths agree on the final table."""
+    dev = torch.device("cuda", 0)
+    n, u, slots = 30_000_000, 3_000_000, 10
+    r = eng.Rater(eng.Env(draw_probability=0.02), 0)
+    gen = eng.make_gen(0xA11CE003, u, slots=slots, mode=1, p_draw=0.02, zipf=True)
+    ids, meta = eng.gen_matches(gen, 0, n, dev)
+    cols = [-1, 0]
+    pred = r.link_pred(ids, meta, u, cols)
+    p64 = pred.to(torch.int64) & 0xFFFFFFFF
+    has = p64 != 0xFFFFFFFF
+    m_idx = torch.arange(n, device=dev).unsqueeze(1).expand(n, slots)
+    assert bool((p64[has] < m_idx[has]).all())
+    bad = 0
+    for lo in range(0, n, 2_000_000):
+        hi = min(n, lo + 2_000_000)
+        rows = ids[p64[lo:hi].clamp(max=n - 1).reshape(-1)].reshape(hi - lo, slots, slots)
+        same = (rows == ids[lo:hi].unsqueeze(2)).any(dim=2)
+        bad += int((~same & has[lo:hi]).sum())
+    assert bad == 0
+    assert int((~has).sum()) == int(torch.unique(ids).numel())
+    del p64, has, m_idx, rows, same
+    tab_a = eng.gen_table(3, 0, u, dev)
+    tab_b = tab_a.clone()
+    pa, pb = eng.PlayerTable.ladder(tab_a, mode=1), eng.PlayerTable.ladder(tab_b, mode=1)
+    r.rate_stream(pa, ids, meta, pred)
+    sch = r.schedule(ids, meta, u, pb.mode_cols)
+    r.rate(pb, sch)
+    assert r.error_count() == 0
+    assert float((tab_a - tab_b).abs().max()) < TOL
+    r.close()
