@@ -25,7 +25,8 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_workspace_bytes", "ts_schedule", "ts_rate", "ts_error_count",
            "ts_reset_errors", "ts_gen_matches", "ts_gen_table",
            "ts_schedule_static", "ts_schedule_static_max_slot_entries",
-           "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream"]
+           "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream",
+           "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_rate_stream_sharded"]
 
 
 class TsParams(C.Structure):
@@ -116,6 +117,13 @@ def lib():
         L.ts_rate_stream.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32, C.c_void_p,
                                      C.c_int64, C.c_void_p]
+        L.ts_shard_alloc.argtypes = [C.c_int, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]
+        L.ts_shard_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
+        L.ts_shard_close.argtypes = [C.c_void_p]
+        L.ts_shard_free.argtypes = [C.c_void_p]
+        L.ts_rate_stream_sharded.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
+                                             C.POINTER(C.c_void_p), C.c_int8, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32, C.c_void_p]
         L.ts_gen_matches.argtypes = [C.POINTER(TsGen), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                      C.c_void_p]
         L.ts_gen_table.argtypes = [C.c_uint64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]

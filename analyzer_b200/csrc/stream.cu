@@ -26,6 +26,7 @@
 // Single-pair ladders only (table.row_pairs == 1, shared_col == -1): the
 // faithful shared + queue layout keeps using ts_rate.
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 #include "vw.cuh"
@@ -34,9 +35,17 @@ namespace {
 
 constexpr int kBlock = 256;
 
+constexpr int kMaxShards = 16;
+
 struct StreamArgs {
     ts_params prm;
-    unsigned long long *vt;       // versioned rows, 4 words per player
+    unsigned long long *vt;       // versioned rows, 4 words per player (single-GPU form)
+    // sharded form: player p lives on GPU p % n_shards, local row p / n_shards; shards[g] is
+    // that GPU's row array (own memory or a peer mapping reached over NVLink)
+    unsigned long long *shards[kMaxShards];
+    uint32_t n_shards;            // power of two
+    uint32_t shard_shift;         // log2(n_shards)
+    uint32_t rank;
     const double *seed;
     ModeCols modes;
     const uint32_t *ids;
@@ -47,11 +56,19 @@ struct StreamArgs {
     unsigned long long *ctrl;
 };
 
+// SYS = rows may live in a peer GPU's memory: system scope (peer accesses bypass the local L2)
+template <bool SYS = false>
 __device__ __forceinline__ void ld_row(const unsigned long long *row, unsigned long long (&w)[4])
 {
-    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(row) : "memory");
-    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(row + 2) : "memory");
+    if (SYS) {
+        asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(row) : "memory");
+        asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(row + 2) : "memory");
+    } else {
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(row) : "memory");
+        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(row + 2) : "memory");
+    }
 }
+template <bool SYS = false>
 __device__ __forceinline__ void st_row(unsigned long long *row, double mu, double sigma, uint32_t ver)
 {
     const unsigned long long v = (unsigned long long)ver << 32;
@@ -59,8 +76,13 @@ __device__ __forceinline__ void st_row(unsigned long long *row, double mu, doubl
     const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
     unsigned long long w0 = (m & 0xFFFFFFFFull) | v, w1 = (m >> 32) | v;
     unsigned long long w2 = (s & 0xFFFFFFFFull) | v, w3 = (s >> 32) | v;
-    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"(w0), "l"(w1) : "memory");
-    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"(w2), "l"(w3) : "memory");
+    if (SYS) {
+        asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"(w0), "l"(w1) : "memory");
+        asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"(w2), "l"(w3) : "memory");
+    } else {
+        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"(w0), "l"(w1) : "memory");
+        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"(w2), "l"(w3) : "memory");
+    }
 }
 __device__ __forceinline__ bool row_has_version(const unsigned long long (&w)[4], uint32_t ver)
 {
@@ -74,6 +96,13 @@ __device__ __forceinline__ double row_mu(const unsigned long long (&w)[4])
 __device__ __forceinline__ double row_sigma(const unsigned long long (&w)[4])
 {
     return __longlong_as_double((long long)((w[2] & 0xFFFFFFFFull) | (w[3] << 32)));
+}
+
+template <bool SHARDED>
+__device__ __forceinline__ unsigned long long *row_of(const StreamArgs &a, uint32_t pid)
+{
+    if (!SHARDED) return a.vt + (size_t)pid * 4;
+    return a.shards[pid & (a.n_shards - 1u)] + (size_t)(pid >> a.shard_shift) * 4;
 }
 
 using tsvw::trunc_vw;
@@ -130,7 +159,10 @@ __device__ __forceinline__ uint32_t group_sum_u32(uint32_t x, uint32_t gmask)
 // ... of W consecutive matches, in increasing order, and never synchronises
 // with the other warps of its block -- a warp that has to wait for a dependency
 // holds up nothing but its own W matches.
-template <int P, int L>
+// SHARDED: this GPU rates the tiles t with t % n_shards == rank of ONE ladder whose
+// rows are spread over all GPUs; the version protocol is the only synchronisation
+// between GPUs (no inter-GPU barrier, no collective).
+template <int P, int L, bool SHARDED>
 __global__ void __launch_bounds__(kBlock) k_rate_stream(const StreamArgs a)
 {
     constexpr int W = 32 / L;
@@ -148,17 +180,18 @@ __global__ void __launch_bounds__(kBlock) k_rate_stream(const StreamArgs a)
     const double beta2 = a.prm.beta * a.prm.beta;
     const double tb2 = tau2 + beta2;
     const uint32_t n_tiles = (a.n_matches + W - 1) / W;
-    const uint32_t n_warps = gridDim.x * kWarps;
-    const uint32_t warp_id = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;   // neighbouring tiles on different SMs
+    const uint32_t stride = gridDim.x * kWarps * (SHARDED ? a.n_shards : 1u);
+    // neighbouring tiles go to different GPUs, then to different SMs
+    const uint32_t first = ((threadIdx.x >> 5) * gridDim.x + blockIdx.x) * (SHARDED ? a.n_shards : 1u) + (SHARDED ? a.rank : 0u);
 
     int pf = 0;
-    if (warp_id < n_tiles) stage_warp_tile<P, W>(stage, pf, a, warp_id, wl);
-    for (uint32_t tile = warp_id; tile < n_tiles; tile += n_warps) {
+    if (first < n_tiles) stage_warp_tile<P, W>(stage, pf, a, first, wl);
+    for (uint32_t tile = first; tile < n_tiles; tile += stride) {
         cp_async_wait_all();
         __syncwarp();
         const int cur = pf;
         pf ^= 1;
-        if (tile + n_warps < n_tiles) stage_warp_tile<P, W>(stage, pf, a, tile + n_warps, wl);
+        if (tile + stride < n_tiles) stage_warp_tile<P, W>(stage, pf, a, tile + stride, wl);
         const uint32_t base = tile * W;
         const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
         const uint32_t m = base + grp;
@@ -196,7 +229,7 @@ __global__ void __launch_bounds__(kBlock) k_rate_stream(const StreamArgs a)
                 unsigned long long w[SPL][4];
 #pragma unroll
                 for (int k = 0; k < SPL; ++k)
-                    if (!have[k]) ld_row(a.vt + (size_t)pid[k] * 4, w[k]);
+                    if (!have[k]) ld_row<SHARDED>(row_of<SHARDED>(a, pid[k]), w[k]);
 #pragma unroll
                 for (int k = 0; k < SPL; ++k) {
                     if (!have[k] && row_has_version(w[k], want[k])) {
@@ -257,7 +290,7 @@ __global__ void __launch_bounds__(kBlock) k_rate_stream(const StreamArgs a)
                             mu2 = fma(sgn[k] * g, v_q, q_mu[k]);
                             sg2 = sqrt(si * (1.0 - (g * rc_q) * w_q));
                         }
-                        st_row(a.vt + (size_t)pid[k] * 4, mu2, sg2, m);      // first: successors are waiting
+                        st_row<SHARDED>(row_of<SHARDED>(a, pid[k]), mu2, sg2, m);      // first: successors are waiting
                         if (status == TS_ST_OK && a.out.out_queue)
                             __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + (size_t)m * P + s, make_double2(mu2, sg2));
                     }
@@ -307,30 +340,30 @@ int stream_blocks_per_sm_cap()
     return cap;
 }
 
-template <int P, int L>
+template <int P, int L, bool SHARDED>
 int launch_stream(ts_ctx *ctx, const StreamArgs &args, cudaStream_t stream)
 {
     int per_sm = 0;
-    TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rate_stream<P, L>, kBlock, 0));
+    TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rate_stream<P, L, SHARDED>, kBlock, 0));
     if (per_sm < 1) { ts_set_error("stream kernel does not fit on an SM"); return TS_E_CUDA; }
     per_sm = per_sm < stream_blocks_per_sm_cap() ? per_sm : stream_blocks_per_sm_cap();
     dim3 grid(ctx->sm_count * per_sm), block(kBlock);
     void *kargs[] = {(void *)&args};
     // cooperative launch only for its guarantee that the whole grid is resident
-    TS_CUDA(cudaLaunchCooperativeKernel((void *)k_rate_stream<P, L>, grid, block, kargs, 0, stream));
+    TS_CUDA(cudaLaunchCooperativeKernel((void *)k_rate_stream<P, L, SHARDED>, grid, block, kargs, 0, stream));
     return 0;
 }
 
-template <int P>
+template <int P, bool SHARDED>
 int dispatch_l(ts_ctx *ctx, const StreamArgs &a, int lanes, cudaStream_t s)
 {
     switch (lanes) {
-    case 1: return launch_stream<P, 1>(ctx, a, s);
-    case 2: return launch_stream<P, 2>(ctx, a, s);
-    case 4: return launch_stream<P, 4>(ctx, a, s);
-    case 8: return launch_stream<P, 8>(ctx, a, s);
-    case 16: return launch_stream<P, 16>(ctx, a, s);
-    case 32: return launch_stream<P, 32>(ctx, a, s);
+    case 1: return launch_stream<P, 1, SHARDED>(ctx, a, s);
+    case 2: return launch_stream<P, 2, SHARDED>(ctx, a, s);
+    case 4: return launch_stream<P, 4, SHARDED>(ctx, a, s);
+    case 8: return launch_stream<P, 8, SHARDED>(ctx, a, s);
+    case 16: return launch_stream<P, 16, SHARDED>(ctx, a, s);
+    case 32: return launch_stream<P, 32, SHARDED>(ctx, a, s);
     }
     ts_set_error("lanes_per_match must be 0,1,2,4,8,16 or 32 (got %d)", lanes);
     return TS_E_ARG;
@@ -383,9 +416,128 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
     const int64_t u = table->n_players;
     k_vt_load<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, a.vt, u);
     int lanes = lanes_per_match ? lanes_per_match : 2;
-    int rc = slots == 6 ? dispatch_l<6>(ctx, a, lanes, s) : dispatch_l<10>(ctx, a, lanes, s);
+    a.n_shards = 1; a.shard_shift = 0; a.rank = 0;
+    for (int i = 0; i < kMaxShards; ++i) a.shards[i] = nullptr;
+    int rc = slots == 6 ? dispatch_l<6, false>(ctx, a, lanes, s) : dispatch_l<10, false>(ctx, a, lanes, s);
     if (rc) return rc;
     k_vt_store<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(a.vt, table->data, u);
     TS_CUDA(cudaGetLastError());
     return 0;
+}
+
+
+// ---------------------------------------------------------------------------
+// One ladder, table hash-sharded over the GPUs of a node (BASELINE.json
+// configs[4]): player p is owned by GPU p % G (G a power of two), local row
+// p / G.  Every GPU maps all shards (its own allocation plus its peers' through
+// CUDA IPC, reached over NVLink) and rates the warp tiles t with t % G == rank.
+// The row versions are the only synchronisation between GPUs.
+// ---------------------------------------------------------------------------
+namespace {
+
+__global__ void __launch_bounds__(256)
+k_shard_load(const double *table_shard, unsigned long long *vt_shard, int64_t rows)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    double2 r = reinterpret_cast<const double2 *>(table_shard)[i];
+    st_row<true>(vt_shard + i * 4, r.x, r.y, TS_NONE);
+}
+__global__ void __launch_bounds__(256)
+k_shard_store(const unsigned long long *vt_shard, double *table_shard, int64_t rows)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows) return;
+    unsigned long long w[4];
+    ld_row<true>(vt_shard + i * 4, w);
+    reinterpret_cast<double2 *>(table_shard)[i] = make_double2(row_mu(w), row_sigma(w));
+}
+
+}  // namespace
+
+extern "C" int ts_shard_alloc(int device, int64_t bytes, void **ptr, void *handle64)
+{
+    if (!ptr || !handle64 || bytes <= 0) { ts_set_error("ts_shard_alloc: bad argument"); return TS_E_ARG; }
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    TS_CUDA(cudaSetDevice(device));
+    TS_CUDA(cudaMalloc(ptr, (size_t)bytes));
+    TS_CUDA(cudaIpcGetMemHandle((cudaIpcMemHandle_t *)handle64, *ptr));
+    return 0;
+}
+extern "C" int ts_shard_open(int device, const void *handle64, void **ptr)
+{
+    if (!ptr || !handle64) { ts_set_error("ts_shard_open: bad argument"); return TS_E_ARG; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, sizeof h);
+    TS_CUDA(cudaSetDevice(device));
+    TS_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+extern "C" int ts_shard_close(void *ptr)
+{
+    if (ptr) TS_CUDA(cudaIpcCloseMemHandle(ptr));
+    return 0;
+}
+extern "C" int ts_shard_free(void *ptr)
+{
+    if (ptr) TS_CUDA(cudaFree(ptr));
+    return 0;
+}
+
+// phase 0: table_shard -> own rows; phase 1: rate this rank's tiles; phase 2: own rows -> table_shard.
+// The caller separates the phases with a barrier across the ranks (every shard must be loaded
+// before any rank polls it, and every rank must have finished before rows are read back).
+extern "C" int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_shard, int64_t n_players,
+                                      int32_t rank, int32_t n_shards, void *const *vt_shards, int8_t mode,
+                                      const uint32_t *ids, const uint32_t *meta, const uint32_t *pred,
+                                      int64_t n_matches, int32_t slots, const ts_outputs *outputs,
+                                      int32_t lanes_per_match, void *stream)
+{
+    if (!ctx || !vt_shards || n_shards < 1 || n_shards > kMaxShards || (n_shards & (n_shards - 1)) || rank < 0 ||
+        rank >= n_shards || n_players < 1) {
+        ts_set_error("ts_rate_stream_sharded: bad argument (n_shards must be a power of two <= %d)", kMaxShards);
+        return TS_E_ARG;
+    }
+    TS_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const int64_t rows = (n_players - rank + n_shards - 1) / n_shards;     // players p with p % G == rank
+    unsigned long long *own = (unsigned long long *)vt_shards[rank];
+    if (phase == 0 || phase == 2) {
+        if (!table_shard || !own) { ts_set_error("ts_rate_stream_sharded: null shard"); return TS_E_ARG; }
+        if (rows > 0) {
+            if (phase == 0) k_shard_load<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(table_shard, own, rows);
+            else k_shard_store<<<(unsigned)((rows + 255) / 256), 256, 0, s>>>(own, table_shard, rows);
+        }
+        TS_CUDA(cudaGetLastError());
+        return 0;
+    }
+    if (phase != 1) { ts_set_error("ts_rate_stream_sharded: phase must be 0, 1 or 2"); return TS_E_ARG; }
+    if (slots != 6 && slots != 10) { ts_set_error("ts_rate_stream_sharded: slots must be 6 or 10"); return TS_E_UNSUPPORTED; }
+    if (n_matches < 0 || n_matches >= 0xFFFFFFFFll || (n_matches > 0 && (!ids || !meta || !pred))) {
+        ts_set_error("ts_rate_stream_sharded: bad match arrays");
+        return TS_E_ARG;
+    }
+    if (n_matches == 0) return 0;
+    StreamArgs a;
+    a.prm = ctx->params;
+    a.vt = nullptr;
+    a.seed = nullptr;
+    for (int i = 0; i < 16; ++i) a.modes.col[i] = (int8_t)-1;
+    if (mode >= 0 && mode < 6) a.modes.col[mode] = 0;
+    a.ids = ids;
+    a.meta = meta;
+    a.pred = pred;
+    a.n_matches = (uint32_t)n_matches;
+    if (outputs) a.out = *outputs;
+    else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
+    a.ctrl = ctx->d_ctrl;
+    a.n_shards = (uint32_t)n_shards;
+    a.shard_shift = 0;
+    while ((1 << a.shard_shift) < n_shards) ++a.shard_shift;
+    a.rank = (uint32_t)rank;
+    for (int i = 0; i < kMaxShards; ++i) a.shards[i] = i < n_shards ? (unsigned long long *)vt_shards[i] : nullptr;
+    for (int i = 0; i < n_shards; ++i)
+        if (!a.shards[i]) { ts_set_error("ts_rate_stream_sharded: shard %d not mapped", i); return TS_E_ARG; }
+    int lanes = lanes_per_match ? lanes_per_match : 2;
+    return slots == 6 ? dispatch_l<6, true>(ctx, a, lanes, s) : dispatch_l<10, true>(ctx, a, lanes, s);
 }

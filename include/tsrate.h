@@ -174,6 +174,29 @@ int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, cons
                    const uint32_t *pred, int64_t n_matches, int32_t slots, const ts_outputs *outputs,
                    int32_t lanes_per_match, void *workspace, int64_t workspace_bytes, void *stream);
 
+/* One ladder whose player table is hash-sharded over the G GPUs of a node
+ * (BASELINE.json configs[4]): player p is owned by GPU p % G
+ * (G a power of two <= 16) at local row p / G, one process per GPU.  Each rank
+ * allocates its row shard with ts_shard_alloc (a dedicated cudaMalloc, because
+ * the block is exported through CUDA IPC), exchanges the 64-byte handles, maps
+ * its peers' shards with ts_shard_open (NVLink peer memory), and calls
+ * ts_rate_stream_sharded in three phases separated by a barrier across ranks:
+ * 0 load table_shard[rows][2] into the own rows, 1 rate the warp tiles t with
+ * t % G == rank (ids / meta / pred are the full arrays of the ladder, stream
+ * order), 2 read the own rows back.  Between GPUs there is no barrier and no
+ * collective while rating: a match waits for the versions of its players' rows
+ * wherever they live.  vt_shards: host array of G device pointers (index rank
+ * = own shard).  Shard size: 32 bytes * ceil((n_players - rank) / G).
+ * No counterpart in the reference (single process, single thread). */
+int ts_shard_alloc(int device, int64_t bytes, void **ptr, void *handle64);
+int ts_shard_open(int device, const void *handle64, void **ptr);
+int ts_shard_close(void *ptr);
+int ts_shard_free(void *ptr);
+int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_shard, int64_t n_players, int32_t rank,
+                           int32_t n_shards, void *const *vt_shards, int8_t mode, const uint32_t *ids,
+                           const uint32_t *meta, const uint32_t *pred, int64_t n_matches, int32_t slots,
+                           const ts_outputs *outputs, int32_t lanes_per_match, void *stream);
+
 /* Number of matches that ended in TS_ST_FP_ERROR / TS_ST_VALUE_ERROR since the
  * last ts_reset_errors (the reference raises and fails the whole batch,
  * worker.py:108-120,195-197).  Synchronises the stream. */
