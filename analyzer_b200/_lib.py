@@ -19,6 +19,7 @@ EMPTY_SLOT = 0xFFFFFFFF
 META_WIN_A, META_WIN_B, META_AFK, META_INVALID = 1, 2, 4, 8
 META_MODE_SHIFT = 4
 MODE_UNSUPPORTED = 15
+STREAM_LOAD, STREAM_STORE = 1, 2
 ST_OK, ST_SKIP_MODE, ST_AFK, ST_INVALID, ST_FP_ERROR, ST_VALUE_ERROR = range(6)
 
 EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
@@ -111,12 +112,13 @@ def lib():
         L.ts_link_workspace_bytes.restype = C.c_int64
         L.ts_link_workspace_bytes.argtypes = [C.c_int64, C.c_int32]
         L.ts_link_pred.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
-                                   C.POINTER(C.c_int8), C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+                                   C.POINTER(C.c_int8), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64,
+                                   C.c_void_p]
         L.ts_rate_stream_workspace_bytes.restype = C.c_int64
         L.ts_rate_stream_workspace_bytes.argtypes = [C.c_int64]
         L.ts_rate_stream.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p,
-                                     C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32, C.c_void_p,
-                                     C.c_int64, C.c_void_p]
+                                     C.c_int64, C.c_int32, C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32,
+                                     C.c_void_p, C.c_int64, C.c_void_p]
         L.ts_shard_alloc.argtypes = [C.c_int, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]
         L.ts_shard_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
         L.ts_shard_close.argtypes = [C.c_void_p]

@@ -406,7 +406,7 @@ k_permute(const uint32_t *ids, const uint32_t *meta, const uint32_t *order, uint
 // once, complete, instead of being read-modified-written eight times.
 __global__ void __launch_bounds__(256)
 k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long long slots_magic, uint32_t sentinel,
-       uint32_t v_lo, uint32_t v_hi, uint32_t *pred)
+       uint32_t v_lo, uint32_t v_hi, uint32_t seq_base, const uint32_t *last, uint32_t *pred)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -416,7 +416,7 @@ k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long lon
     const uint32_t kp = i > 0 ? __ldcs(keys + i - 1) : ~k, vp = i > 0 ? __ldcs(vals + i - 1) : 0u;
     if (v < v_lo || v >= v_hi || k >= sentinel) return;   // other pass / empty slot / gated match
     const uint32_t m = (uint32_t)__umul64hi((unsigned long long)v, slots_magic);
-    uint32_t pm = TS_NONE;
+    uint32_t pm = TS_NONE;      // local index of the previous match in this window
     if (kp == k) {
         pm = (uint32_t)__umul64hi((unsigned long long)vp, slots_magic);
         if (pm == m) {          // the player is listed twice in this match: walk back to a different match
@@ -427,7 +427,23 @@ k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long lon
             }
         }
     }
+    // stream-wide match numbers; a player's first match of this window continues the
+    // chain at the tail carried over from earlier windows
+    pm = pm != TS_NONE ? seq_base + pm : (last ? __ldg(last + k) : TS_NONE);
     pred[v] = pm;
+}
+
+// after all pred passes: the last slot of every player's run becomes the carried tail
+__global__ void __launch_bounds__(256)
+k_last_update(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long long slots_magic,
+              uint32_t sentinel, uint32_t seq_base, uint32_t *last)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t k = __ldcs(keys + i);
+    if (k >= sentinel) return;
+    if (i + 1 < n && __ldcs(keys + i + 1) == k) return;
+    last[k] = seq_base + (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + i), slots_magic);
 }
 
 struct Workspace {
@@ -645,9 +661,13 @@ extern "C" int64_t ts_link_workspace_bytes(int64_t n_matches, int32_t slots)
 }
 
 extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
-                            int64_t n_players, const int8_t mode_col[16], uint32_t *pred, void *workspace,
-                            int64_t workspace_bytes, void *stream)
+                            int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last,
+                            uint32_t *pred, void *workspace, int64_t workspace_bytes, void *stream)
 {
+    if (seq_base < 0 || seq_base + n_matches >= 0xFFFFFFFFll) {
+        ts_set_error("ts_link_pred: stream-wide match numbers must stay below 2^32 - 1");
+        return TS_E_ARG;
+    }
     if (!ctx || !mode_col || (n_matches > 0 && (!ids || !meta || !pred || !workspace))) {
         ts_set_error("ts_link_pred: null argument");
         return TS_E_ARG;
@@ -686,13 +706,19 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s);
     if (buf < 0) return buf;
-    // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2
-    const uint32_t range = 16u << 20;
+    // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2.
+    // Every pass re-reads the sorted pairs, so this only pays for a handful of passes; a window
+    // too large for that (more than 128 Mi slot entries) takes one pass and the read-modify-writes.
+    uint32_t range = 16u << 20;
+    if (((uint64_t)np + range - 1) / range > 8) range = 0xFFFFFFFFu;
     for (uint64_t lo = 0; lo < np; lo += range) {
         uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);
         k_pred<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, src.slots_magic, (uint32_t)n_players,
-                                                (uint32_t)lo, hi, pred);
+                                                (uint32_t)lo, hi, (uint32_t)seq_base, last, pred);
     }
+    if (last)
+        k_last_update<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, src.slots_magic,
+                                                       (uint32_t)n_players, (uint32_t)seq_base, last);
     TS_CUDA(cudaGetLastError());
     return 0;
 }

@@ -52,6 +52,7 @@ struct StreamArgs {
     const uint32_t *meta;
     const uint32_t *pred;
     uint32_t n_matches;
+    uint32_t seq_base;            // stream-wide number of the first match of this window
     ts_outputs out;
     unsigned long long *ctrl;
 };
@@ -290,7 +291,7 @@ __global__ void __launch_bounds__(kBlock) k_rate_stream(const StreamArgs a)
                             mu2 = fma(sgn[k] * g, v_q, q_mu[k]);
                             sg2 = sqrt(si * (1.0 - (g * rc_q) * w_q));
                         }
-                        st_row<SHARDED>(row_of<SHARDED>(a, pid[k]), mu2, sg2, m);      // first: successors are waiting
+                        st_row<SHARDED>(row_of<SHARDED>(a, pid[k]), mu2, sg2, a.seq_base + m);   // first: successors are waiting
                         if (status == TS_ST_OK && a.out.out_queue)
                             __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + (size_t)m * P + s, make_double2(mu2, sg2));
                     }
@@ -374,9 +375,14 @@ int dispatch_l(ts_ctx *ctx, const StreamArgs &a, int lanes, cudaStream_t s)
 extern "C" int64_t ts_rate_stream_workspace_bytes(int64_t n_players) { return n_players < 0 ? TS_E_ARG : n_players * 32; }
 
 extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
-                              const uint32_t *pred, int64_t n_matches, int32_t slots, const ts_outputs *outputs,
-                              int32_t lanes_per_match, void *workspace, int64_t workspace_bytes, void *stream)
+                              const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
+                              const ts_outputs *outputs, int32_t lanes_per_match, void *workspace,
+                              int64_t workspace_bytes, void *stream)
 {
+    if (seq_base < 0 || seq_base + n_matches >= 0xFFFFFFFFll) {
+        ts_set_error("ts_rate_stream: stream-wide match numbers must stay below 2^32 - 1");
+        return TS_E_ARG;
+    }
     if (!ctx || !table || !table->data || (n_matches > 0 && (!ids || !meta || !pred || !workspace))) {
         ts_set_error("ts_rate_stream: null argument");
         return TS_E_ARG;
@@ -398,7 +404,6 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
                      (long long)table->n_players * 32);
         return TS_E_WORKSPACE;
     }
-    if (n_matches == 0) return 0;
     TS_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
     StreamArgs a;
@@ -410,17 +415,19 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
     a.meta = meta;
     a.pred = pred;
     a.n_matches = (uint32_t)n_matches;
+    a.seq_base = (uint32_t)seq_base;
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;
     const int64_t u = table->n_players;
-    k_vt_load<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, a.vt, u);
+    if (flags & TS_STREAM_LOAD) k_vt_load<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, a.vt, u);
     int lanes = lanes_per_match ? lanes_per_match : 2;
     a.n_shards = 1; a.shard_shift = 0; a.rank = 0;
     for (int i = 0; i < kMaxShards; ++i) a.shards[i] = nullptr;
-    int rc = slots == 6 ? dispatch_l<6, false>(ctx, a, lanes, s) : dispatch_l<10, false>(ctx, a, lanes, s);
+    int rc = 0;
+    if (n_matches > 0) rc = slots == 6 ? dispatch_l<6, false>(ctx, a, lanes, s) : dispatch_l<10, false>(ctx, a, lanes, s);
     if (rc) return rc;
-    k_vt_store<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(a.vt, table->data, u);
+    if (flags & TS_STREAM_STORE) k_vt_store<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(a.vt, table->data, u);
     TS_CUDA(cudaGetLastError());
     return 0;
 }
@@ -528,6 +535,7 @@ extern "C" int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_
     a.meta = meta;
     a.pred = pred;
     a.n_matches = (uint32_t)n_matches;
+    a.seq_base = 0;
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;

@@ -211,9 +211,11 @@ class Rater(object):
                 _ptr(sch.round_offsets), _ptr(sch.info), sch.n_matches, sch.slots, C.byref(out),
                 int(lanes_per_match), _stream_ptr()))
 
-    def link_pred(self, ids, meta, n_players, mode_cols):
-        """First half of the scheduler only: pred[N, P] (previous rated match of
-        each slot's player) for the streaming rating kernel."""
+    def link_pred(self, ids, meta, n_players, mode_cols, seq_base=0, last=None):
+        """First half of the scheduler only: pred[N, P] (stream-wide number of the
+        previous rated match of each slot's player) for the streaming rating
+        kernel.  Windows: seq_base = matches in earlier windows, last = int32
+        [n_players] device tensor of carried chain tails (updated in place)."""
         assert ids.is_cuda and ids.is_contiguous() and meta.is_contiguous()
         n, p = ids.shape
         pred = torch.empty_like(ids)
@@ -222,11 +224,12 @@ class Rater(object):
         cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
         with torch.cuda.device(ids.device):
             L.check(self._lib.ts_link_pred(self._ctx, _ptr(ids), _ptr(meta), n, p, int(n_players),
-                                           (C.c_int8 * 16)(*cols), _ptr(pred), _ptr(ws), ws.numel(),
-                                           _stream_ptr()))
+                                           (C.c_int8 * 16)(*cols), int(seq_base), _ptr(last), _ptr(pred), _ptr(ws),
+                                           ws.numel(), _stream_ptr()))
         return pred
 
-    def rate_stream(self, table, ids, meta, pred, outputs=None, lanes_per_match=0):
+    def rate_stream(self, table, ids, meta, pred, outputs=None, lanes_per_match=0, seq_base=0,
+                    flags=L.STREAM_LOAD | L.STREAM_STORE):
         """Dataflow rating in stream order (single-pair ladder tables only)."""
         out = L.TsOutputs()
         if outputs:
@@ -237,11 +240,24 @@ class Rater(object):
         n, p = ids.shape
         nbytes = L.check(self._lib.ts_rate_stream_workspace_bytes(table.n_players))
         if self._vt is None or self._vt.numel() < nbytes:
+            assert flags & L.STREAM_LOAD, "the versioned rows of an earlier window are gone"
             self._vt = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=self.device)
         with torch.cuda.device(table.data.device):
             L.check(self._lib.ts_rate_stream(self._ctx, C.byref(desc), _ptr(ids), _ptr(meta), _ptr(pred), n, p,
-                                             C.byref(out), int(lanes_per_match), _ptr(self._vt),
-                                             self._vt.numel(), _stream_ptr()))
+                                             int(seq_base), int(flags), C.byref(out), int(lanes_per_match),
+                                             _ptr(self._vt), self._vt.numel(), _stream_ptr()))
+
+    def rate_stream_windows(self, table, ids, meta, window, lanes_per_match=0):
+        """The whole ladder in windows of `window` matches (worker.py:18-20's
+        micro-batches): link + rate per window, chain tails and versioned rows
+        carried from window to window.  Same result as one link + rate."""
+        n, p = ids.shape
+        last = torch.full((table.n_players,), -1, dtype=torch.int32, device=ids.device)   # TS_NONE
+        for lo in range(0, max(n, 1), window):
+            hi = min(n, lo + window)
+            flags = (L.STREAM_LOAD if lo == 0 else 0) | (L.STREAM_STORE if hi >= n else 0)
+            pred = self.link_pred(ids[lo:hi], meta[lo:hi], table.n_players, table.mode_cols, seq_base=lo, last=last)
+            self.rate_stream(table, ids[lo:hi], meta[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags)
 
     def error_count(self):
         return L.check(self._lib.ts_error_count(self._ctx, _stream_ptr()))

@@ -53,6 +53,9 @@ def parse():
                     help="headline path. stream: ts_link_pred + ts_rate_stream (sort, link, dataflow rating in stream "
                          "order); rounds: ts_schedule + ts_rate (sort, link, frontier relaxation, round buckets, one "
                          "grid barrier per round).  Both are timed every run; the other one is reported under 'paths'.")
+    ap.add_argument("--sharded", action="store_true",
+                    help="ONE ladder of --matches over all ranks: player table hash-sharded in NVLink peer memory "
+                         "(BASELINE.json configs[4]); strong scaling.  Default without it: one ladder per rank.")
     ap.add_argument("--zipf", action="store_true")
     ap.add_argument("--p-draw", type=float, default=0.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -443,6 +446,79 @@ def run_b200(a):
     return 0
 
 
+def run_sharded(a):
+    """One ladder, table sharded by player id over the ranks' GPUs; every rank
+    holds the match stream, computes the links (replicated: the distributed
+    sort is not built yet) and rates the tiles t with t % world == rank."""
+    import torch
+    import torch.distributed as dist
+    from analyzer_b200 import engine, sharded
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    else:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29555")
+        dist.init_process_group("gloo", rank=0, world_size=1)
+    n, u, p = a.matches, a.players, a.slots
+    rater = engine.Rater(engine.Env(draw_probability=a.p_draw), local)
+    gen = engine.make_gen(SEED, u, slots=p, mode=1, p_draw=a.p_draw, zipf=a.zipf)
+    ids_d, meta_d = engine.gen_matches(gen, 0, n, dev)
+    full = engine.gen_table(SEED, 0, u, dev).reshape(u, 2)
+    mine0 = sharded.split_table(full, rank, world)
+    mine = mine0.clone()
+    ladder = sharded.ShardedLadder(rater, u, rank, world)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    link_ms, rate_ms = [], []
+    for it in range(a.warmup + a.steps):
+        mine.copy_(mine0)
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = ev(), ev()
+        e0.record()
+        pred = rater.link_pred(ids_d, meta_d, u, [-1, 0])
+        e1.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()          # the rate phase spans host barriers: wall clock between syncs
+        ladder.rate(mine, ids_d, meta_d, pred, mode=1, lanes=a.lanes)
+        dist.barrier()
+        dt = time.perf_counter() - t0
+        if it >= a.warmup:
+            link_ms.append(e0.elapsed_time(e1))
+            rate_ms.append(dt * 1e3)
+    t = torch.tensor([sum(link_ms) / len(link_ms), sum(rate_ms) / len(rate_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_link, ms_rate = (float(x) for x in t.cpu())
+    assert rater.error_count() == 0
+    if rank == 0:
+        remote = (world - 1) / world
+        nv_bytes = remote * p * 64 * n / world          # per GPU, rows read + written remotely (32 B each way)
+        line = {"metric": METRIC, "value": n / ((ms_link + ms_rate) * 1e-3), "unit": UNIT, "n_gpus": world,
+                "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_link + ms_rate, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": workload_name(a) + ", table hash-sharded over %d GPUs (NVLink peer memory)" % world,
+                           "seed": hex(SEED), "path": "stream-sharded",
+                           "note": "link phase replicated on every rank; rate phase split by warp tile, no inter-GPU "
+                                   "barrier or collective; rate_ms is wall clock between host barriers"},
+                "phases": {"schedule_ms": ms_link, "rate_ms": ms_rate, "rate_only_matches_per_s": n / (ms_rate * 1e-3)},
+                "nvlink": {"bytes_per_gpu_per_step": nv_bytes, "achieved_gbs_per_gpu": nv_bytes / (ms_rate * 1e-3) / 1e9,
+                           "peak_gbs_per_direction": 770.0, "note": "remote row reads + writes; 770 GB/s = measured peer copy "
+                           "per direction (B200_PROFILING.md)"}}
+        print(json.dumps(line))
+    ladder.close()
+    dist.destroy_process_group()
+    return 0
+
+
 if __name__ == "__main__":
     args = parse()
-    sys.exit(run_reference(args) if args.impl == "reference" else run_b200(args))
+    if args.impl == "reference":
+        sys.exit(run_reference(args))
+    sys.exit(run_sharded(args) if args.sharded else run_b200(args))

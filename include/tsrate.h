@@ -159,20 +159,33 @@ int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_sorted,
  * (table.row_pairs == 1, shared_col == -1): no rounds, no barriers.
  * ts_link_pred does the first half of the scheduler only -- radix sort by
  * player id and chain linking -- and writes pred[N][P]: for every slot the
- * index of that player's previous rated match in the stream (TS_NONE if none;
+ * stream-wide number of that player's previous rated match (TS_NONE if none;
  * undefined for empty slots and gated matches).  ts_rate_stream then rates
  * the matches in stream order (worker.py:192), each match waiting until its
  * players' rows carry the version pred names.  Results are identical to
  * ts_schedule + ts_rate.  ids / meta are in ORIGINAL order; outputs (quality,
- * out_queue, status) too.  workspace: ts_rate_stream_workspace_bytes(U). */
+ * out_queue, status) too.  workspace: ts_rate_stream_workspace_bytes(U).
+ *
+ * Windows (worker.py:18-20 micro-batches; ladders beyond 2^32 slot entries):
+ * a stream is processed window after window by passing seq_base = number of
+ * matches in the earlier windows, and `last` = device uint32[n_players]
+ * holding every player's latest match so far (all TS_NONE before the first
+ * window; ts_link_pred reads it for chain heads and then updates it).  The
+ * versioned rows stay in `workspace` between windows: pass TS_STREAM_LOAD with
+ * the first window (rows are built from the table) and TS_STREAM_STORE with
+ * the last (table is written back); a one-shot call passes both, seq_base 0
+ * and last = NULL.  Stream-wide match numbers must stay below 2^32 - 1. */
+#define TS_STREAM_LOAD 1
+#define TS_STREAM_STORE 2
 int64_t ts_link_workspace_bytes(int64_t n_matches, int32_t slots);
 int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
-                 int64_t n_players, const int8_t mode_col[16], uint32_t *pred, void *workspace,
-                 int64_t workspace_bytes, void *stream);
+                 int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last, uint32_t *pred,
+                 void *workspace, int64_t workspace_bytes, void *stream);
 int64_t ts_rate_stream_workspace_bytes(int64_t n_players);
 int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
-                   const uint32_t *pred, int64_t n_matches, int32_t slots, const ts_outputs *outputs,
-                   int32_t lanes_per_match, void *workspace, int64_t workspace_bytes, void *stream);
+                   const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
+                   const ts_outputs *outputs, int32_t lanes_per_match, void *workspace, int64_t workspace_bytes,
+                   void *stream);
 
 /* One ladder whose player table is hash-sharded over the G GPUs of a node
  * (BASELINE.json configs[4]): player p is owned by GPU p % G

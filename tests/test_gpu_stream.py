@@ -173,3 +173,23 @@ def test_large_index_range(eng):
     assert r.error_count() == 0
     assert float((tab_a - tab_b).abs().max()) < TOL
     r.close()
+
+
+@pytest.mark.parametrize("window", [1, 777, 50_000, 10**9])
+def test_windows_equal_one_shot(eng, window):
+    """Micro-batch windows with carried chain tails (worker.py:18-20) give the same
+    table as one link + rate over the whole stream."""
+    dev = torch.device("cuda", 0)
+    n, u = (3_000 if window == 1 else 120_000), 2_000
+    r = eng.Rater(eng.Env(), 0)
+    gen = eng.make_gen(0xA11CE0F7, u, slots=6, mode=1, p_afk=0.05)
+    ids, meta = eng.gen_matches(gen, 0, n, dev)
+    tab_a = eng.gen_table(9, 0, u, dev)
+    tab_b = tab_a.clone()
+    pa, pb = eng.PlayerTable.ladder(tab_a, mode=1), eng.PlayerTable.ladder(tab_b, mode=1)
+    r.rate_stream_windows(pa, ids, meta, window)
+    pred = r.link_pred(ids, meta, u, pb.mode_cols)
+    r.rate_stream(pb, ids, meta, pred)
+    assert r.error_count() == 0
+    assert torch.equal(tab_a, tab_b)
+    r.close()
