@@ -145,6 +145,7 @@ class Rater(object):
         L.check(self._lib.ts_ctx_create(C.byref(prm), self.device.index or 0, C.byref(self._ctx)))
         self._ws = None
         self._vt = None
+        self._copy_stream = None
 
     def close(self):
         if self._ctx:
@@ -277,7 +278,7 @@ class Rater(object):
 
     # ------------------------------------------------------------------
     def rate_batch(self, ids, meta, table, seed=None, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6),
-                   want_outputs=True, lanes_per_match=0, table_out=None, path="auto"):
+                   want_outputs=True, lanes_per_match=0, table_out=None, path="auto", windows=None):
         """The reference-facing batch call with HOST buffers: numpy ids
         [N, P] uint32, meta [N] uint32, table [U, C, 2] float64 (NaN = NULL),
         optional seed [U, 2].  Copies in, schedules, rates, copies back.
@@ -293,25 +294,62 @@ class Rater(object):
             return torch.from_numpy(a.view(np.int32) if as_i32 else a)
 
         ids_t, meta_t, tab_t, seed_t = host(ids, True), host(meta, True), host(table), host(seed)
-        ids_d = ids_t.to(dev, non_blocking=True)
-        meta_d = meta_t.to(dev, non_blocking=True)
-        tab_d = tab_t.to(dev, non_blocking=True)
-        seed_d = seed_t.to(dev, non_blocking=True) if seed_t is not None else None
-        ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
-        n, p = ids_d.shape
-        self.reset_errors()
-        outs = self.alloc_outputs(n, p) if want_outputs else None
-        # single-pair ladders take the streaming (dataflow) path unless told otherwise
-        stream = path == "stream" or (path == "auto" and ptab.shared_col < 0 and tab_d.shape[1] == 1
+        n, p = ids_t.shape
+        stream = path == "stream" or (path == "auto" and shared_col < 0 and tab_t.shape[1] == 1
                                        and p in (6, 10) and n > 0)
-        if stream:
-            pred = self.link_pred(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
-            self.rate_stream(ptab, ids_d, meta_d, pred, outs, lanes_per_match)
+        if windows is None:
+            windows = 4 if (stream and n >= 1_000_000 and not want_outputs) else 1
+        self.reset_errors()
+        if stream and windows > 1:
+            # Pipelined ingest: the match stream is copied window by window on a side
+            # stream while the previous window is linked and rated, so the PCIe copy
+            # and the GPU work overlap (worker.py:18-20's micro-batches, in one call).
+            # Windows are consecutive ranges of the stream; chain tails and the
+            # versioned rows carry the state from one to the next.
+            cur = torch.cuda.current_stream(dev)
+            side = self._copy_stream or torch.cuda.Stream(dev)
+            self._copy_stream = side
+            ids_d = torch.empty((n, p), dtype=torch.int32, device=dev)
+            meta_d = torch.empty((n,), dtype=torch.int32, device=dev)
+            tab_d = tab_t.to(dev, non_blocking=True)
+            seed_d = seed_t.to(dev, non_blocking=True) if seed_t is not None else None
+            ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
+            last = torch.full((ptab.n_players,), -1, dtype=torch.int32, device=dev)
+            bounds = [(w * n) // windows for w in range(windows + 1)]
+            side.wait_stream(cur)
+            ready = []
+            with torch.cuda.stream(side):
+                for w in range(windows):
+                    lo, hi = bounds[w], bounds[w + 1]
+                    ids_d[lo:hi].copy_(ids_t[lo:hi], non_blocking=True)
+                    meta_d[lo:hi].copy_(meta_t[lo:hi], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(side)
+                    ready.append(ev)
+            for w in range(windows):
+                lo, hi = bounds[w], bounds[w + 1]
+                cur.wait_event(ready[w])
+                flags = (L.STREAM_LOAD if w == 0 else 0) | (L.STREAM_STORE if w == windows - 1 else 0)
+                pred = self.link_pred(ids_d[lo:hi], meta_d[lo:hi], ptab.n_players, ptab.mode_cols, seq_base=lo, last=last)
+                self.rate_stream(ptab, ids_d[lo:hi], meta_d[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags)
+            outs = None
             n_rounds = None
         else:
-            sch = self.schedule(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
-            self.rate(ptab, sch, outs, lanes_per_match)
-            n_rounds = sch.n_rounds
+            ids_d = ids_t.to(dev, non_blocking=True)
+            meta_d = meta_t.to(dev, non_blocking=True)
+            tab_d = tab_t.to(dev, non_blocking=True)
+            seed_d = seed_t.to(dev, non_blocking=True) if seed_t is not None else None
+            ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
+            outs = self.alloc_outputs(n, p) if want_outputs else None
+            if stream:
+                # single-pair ladders take the streaming (dataflow) path unless told otherwise
+                pred = self.link_pred(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
+                self.rate_stream(ptab, ids_d, meta_d, pred, outs, lanes_per_match)
+                n_rounds = None
+            else:
+                sch = self.schedule(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
+                self.rate(ptab, sch, outs, lanes_per_match)
+                n_rounds = sch.n_rounds
         bad = self.error_count()
         result = dict(n_rounds=n_rounds, errors=bad)
         if outs is not None:

@@ -193,3 +193,17 @@ def test_windows_equal_one_shot(eng, window):
     assert r.error_count() == 0
     assert torch.equal(tab_a, tab_b)
     r.close()
+
+
+def test_rate_batch_pipelined_windows(eng):
+    """Host-buffer call with the copy / compute pipeline over windows == one shot."""
+    r = eng.Rater(eng.Env(), 0)
+    n, u = 300_000, 20_000
+    gen = eng.make_gen(0xA11CE0F8, u, slots=6, mode=1)
+    ids_d, meta_d = eng.gen_matches(gen, 0, n, torch.device("cuda", 0))
+    ids_h, meta_h = ids_d.cpu().pin_memory(), meta_d.cpu().pin_memory()
+    tab_h = eng.gen_table(5, 0, u, torch.device("cuda", 0)).cpu().pin_memory()
+    a = r.rate_batch(ids_h, meta_h, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=5)
+    b = r.rate_batch(ids_h, meta_h, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=1)
+    assert np.array_equal(a["table"], b["table"]) and a["errors"] == b["errors"] == 0
+    r.close()
