@@ -110,3 +110,64 @@ extern "C" int ts_gen_table(uint64_t seed, int64_t first, int64_t count, double 
     TS_CUDA(cudaGetLastError());
     return 0;
 }
+
+// ---------------------------------------------------------------------------
+// Seed policy on the device: get_trueskill_seed (rater.py:42-62) for a whole
+// column of players.  rank_points_* are doubles with NaN = None; 0 counts as
+// absent like in the reference (rater.py:45,47).  vst[tier + 1] is the
+// reference's vst_points table (rater.py:13-27), passed in by the host so that
+// there is one source for it.  A tier outside -1..29 with no rank points raises
+// KeyError in the reference: here the seed stays NaN and bad[i] = 1.
+// ---------------------------------------------------------------------------
+namespace {
+
+struct VstTable {
+    double pts[31];
+};
+
+__global__ void __launch_bounds__(256)
+k_seed(const double *ranked, const double *blitz, const int8_t *tier, int64_t n, double unknown_sigma, VstTable vst,
+       double *seed, uint8_t *bad)
+{
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double best = nan("");
+    const double r = ranked ? ranked[i] : nan(""), b = blitz ? blitz[i] : nan("");
+    if (!isnan(r) && r != 0.0) best = r;
+    if (!isnan(b) && b != 0.0 && (isnan(best) || b > best)) best = b;
+    double mu = nan(""), sigma = nan("");
+    uint8_t flag = 0;
+    if (!isnan(best)) {
+        sigma = unknown_sigma * (2.0 / 3.0);
+        mu = best + sigma;
+    } else {
+        const int t = tier ? (int)tier[i] : 127;
+        if (t >= -1 && t <= 29) {
+            sigma = unknown_sigma;
+            mu = vst.pts[t + 1] + sigma;
+        } else {
+            flag = 1;
+        }
+    }
+    reinterpret_cast<double2 *>(seed)[i] = make_double2(mu, sigma);
+    if (bad) bad[i] = flag;
+}
+
+}  // namespace
+
+extern "C" int ts_seed_table(const double *rank_points_ranked, const double *rank_points_blitz, const int8_t *skill_tier,
+                             int64_t n_players, double unknown_player_sigma, const double vst_points[31], double *seed,
+                             uint8_t *bad, void *stream)
+{
+    if (!seed || !vst_points || n_players < 0) {
+        ts_set_error("ts_seed_table: bad argument");
+        return TS_E_ARG;
+    }
+    if (n_players == 0) return 0;
+    VstTable v;
+    for (int i = 0; i < 31; ++i) v.pts[i] = vst_points[i];
+    k_seed<<<(unsigned)((n_players + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        rank_points_ranked, rank_points_blitz, skill_tier, n_players, unknown_player_sigma, v, seed, bad);
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -251,7 +251,9 @@ class Rater(object):
     def rate_stream_windows(self, table, ids, meta, window, lanes_per_match=0):
         """The whole ladder in windows of `window` matches (worker.py:18-20's
         micro-batches): link + rate per window, chain tails and versioned rows
-        carried from window to window.  Same result as one link + rate."""
+        carried from window to window.  Same result as one link + rate.
+        (Linking window k+1 on a side stream while window k is rated was tried
+        and gives nothing: the rating kernel holds the whole register file.)"""
         n, p = ids.shape
         last = torch.full((table.n_players,), -1, dtype=torch.int32, device=ids.device)   # TS_NONE
         for lo in range(0, max(n, 1), window):
@@ -391,6 +393,19 @@ def gen_matches(gen, first, count, device):
     with torch.cuda.device(device):
         L.check(L.lib().ts_gen_matches(C.byref(gen), first, count, _ptr(ids), _ptr(meta), _stream_ptr()))
     return ids, meta
+
+
+def seed_table(vst_points, unknown_sigma, n_players, device, ranked=None, blitz=None, tier=None):
+    """get_trueskill_seed (rater.py:42-62) for whole columns on the device.
+    ranked / blitz: float64 device tensors with NaN = None; tier: int8.
+    Returns (seed [U, 2], bad [U] uint8 -- 1 where the reference raises KeyError)."""
+    seed = torch.empty((n_players, 2), dtype=torch.float64, device=device)
+    bad = torch.empty((n_players,), dtype=torch.uint8, device=device)
+    vst = (C.c_double * 31)(*[float(vst_points[t]) for t in range(-1, 30)])
+    with torch.cuda.device(device):
+        L.check(L.lib().ts_seed_table(_ptr(ranked), _ptr(blitz), _ptr(tier), n_players, float(unknown_sigma), vst,
+                                      _ptr(seed), _ptr(bad), _stream_ptr()))
+    return seed, bad
 
 
 def gen_table(seed, first, count, device):

@@ -216,6 +216,15 @@ int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_shard, int6
 int64_t ts_error_count(ts_ctx *ctx, void *stream);
 int ts_reset_errors(ts_ctx *ctx, void *stream);
 
+/* get_trueskill_seed (rater.py:42-62) for a column of players, on the device:
+ * rank points as doubles (NaN = None; 0 = absent, rater.py:45,47), skill_tier
+ * int8 (-1..29; anything else with no rank points is the reference's KeyError:
+ * seed stays NaN and bad[i] = 1).  vst_points[tier + 1] = rater.py:13-27.
+ * Any input column may be NULL (= all None); bad may be NULL. */
+int ts_seed_table(const double *rank_points_ranked, const double *rank_points_blitz, const int8_t *skill_tier,
+                  int64_t n_players, double unknown_player_sigma, const double vst_points[31], double *seed,
+                  uint8_t *bad, void *stream);
+
 /* Synthetic ladders of BASELINE.json's configs (SURVEY.md 8d "Generator"):
  * counter-based, so any window [first, first+count) can be produced on its
  * own.  No counterpart in the reference (it has no benchmark input). */

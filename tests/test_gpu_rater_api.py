@@ -113,3 +113,28 @@ def test_rate_matches_equals_sequential_port(rater):
                 assert (a is None) == (b is None)
                 if a is not None:
                     assert abs(a - b) < 1e-9
+
+
+def test_seed_policy_on_device(rater):
+    """ts_seed_table == get_trueskill_seed (rater.py:42-62), bit for bit, KeyError cases flagged."""
+    import torch
+    from analyzer_b200 import engine
+    rng = np.random.default_rng(4)
+    n = 5000
+    tier = rng.integers(-3, 33, n).astype(np.int8)
+    ranked = np.where(rng.random(n) < 0.4, rng.integers(0, 3000, n).astype(np.float64), np.nan)
+    blitz = np.where(rng.random(n) < 0.3, rng.integers(0, 3000, n).astype(np.float64), np.nan)
+    ranked[::17] = 0.0
+    dev = torch.device("cuda", 0)
+    seed, bad = engine.seed_table(rater.vst_points, rater.UNKNOWN_PLAYER_SIGMA, n, dev,
+                                  torch.from_numpy(ranked).to(dev), torch.from_numpy(blitz).to(dev),
+                                  torch.from_numpy(tier).to(dev))
+    seed, bad = seed.cpu().numpy(), bad.cpu().numpy()
+    for i in range(n):
+        r = None if np.isnan(ranked[i]) else ranked[i]
+        b = None if np.isnan(blitz[i]) else blitz[i]
+        try:
+            want = rp.seed_from_fields(r, b, int(tier[i]))
+            assert bad[i] == 0 and tuple(seed[i]) == want, (i, seed[i], want)
+        except KeyError:
+            assert bad[i] == 1 and np.isnan(seed[i]).all()
