@@ -34,6 +34,9 @@
 namespace {
 
 constexpr int kBlock = 256;
+#ifndef TS_STREAM_MIN_BLOCKS
+#define TS_STREAM_MIN_BLOCKS 2   // <= 128 registers: 2 blocks/SM; 3 (80 registers, spills) and 1 were measured slower
+#endif
 
 constexpr int kMaxShards = 16;
 
@@ -53,6 +56,7 @@ struct StreamArgs {
     const uint32_t *pred;
     uint32_t n_matches;
     uint32_t seq_base;            // stream-wide number of the first match of this window
+    uint32_t sleep_ns;            // back-off between polls of a waiting group
     ts_outputs out;
     unsigned long long *ctrl;
 };
@@ -164,7 +168,7 @@ __device__ __forceinline__ uint32_t group_sum_u32(uint32_t x, uint32_t gmask)
 // rows are spread over all GPUs; the version protocol is the only synchronisation
 // between GPUs (no inter-GPU barrier, no collective).
 template <int P, int L, bool SHARDED>
-__global__ void __launch_bounds__(kBlock) k_rate_stream(const StreamArgs a)
+__global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(const StreamArgs a)
 {
     constexpr int W = 32 / L;
     constexpr int SPL = (P + L - 1) / L;
@@ -306,7 +310,7 @@ __global__ void __launch_bounds__(kBlock) k_rate_stream(const StreamArgs a)
                     }
                     done = true;
                 } else {
-                    __nanosleep(20);
+                    __nanosleep(a.sleep_ns);
                 }
             }
         }
@@ -328,6 +332,17 @@ __global__ void __launch_bounds__(256) k_vt_store(const unsigned long long *vt, 
     unsigned long long w[4];
     ld_row(vt + i * 4, w);
     reinterpret_cast<double2 *>(table)[i] = make_double2(row_mu(w), row_sigma(w));
+}
+
+int stream_sleep_ns()
+{
+    static int ns = -1;
+    if (ns < 0) {
+        const char *e = getenv("TSRATE_STREAM_SLEEP_NS");
+        ns = e ? atoi(e) : 20;
+        if (ns < 0) ns = 0;
+    }
+    return ns;
 }
 
 int stream_blocks_per_sm_cap()
@@ -416,6 +431,7 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
     a.pred = pred;
     a.n_matches = (uint32_t)n_matches;
     a.seq_base = (uint32_t)seq_base;
+    a.sleep_ns = stream_sleep_ns();
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;
@@ -536,6 +552,7 @@ extern "C" int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_
     a.pred = pred;
     a.n_matches = (uint32_t)n_matches;
     a.seq_base = 0;
+    a.sleep_ns = stream_sleep_ns();
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;
