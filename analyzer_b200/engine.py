@@ -297,10 +297,16 @@ class Rater(object):
 
         ids_t, meta_t, tab_t, seed_t = host(ids, True), host(meta, True), host(table), host(seed)
         n, p = ids_t.shape
+        # Single-pair ladders take the streaming (dataflow) path when chains are deep
+        # (several matches per player: latency-bound, barriers hurt); sparse ladders over a
+        # table much larger than the batch are bandwidth-bound and cheaper round by round
+        # (16-byte rows, no versioned copy of the table).  Measured crossover, DESIGN.md 4.
         stream = path == "stream" or (path == "auto" and shared_col < 0 and tab_t.shape[1] == 1
-                                       and p in (6, 10) and n > 0)
+                                       and p in (6, 10) and n > 0 and n * p >= 2 * tab_t.shape[0])
         if windows is None:
-            windows = 4 if (stream and n >= 1_000_000 and not want_outputs) else 1
+            # ~1M matches per window, at most 8: enough to hide all but the last window's
+            # link + rate behind the PCIe copy of the stream
+            windows = max(1, min(8, n // 1_000_000)) if (stream and not want_outputs) else 1
         self.reset_errors()
         if stream and windows > 1:
             # Pipelined ingest: the match stream is copied window by window on a side

@@ -137,6 +137,46 @@ def cpu_rate_match_rate(ids, meta, seconds):
     return done / (time.perf_counter() - t0), done
 
 
+def object_api_rate(ids_d, meta_d, n=5000):
+    """The drop-in object API: analyzer_b200.rater.rate_matches on ORM-like object
+    graphs (the shape worker.py:176-192 hands to rate_match), against the port's
+    rate_match loop on the same graphs.  Ingest and write-back are Python."""
+    import logging
+    import numpy as np
+    from analyzer_b200 import rater as gpu_rater
+    from oracle import rater_port as rp
+    gpu_rater.logger.setLevel(logging.ERROR)
+    ids = ids_d[:n].cpu().numpy().view(np.uint32) % 3000        # 3000 players: chains inside the batch
+    meta = meta_d[:n].cpu().numpy().view(np.uint32)
+    for row in ids:                                              # keep players distinct inside a match
+        seen = set()
+        for k in range(len(row)):
+            while int(row[k]) in seen:
+                row[k] = (int(row[k]) + 1) % 3000
+            seen.add(int(row[k]))
+
+    def graphs():
+        players = {i: rp.new_player(skill_tier=i % 30) for i in range(3000)}
+        return rp.matches_from_columns(ids, meta, players)
+
+    gpu_rater.rate_matches(graphs()[:64])                        # warm-up (context, first launches)
+    g = graphs()
+    t0 = time.perf_counter()
+    gpu_rater.rate_matches(g)
+    dt_gpu = time.perf_counter() - t0
+    g2 = graphs()[:400]
+    t0 = time.perf_counter()
+    for m in g2:
+        rp.rate_match(m)
+    dt_cpu = (time.perf_counter() - t0) / len(g2)
+    # same answer on the shared prefix
+    err = max(abs(a.participants[0].trueskill_mu - b.participants[0].trueskill_mu)
+              for a, b in zip(g[:400], g2) if b.participants[0].trueskill_mu is not None)
+    return {"rate_matches_per_s": n / dt_gpu, "batch": n, "reference_loop_per_s": 1.0 / dt_cpu,
+            "note": "faithful shared + queue path (rounds), %d-match batch of object graphs, 3000 players; "
+                    "Python ingest + write-back included" % n, "check_max_abs_diff": err}
+
+
 def cpu_c_baselines(ids, meta, table, n_players):
     """the closed form in C, fp64, 1 core sequential and
     round-parallel OpenMP on all host cores (reported, not the target)."""
@@ -422,6 +462,11 @@ def run_b200(a):
     }
     if e2e:
         line["e2e"] = e2e
+    if world == 1 and not a.no_cpu_baseline:
+        try:
+            line["object_api"] = object_api_rate(ids_d, meta_d)
+        except Exception as exc:
+            line["object_api"] = {"error": repr(exc)}
     if world == 1 and not a.no_cpu_baseline:
         sample = min(n, 200_000)
         ids = ids_d[:sample].cpu().numpy().view(np.uint32)
