@@ -221,6 +221,164 @@ k_radix_scatter(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n,
     }
 }
 
+// ---------------------------------------------------------------------------
+// Single-sweep form of a radix pass (decoupled look-back, in the manner of
+// Merrill & Garland's scan and Adinets & Merrill's "onesweep" sort): the digit
+// totals of all passes are counted once up front (keys do not change from pass to
+// pass), and each scatter block publishes its per-digit counts in a status row and
+// looks back over the rows of earlier tiles for its offsets.  No per-pass histogram
+// kernel, no scan kernels, keys are read once per pass.  Tile numbers are handed
+// out by an atomic ticket so that every tile a block waits for has already started.
+// Status word: bit 31 = inclusive prefix available, bit 30 = tile count available,
+// low 30 bits the value (so this form needs n < 2^30).
+// ---------------------------------------------------------------------------
+constexpr uint32_t kStPrefix = 0x80000000u, kStCount = 0x40000000u, kStMask = 0x3FFFFFFFu;
+constexpr int kMaxPasses = 4;
+constexpr int kTotalsWords = kMaxPasses * 256 + 64;    // digit bases of every pass + the ticket
+
+__global__ void __launch_bounds__(kSortBlock)
+k_radix_hist_all(KeySrc src, uint32_t n, int passes, uint32_t *ghist)
+{
+    __shared__ uint32_t h[kMaxPasses][256];
+    for (int i = threadIdx.x; i < kMaxPasses * 256; i += kSortBlock) (&h[0][0])[i] = 0;
+    __syncthreads();
+    for (uint32_t idx = blockIdx.x * kSortBlock + threadIdx.x; idx < n; idx += gridDim.x * kSortBlock) {
+        const uint32_t k = load_key(src, idx);
+        for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(k >> (8 * p)) & 255u], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * 256; i += kSortBlock) {
+        const uint32_t c = (&h[0][0])[i];
+        if (c) atomicAdd(&ghist[i], c);
+    }
+}
+
+// exclusive scan of each pass's 256 digit totals (one block, thread = digit)
+__global__ void __launch_bounds__(256) k_radix_scan_all(uint32_t *ghist, int passes)
+{
+    __shared__ uint32_t s[256];
+    for (int p = 0; p < passes; ++p) {
+        s[threadIdx.x] = ghist[p * 256 + threadIdx.x];
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t run = 0;
+            for (int d = 0; d < 256; ++d) { uint32_t c = s[d]; s[d] = run; run += c; }
+        }
+        __syncthreads();
+        ghist[p * 256 + threadIdx.x] = s[threadIdx.x];
+        __syncthreads();
+    }
+}
+
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(uint32_t *p, uint32_t v)
+{
+    asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(kSortBlock, 4)
+k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n, int shift,
+                 const uint32_t *digit_base, uint32_t *status, uint32_t *ticket, uint32_t *keys_out,
+                 uint32_t *vals_out)
+{
+    __shared__ uint32_t wcount[kWarps][256];
+    __shared__ uint32_t gbase[256];
+    __shared__ uint32_t warp_tot[kWarps];
+    __shared__ uint32_t skey[kSortTile];
+    __shared__ uint32_t sval[kSortTile];
+    __shared__ uint32_t s_tile;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    for (int i = threadIdx.x; i < kWarps * 256; i += kSortBlock) (&wcount[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t tile_base = tile * kSortTile;
+    const uint32_t wbase = tile_base + warp * (kSortItems * 32);
+    uint32_t key[kSortItems], off[kSortItems];
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        uint32_t idx = wbase + k * 32 + lane;
+        key[k] = idx < n ? load_key(src, idx) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        uint32_t idx = wbase + k * 32 + lane;
+        bool ok = idx < n;
+        const uint32_t d = (key[k] >> shift) & 255u;
+        uint32_t peers = __ballot_sync(0xFFFFFFFFu, ok);
+        peers = ok ? peers : ~peers;
+#pragma unroll
+        for (int b = 0; b < 8; ++b) {
+            const bool bit = (d >> b) & 1u;
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, bit);
+            peers &= bit ? bal : ~bal;
+        }
+        int leader = __ffs(peers) - 1;
+        uint32_t prev = 0;
+        if (ok && lane == leader) prev = atomicAdd(&wcount[warp][d], (uint32_t)__popc(peers));
+        off[k] = __shfl_sync(0xFFFFFFFFu, prev, leader) + __popc(peers & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+    {
+        const uint32_t d = threadIdx.x;
+        uint32_t run = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) {
+            uint32_t c = wcount[w][d];
+            wcount[w][d] = run;
+            run += c;
+        }
+        // publish this tile's count of digit d, then find the tiles before it
+        uint32_t *row = status + (size_t)tile * 256;
+        st_relaxed_u32(row + d, run | (tile == 0 ? kStPrefix : kStCount));
+        uint32_t incl = run;   // exclusive scan of the 256 digit totals across the block (tile-local starts)
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        uint32_t before = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) before += (w < warp) ? warp_tot[w] : 0u;
+        const uint32_t dstart = before + incl - run;
+        uint32_t excl = 0;
+        for (uint32_t j = tile; j > 0;) {
+            const uint32_t v = ld_relaxed_u32(status + (size_t)(j - 1) * 256 + d);
+            if (v & kStPrefix) { excl += v & kStMask; break; }
+            if (v & kStCount) { excl += v & kStMask; --j; }
+        }
+        if (tile > 0) st_relaxed_u32(row + d, (excl + run) | kStPrefix);
+        gbase[d] = __ldg(digit_base + d) + excl - dstart;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) wcount[w][d] += dstart;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        uint32_t idx = wbase + k * 32 + lane;
+        if (idx < n) {
+            uint32_t pos = wcount[warp][(key[k] >> shift) & 255u] + off[k];
+            skey[pos] = key[k];
+            sval[pos] = ident_vals ? idx : __ldg(vals_in + idx);
+        }
+    }
+    __syncthreads();
+    const uint32_t cnt = min((uint32_t)kSortTile, n - tile_base);
+    for (uint32_t i = threadIdx.x; i < cnt; i += kSortBlock) {
+        uint32_t k = skey[i];
+        uint32_t pos = gbase[(k >> shift) & 255u] + i;
+        keys_out[pos] = k;
+        vals_out[pos] = sval[i];
+    }
+}
+
 // ---- chain linking --------------------------------------------------------
 // Sorted pairs (key = player, val = slot index i = m*P + s).  Runs of equal key
 // list one player's slots in match order.  The first entry of a (player, match)
@@ -468,7 +626,7 @@ Workspace carve(char *base, int64_t n_matches, int32_t slots)
     auto take = [&](size_t bytes) { char *p = base ? base + off : nullptr; off += align_up(bytes); return (uint32_t *)p; };
     for (int i = 0; i < 2; ++i) { w.keys[i] = take(np * 4); w.vals[i] = take(np * 4); }
     w.hist = take((n_blocks * 256 + 256) * 4);
-    w.totals = take(256 * 4);
+    w.totals = take(kTotalsWords * 4);
     w.succ = take(np * 4);
     w.pending = take((size_t)n_matches * 4);
     w.queue = take((size_t)n_matches * 4);
@@ -497,7 +655,7 @@ int bits_for(uint64_t max_value)
 // LSD radix sort of n (key, val) pairs on the low `bits` bits.  Pass 0 reads
 // `src` (with identity values); results ping-pong between the two buffers.
 // Returns the index of the buffer holding the result (or <0).
-int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream)
+int radix_sort_3kernel(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream)
 {
     const uint32_t n_blocks = (n + kSortTile - 1) / kSortTile;
     const int passes = (bits + 7) / 8;
@@ -513,6 +671,47 @@ int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStrea
         k_radix_scan_totals<<<1, 256, 0, stream>>>(w.totals);
         k_radix_scatter<<<n_blocks, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n, p * 8, w.hist,
                                                              w.totals, n_blocks, w.keys[dst], w.vals[dst]);
+        cur = dst;
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return ts_cuda_fail(e, "radix sort launch");
+    return cur;
+}
+
+int radix_onesweep_enabled()
+{
+    static int on = -1;
+    if (on < 0) {
+        const char *e = getenv("TSRATE_ONESWEEP");
+        on = e ? atoi(e) : 1;
+    }
+    return on;
+}
+
+// LSD radix sort of n (key, val) pairs on the low `bits` bits.  Pass 0 reads
+// `src` (with identity values); results ping-pong between the two buffers.
+// Returns the index of the buffer holding the result (or <0).
+int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream, int sm_count)
+{
+    const int passes = (bits + 7) / 8;
+    if (n >= (1u << 30) || passes > kMaxPasses || !radix_onesweep_enabled())
+        return radix_sort_3kernel(src0, n, bits, w, stream);
+    const uint32_t n_tiles = (n + kSortTile - 1) / kSortTile;
+    uint32_t *ghist = w.totals, *ticket = w.totals + kMaxPasses * 256;
+    if (cudaMemsetAsync(w.totals, 0, kTotalsWords * 4, stream) != cudaSuccess) return ts_cuda_fail(cudaGetLastError(), "memset");
+    k_radix_hist_all<<<sm_count * 8, kSortBlock, 0, stream>>>(src0, n, passes, ghist);
+    k_radix_scan_all<<<1, 256, 0, stream>>>(ghist, passes);
+    int cur = -1;
+    for (int p = 0; p < passes; ++p) {
+        KeySrc src = src0;
+        const uint32_t *vals_in = nullptr;
+        if (p > 0) { src.keys = w.keys[cur]; src.from_ids = 0; vals_in = w.vals[cur]; }
+        int dst = cur < 0 ? 0 : ((cur + 1) & 1);
+        if (cudaMemsetAsync(w.hist, 0, (size_t)n_tiles * 256 * 4, stream) != cudaSuccess ||
+            cudaMemsetAsync(ticket, 0, 4, stream) != cudaSuccess)
+            return ts_cuda_fail(cudaGetLastError(), "memset");
+        k_radix_onesweep<<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n, p * 8, ghist + p * 256,
+                                                             w.hist, ticket, w.keys[dst], w.vals[dst]);
         cur = dst;
     }
     cudaError_t e = cudaGetLastError();
@@ -589,7 +788,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
-    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s);
+    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
     if (buf < 0) return buf;
 
     // 2. link chains
@@ -638,7 +837,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     rsrc.sentinel = 0;
     rsrc.from_ids = 0;
     rsrc.slots_magic = 0ull;   // unused: keys are read as they are
-    buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s);
+    buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s, ctx->sm_count);
     if (buf < 0) return buf;
     TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
     if (ids_sorted && meta_sorted) {
@@ -657,7 +856,7 @@ extern "C" int64_t ts_link_workspace_bytes(int64_t n_matches, int32_t slots)
     if (n_matches < 0 || slots < 2 || slots > TS_MAX_SLOTS) return TS_E_ARG;
     size_t np = (size_t)n_matches * slots;
     size_t n_blocks = (np + kSortTile - 1) / kSortTile;
-    return (int64_t)(4 * align_up(np * 4) + align_up((n_blocks * 256 + 256) * 4) + align_up(256 * 4));
+    return (int64_t)(4 * align_up(np * 4) + align_up((n_blocks * 256 + 256) * 4) + align_up(kTotalsWords * 4));
 }
 
 extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
@@ -692,7 +891,7 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
         auto take = [&](size_t bytes) { char *p = base + off; off += align_up(bytes); return (uint32_t *)p; };
         for (int i = 0; i < 2; ++i) { w.keys[i] = take((size_t)np * 4); w.vals[i] = take((size_t)np * 4); }
         w.hist = take((n_blocks * 256 + 256) * 4);
-        w.totals = take(256 * 4);
+        w.totals = take(kTotalsWords * 4);
         w.succ = w.pending = w.queue = nullptr;
         w.bytes = off;
     }
@@ -704,7 +903,7 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
-    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s);
+    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
     if (buf < 0) return buf;
     // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2.
     // Every pass re-reads the sorted pairs, so this only pays for a handful of passes; a window
