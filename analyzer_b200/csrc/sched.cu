@@ -566,29 +566,47 @@ __global__ void __launch_bounds__(256)
 k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long long slots_magic, uint32_t sentinel,
        uint32_t v_lo, uint32_t v_hi, uint32_t seq_base, const uint32_t *last, uint32_t *pred)
 {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    // all four loads are issued up front (coalesced; the i-1 ones hit L1): one
-    // memory latency per thread instead of a chain of three
-    const uint32_t v = __ldcs(vals + i), k = __ldcs(keys + i);
-    const uint32_t kp = i > 0 ? __ldcs(keys + i - 1) : ~k, vp = i > 0 ? __ldcs(vals + i - 1) : 0u;
-    if (v < v_lo || v >= v_hi || k >= sentinel) return;   // other pass / empty slot / gated match
-    const uint32_t m = (uint32_t)__umul64hi((unsigned long long)v, slots_magic);
-    uint32_t pm = TS_NONE;      // local index of the previous match in this window
-    if (kp == k) {
-        pm = (uint32_t)__umul64hi((unsigned long long)vp, slots_magic);
-        if (pm == m) {          // the player is listed twice in this match: walk back to a different match
-            pm = TS_NONE;
-            for (uint32_t j = i - 1; j > 0 && __ldcs(keys + j - 1) == k; --j) {
-                uint32_t mj = (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + j - 1), slots_magic);
-                if (mj != m) { pm = mj; break; }
-            }
+    // four consecutive sorted entries per thread: two 16-byte streaming loads plus the
+    // entry just before them, all issued up front
+    const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
+    if (i0 >= n) return;
+    uint32_t k[5], v[5];
+    if (i0 + 4 <= n) {
+        const uint4 kk = __ldcs(reinterpret_cast<const uint4 *>(keys + i0));
+        const uint4 vv = __ldcs(reinterpret_cast<const uint4 *>(vals + i0));
+        k[1] = kk.x; k[2] = kk.y; k[3] = kk.z; k[4] = kk.w;
+        v[1] = vv.x; v[2] = vv.y; v[3] = vv.z; v[4] = vv.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const bool ok = i0 + j < n;
+            k[j + 1] = ok ? __ldcs(keys + i0 + j) : 0xFFFFFFFFu;
+            v[j + 1] = ok ? __ldcs(vals + i0 + j) : 0u;
         }
     }
-    // stream-wide match numbers; a player's first match of this window continues the
-    // chain at the tail carried over from earlier windows
-    pm = pm != TS_NONE ? seq_base + pm : (last ? __ldg(last + k) : TS_NONE);
-    pred[v] = pm;
+    k[0] = i0 > 0 ? __ldcs(keys + i0 - 1) : ~k[1];
+    v[0] = i0 > 0 ? __ldcs(vals + i0 - 1) : 0u;
+#pragma unroll
+    for (int j = 1; j <= 4; ++j) {
+        const uint32_t i = i0 + j - 1;
+        if (i >= n || v[j] < v_lo || v[j] >= v_hi || k[j] >= sentinel) continue;   // other pass / empty slot / gated match
+        const uint32_t m = (uint32_t)__umul64hi((unsigned long long)v[j], slots_magic);
+        uint32_t pm = TS_NONE;      // local index of the previous match in this window
+        if (k[j - 1] == k[j]) {
+            pm = (uint32_t)__umul64hi((unsigned long long)v[j - 1], slots_magic);
+            if (pm == m) {          // the player is listed twice in this match: walk back to a different match
+                pm = TS_NONE;
+                for (uint32_t q = i - 1; q > 0 && __ldcs(keys + q - 1) == k[j]; --q) {
+                    uint32_t mq = (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + q - 1), slots_magic);
+                    if (mq != m) { pm = mq; break; }
+                }
+            }
+        }
+        // stream-wide match numbers; a player's first match of this window continues the
+        // chain at the tail carried over from earlier windows
+        pm = pm != TS_NONE ? seq_base + pm : (last ? __ldg(last + k[j]) : TS_NONE);
+        pred[v[j]] = pm;
+    }
 }
 
 // after all pred passes: the last slot of every player's run becomes the carried tail
@@ -912,7 +930,7 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
     if (((uint64_t)np + range - 1) / range > 8) range = 0xFFFFFFFFu;
     for (uint64_t lo = 0; lo < np; lo += range) {
         uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);
-        k_pred<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, src.slots_magic, (uint32_t)n_players,
+        k_pred<<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, src.slots_magic, (uint32_t)n_players,
                                                 (uint32_t)lo, hi, (uint32_t)seq_base, last, pred);
     }
     if (last)
