@@ -28,6 +28,9 @@
 
 namespace {
 
+#ifndef TS_SORT_MIN_BLOCKS
+#define TS_SORT_MIN_BLOCKS 5   // 48 registers, 5 x 42 KB shared: measured 2.75 ms link vs 2.94 (4) and 3.32 (3)
+#endif
 constexpr int kSortBlock = 256;
 constexpr int kSortItems = 16;
 constexpr int kSortTile = kSortBlock * kSortItems;   // 4096 elements per block
@@ -281,7 +284,7 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t *p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(kSortBlock, 4)
+__global__ void __launch_bounds__(kSortBlock, TS_SORT_MIN_BLOCKS)
 k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n, int shift,
                  const uint32_t *digit_base, uint32_t *status, uint32_t *ticket, uint32_t *keys_out,
                  uint32_t *vals_out)
