@@ -32,7 +32,10 @@ namespace {
 #define TS_SORT_MIN_BLOCKS 5   // 48 registers, 5 x 42 KB shared: measured 2.75 ms link vs 2.94 (4) and 3.32 (3)
 #endif
 constexpr int kSortBlock = 256;
-constexpr int kSortItems = 16;
+#ifndef TS_SORT_ITEMS
+#define TS_SORT_ITEMS 16
+#endif
+constexpr int kSortItems = TS_SORT_ITEMS;
 constexpr int kSortTile = kSortBlock * kSortItems;   // 4096 elements per block
 constexpr int kWarps = kSortBlock / 32;
 

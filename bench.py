@@ -429,8 +429,10 @@ def run_b200(a):
     passes_p = (max(1, u.bit_length()) + 7) // 8
     passes_r = (max(1, n_rounds.bit_length()) + 7) // 8
     pred_passes = -(-(n * p) // (16 << 20))
-    launches = {"stream": 4 * passes_p + pred_passes + 3,      # sort, pred passes, vt load, rate_stream, vt store
-                "rounds": 4 * passes_p + 2 + 1 + 1 + 4 * passes_r + 1 + 1}   # sort, link+init, frontier, offsets, sort, permute, rate
+    # kernels of this library per step (memsets / copies are not kernels): the sort is
+    # 1 histogram + 1 scan + one single-sweep kernel per pass
+    launches = {"stream": (2 + passes_p) + pred_passes + 3,                 # sort, pred passes, rows load, rate_stream, rows store
+                "rounds": (2 + passes_p) + 2 + 1 + 1 + (2 + passes_r) + 1 + 1}   # sort, link+init, frontier, offsets, sort, permute, rate
     kernel = "k_rate_stream" if a.path == "stream" else "k_rate"
     line = {
         "metric": METRIC, "value": n * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
