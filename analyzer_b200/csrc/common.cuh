@@ -19,8 +19,9 @@ struct ts_ctx {
 };
 
 // Control words (device): word 0 barrier counter, 2 error count, 3 queue tail,
-// 4 tail snapshot, 8..10 rotating per-level words of the frontier sweep.
-enum { CTRL_ARRIVE = 0, CTRL_ERRORS = 2, CTRL_TAIL = 3, CTRL_LEVEL = 8, CTRL_WORDS = 16 };
+// 4 tail snapshot, 5 stall flag of the streaming kernel, 8..10 rotating per-level
+// words of the frontier sweep.
+enum { CTRL_ARRIVE = 0, CTRL_ERRORS = 2, CTRL_TAIL = 3, CTRL_STALLED = 5, CTRL_LEVEL = 8, CTRL_WORDS = 16 };
 constexpr size_t TS_CTRL_BYTES = CTRL_WORDS * 8;
 
 void ts_set_error(const char *fmt, ...);

@@ -57,6 +57,7 @@ struct StreamArgs {
     uint32_t n_matches;
     uint32_t seq_base;            // stream-wide number of the first match of this window
     uint32_t sleep_ns;            // back-off between polls of a waiting group
+    uint32_t max_spins;           // watchdog: fruitless polls before a warp declares the stream stalled
     ts_outputs out;
     unsigned long long *ctrl;
 };
@@ -227,8 +228,16 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
         }
         bool done = !live;
         // warp-uniform wait loop: a group that finds all its rows at the expected
-        // version rates its match inside the iteration
+        // version rates its match inside the iteration.  Watchdog: links that can never
+        // be satisfied (a pred array that does not belong to this stream) must not hang
+        // the GPU -- after max_spins (2^24) fruitless polls (tens of seconds; a legitimate wait is
+        // milliseconds) a warp raises the stall flag, and every warp that sees it gives up.
+        uint32_t spins = 0;
         while (!__all_sync(0xFFFFFFFFu, done)) {
+            if ((++spins & 0x3FFu) == 0u) {
+                if (spins >= a.max_spins && wl == 0) atomicExch(&a.ctrl[CTRL_STALLED], 1ull);
+                if (ld_relaxed_u64(&a.ctrl[CTRL_STALLED]) != 0ull) return;
+            }
             if (!done) {
                 bool ready = true;
                 unsigned long long w[SPL][4];
@@ -345,6 +354,13 @@ int stream_sleep_ns()
     return ns;
 }
 
+int stream_max_spins()
+{
+    const char *e = getenv("TSRATE_STREAM_MAX_SPINS");     // read every call: tests lower it
+    long v = e ? atol(e) : (1l << 24);
+    return (int)(v < 1024 ? 1024 : v);
+}
+
 int stream_blocks_per_sm_cap()
 {
     static int cap = -1;
@@ -389,6 +405,15 @@ int dispatch_l(ts_ctx *ctx, const StreamArgs &a, int lanes, cudaStream_t s)
 
 extern "C" int64_t ts_rate_stream_workspace_bytes(int64_t n_players) { return n_players < 0 ? TS_E_ARG : n_players * 32; }
 
+extern "C" int ts_stream_stalled(ts_ctx *ctx, void *stream)
+{
+    if (!ctx) return TS_E_ARG;
+    unsigned long long v = 0;
+    TS_CUDA(cudaMemcpyAsync(&v, ctx->d_ctrl + CTRL_STALLED, sizeof v, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    TS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    return v != 0ull ? 1 : 0;
+}
+
 extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
                               const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
                               const ts_outputs *outputs, int32_t lanes_per_match, void *workspace,
@@ -432,6 +457,7 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
     a.n_matches = (uint32_t)n_matches;
     a.seq_base = (uint32_t)seq_base;
     a.sleep_ns = stream_sleep_ns();
+    a.max_spins = stream_max_spins();
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;
@@ -440,6 +466,7 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
     int lanes = lanes_per_match ? lanes_per_match : 2;
     a.n_shards = 1; a.shard_shift = 0; a.rank = 0;
     for (int i = 0; i < kMaxShards; ++i) a.shards[i] = nullptr;
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
     int rc = 0;
     if (n_matches > 0) rc = slots == 6 ? dispatch_l<6, false>(ctx, a, lanes, s) : dispatch_l<10, false>(ctx, a, lanes, s);
     if (rc) return rc;
@@ -553,6 +580,7 @@ extern "C" int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_
     a.n_matches = (uint32_t)n_matches;
     a.seq_base = 0;
     a.sleep_ns = stream_sleep_ns();
+    a.max_spins = stream_max_spins();
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;
@@ -563,6 +591,7 @@ extern "C" int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_
     for (int i = 0; i < kMaxShards; ++i) a.shards[i] = i < n_shards ? (unsigned long long *)vt_shards[i] : nullptr;
     for (int i = 0; i < n_shards; ++i)
         if (!a.shards[i]) { ts_set_error("ts_rate_stream_sharded: shard %d not mapped", i); return TS_E_ARG; }
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
     int lanes = lanes_per_match ? lanes_per_match : 2;
     return slots == 6 ? dispatch_l<6, true>(ctx, a, lanes, s) : dispatch_l<10, true>(ctx, a, lanes, s);
 }

@@ -263,6 +263,8 @@ class Rater(object):
             self.rate_stream(table, ids[lo:hi], meta[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags)
 
     def error_count(self):
+        if L.check(self._lib.ts_stream_stalled(self._ctx, _stream_ptr())):
+            raise L.TsError("ts_rate_stream gave up: the links (pred) do not belong to the stream they were given with")
         return L.check(self._lib.ts_error_count(self._ctx, _stream_ptr()))
 
     def reset_errors(self):

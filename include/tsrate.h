@@ -182,6 +182,11 @@ int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t
                  int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last, uint32_t *pred,
                  void *workspace, int64_t workspace_bytes, void *stream);
 int64_t ts_rate_stream_workspace_bytes(int64_t n_players);
+/* 1 if the last ts_rate_stream / ts_rate_stream_sharded on this context gave up
+ * because some match's links were never satisfied (pred does not belong to the
+ * stream it was given with): the table is then unusable.  A watchdog inside the
+ * kernel, so that bad links cannot hang the GPU.  Synchronises the stream. */
+int ts_stream_stalled(ts_ctx *ctx, void *stream);
 int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
                    const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
                    const ts_outputs *outputs, int32_t lanes_per_match, void *workspace, int64_t workspace_bytes,

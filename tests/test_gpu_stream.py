@@ -207,3 +207,28 @@ def test_rate_batch_pipelined_windows(eng):
     b = r.rate_batch(ids_h, meta_h, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=1)
     assert np.array_equal(a["table"], b["table"]) and a["errors"] == b["errors"] == 0
     r.close()
+
+
+def test_watchdog_on_unsatisfiable_links(eng, monkeypatch):
+    """pred from a different stream can never be satisfied: the kernel must give up
+    (not hang the GPU) and the host must be told."""
+    from analyzer_b200._lib import TsError
+    monkeypatch.setenv("TSRATE_STREAM_MAX_SPINS", "4096")
+    dev = torch.device("cuda", 0)
+    r = eng.Rater(eng.Env(), 0)
+    n, u = 4000, 500
+    gen = eng.make_gen(11, u, slots=6, mode=1)
+    ids, meta = eng.gen_matches(gen, 0, n, dev)
+    tab = eng.gen_table(11, 0, u, dev)
+    pt = eng.PlayerTable.ladder(tab, mode=1)
+    pred = torch.full_like(ids, 123456)              # a match that is not in this stream
+    r.rate_stream(pt, ids, meta, pred)
+    with pytest.raises(TsError, match="gave up"):
+        r.error_count()
+    # the context recovers: a proper run afterwards is fine
+    monkeypatch.delenv("TSRATE_STREAM_MAX_SPINS")
+    tab2 = eng.gen_table(11, 0, u, dev)
+    pt2 = eng.PlayerTable.ladder(tab2, mode=1)
+    r.rate_stream(pt2, ids, meta, r.link_pred(ids, meta, u, pt2.mode_cols))
+    assert r.error_count() == 0
+    r.close()
