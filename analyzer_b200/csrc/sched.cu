@@ -704,12 +704,8 @@ int radix_sort_3kernel(const KeySrc &src0, uint32_t n, int bits, Workspace &w, c
 
 int radix_onesweep_enabled()
 {
-    static int on = -1;
-    if (on < 0) {
-        const char *e = getenv("TSRATE_ONESWEEP");
-        on = e ? atoi(e) : 1;
-    }
-    return on;
+    const char *e = getenv("TSRATE_ONESWEEP");   // read every call: tests switch it
+    return e ? atoi(e) : 1;
 }
 
 // LSD radix sort of n (key, val) pairs on the low `bits` bits.  Pass 0 reads

@@ -212,14 +212,15 @@ class Rater(object):
                 _ptr(sch.round_offsets), _ptr(sch.info), sch.n_matches, sch.slots, C.byref(out),
                 int(lanes_per_match), _stream_ptr()))
 
-    def link_pred(self, ids, meta, n_players, mode_cols, seq_base=0, last=None):
+    def link_pred(self, ids, meta, n_players, mode_cols, seq_base=0, last=None, out=None):
         """First half of the scheduler only: pred[N, P] (stream-wide number of the
         previous rated match of each slot's player) for the streaming rating
         kernel.  Windows: seq_base = matches in earlier windows, last = int32
         [n_players] device tensor of carried chain tails (updated in place)."""
         assert ids.is_cuda and ids.is_contiguous() and meta.is_contiguous()
         n, p = ids.shape
-        pred = torch.empty_like(ids)
+        pred = out if out is not None else torch.empty_like(ids)
+        assert pred.shape == ids.shape and pred.is_contiguous()
         nbytes = L.check(self._lib.ts_link_workspace_bytes(n, p))
         ws = self._workspace(nbytes)
         cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
@@ -227,6 +228,23 @@ class Rater(object):
             L.check(self._lib.ts_link_pred(self._ctx, _ptr(ids), _ptr(meta), n, p, int(n_players),
                                            (C.c_int8 * 16)(*cols), int(seq_base), _ptr(last), _ptr(pred), _ptr(ws),
                                            ws.numel(), _stream_ptr()))
+        return pred
+
+    def link_pred_windows(self, ids, meta, n_players, mode_cols, window=None):
+        """pred for a long stream, linked window by window with carried chain tails:
+        same result as one link_pred call, but the scatter of every window stays
+        inside L2 (a single pass over more than ~128 Mi slot entries read-modify-
+        writes every sector) and the sort workspace is that of one window."""
+        n, p = ids.shape
+        if window is None:
+            window = max(1, (60 << 20) // p)          # ~60 Mi slot entries per window
+        if n <= window:
+            return self.link_pred(ids, meta, n_players, mode_cols)
+        pred = torch.empty_like(ids)
+        last = torch.full((n_players,), -1, dtype=torch.int32, device=ids.device)   # TS_NONE
+        for lo in range(0, n, window):
+            hi = min(n, lo + window)
+            self.link_pred(ids[lo:hi], meta[lo:hi], n_players, mode_cols, seq_base=lo, last=last, out=pred[lo:hi])
         return pred
 
     def rate_stream(self, table, ids, meta, pred, outputs=None, lanes_per_match=0, seq_base=0,

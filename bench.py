@@ -331,7 +331,7 @@ def run_b200(a):
         e0, e1, e2 = ev(), ev(), ev()
         e0.record()
         if path == "stream":
-            pred = rater.link_pred(ids_d, meta_d, u, ptab.mode_cols)
+            pred = rater.link_pred_windows(ids_d, meta_d, u, ptab.mode_cols)
             e1.record()
             rater.rate_stream(ptab, ids_d, meta_d, pred, None, a.lanes)
         else:

@@ -232,3 +232,24 @@ def test_watchdog_on_unsatisfiable_links(eng, monkeypatch):
     r.rate_stream(pt2, ids, meta, r.link_pred(ids, meta, u, pt2.mode_cols))
     assert r.error_count() == 0
     r.close()
+
+
+def test_link_windows_and_sort_variants_bit_exact(eng, monkeypatch):
+    """pred from windowed linking == one call; the 3-kernel radix passes (fallback for
+    2^30 and more slot entries) == the single-sweep passes."""
+    dev = torch.device("cuda", 0)
+    r = eng.Rater(eng.Env(), 0)
+    n, u = 400_000, 30_000
+    gen = eng.make_gen(0xA11CE0F9, u, slots=10, mode=1, p_afk=0.05, zipf=True)
+    ids, meta = eng.gen_matches(gen, 0, n, dev)
+    cols = [-1, 0]
+    one = r.link_pred(ids, meta, u, cols)
+    win = r.link_pred_windows(ids, meta, u, cols, window=70_001)
+    assert torch.equal(one, win)
+    sch_a = r.schedule(ids, meta, u, cols)
+    monkeypatch.setenv("TSRATE_ONESWEEP", "0")
+    three = r.link_pred(ids, meta, u, cols)
+    sch_b = r.schedule(ids, meta, u, cols)
+    assert torch.equal(one, three)
+    assert torch.equal(sch_a.order, sch_b.order) and torch.equal(sch_a.round, sch_b.round)
+    r.close()
