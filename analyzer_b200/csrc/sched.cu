@@ -925,6 +925,8 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
     if (buf < 0) return buf;
+    // slots that take no part (empty, gated match) read TS_NONE: the output is fully defined
+    TS_CUDA(cudaMemsetAsync(pred, 0xFF, (size_t)np * 4, s));
     // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2.
     // Every pass re-reads the sorted pairs, so this only pays for a handful of passes; a window
     // too large for that (more than 128 Mi slot entries) takes one pass and the read-modify-writes.

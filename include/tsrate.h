@@ -159,8 +159,8 @@ int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_sorted,
  * (table.row_pairs == 1, shared_col == -1): no rounds, no barriers.
  * ts_link_pred does the first half of the scheduler only -- radix sort by
  * player id and chain linking -- and writes pred[N][P]: for every slot the
- * stream-wide number of that player's previous rated match (TS_NONE if none;
- * undefined for empty slots and gated matches).  ts_rate_stream then rates
+ * stream-wide number of that player's previous rated match (TS_NONE if none,
+ * and for empty slots and gated matches).  ts_rate_stream then rates
  * the matches in stream order (worker.py:192), each match waiting until its
  * players' rows carry the version pred names.  Results are identical to
  * ts_schedule + ts_rate.  ids / meta are in ORIGINAL order; outputs (quality,
