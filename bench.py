@@ -416,6 +416,7 @@ def run_b200(a):
     peak, peak_src = hbm_peak()
     b_rate = rate_bytes_per_match(p, 1)
     achieved = b_rate * n / (ms_rate * 1e-3) / 1e9
+    kernel = "k_rate_stream" if a.path == "stream" else "k_rate"
     traffic = None
     tp = os.path.join(ROOT, "profiles", "rate_kernel_traffic.json")
     if os.path.exists(tp):
@@ -433,7 +434,6 @@ def run_b200(a):
     # 1 histogram + 1 scan + one single-sweep kernel per pass
     launches = {"stream": (2 + passes_p) + pred_passes + 3,                 # sort, pred passes, rows load, rate_stream, rows store
                 "rounds": (2 + passes_p) + 2 + 1 + 1 + (2 + passes_r) + 1 + 1}   # sort, link+init, frontier, offsets, sort, permute, rate
-    kernel = "k_rate_stream" if a.path == "stream" else "k_rate"
     line = {
         "metric": METRIC, "value": n * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True,
