@@ -28,7 +28,7 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_static", "ts_schedule_static_max_slot_entries",
            "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream",
            "ts_stream_stalled",
-           "ts_seed_table", "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_rate_stream_sharded"]
+           "ts_seed_table", "ts_link_pred_sharded", "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_rate_stream_sharded"]
 
 
 class TsParams(C.Structure):
@@ -120,6 +120,9 @@ def lib():
         L.ts_rate_stream.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_int64, C.c_int32, C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32,
                                      C.c_void_p, C.c_int64, C.c_void_p]
+        L.ts_link_pred_sharded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
+                                           C.POINTER(C.c_int8), C.c_int64, C.c_void_p, C.c_void_p, C.c_int32,
+                                           C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]
         L.ts_shard_alloc.argtypes = [C.c_int, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]
         L.ts_shard_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
         L.ts_shard_close.argtypes = [C.c_void_p]

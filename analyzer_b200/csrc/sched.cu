@@ -49,6 +49,11 @@ struct KeySrc {
     uint32_t sentinel;
     int from_ids;
     unsigned long long slots_magic;   // floor(2^64 / slots) + 1: idx / slots == umul64hi(idx, magic) for idx < 2^32
+    // sharded linking: this rank links only the players p with (p & owner_mask) == owner_rank and
+    // sorts them by their local index p >> owner_shift; other slots become the sentinel.
+    // drop: sentinel keys leave the sort in pass 0 (the later passes see only *n_dev entries).
+    uint32_t owner_mask, owner_rank, owner_shift;
+    int drop;
 };
 
 __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
@@ -56,7 +61,8 @@ __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
     uint32_t k = __ldg(src.keys + idx);
     if (src.from_ids) {
         uint32_t m = __ldg(src.meta + (uint32_t)__umul64hi((unsigned long long)idx, src.slots_magic));
-        if (k == TS_EMPTY_SLOT || meta_is_gated(m, src.modes.col)) k = src.sentinel;
+        if (k == TS_EMPTY_SLOT || meta_is_gated(m, src.modes.col) || (k & src.owner_mask) != src.owner_rank) k = src.sentinel;
+        else k >>= src.owner_shift;
     }
     return k;
 }
@@ -250,6 +256,7 @@ k_radix_hist_all(KeySrc src, uint32_t n, int passes, uint32_t *ghist)
     __syncthreads();
     for (uint32_t idx = blockIdx.x * kSortBlock + threadIdx.x; idx < n; idx += gridDim.x * kSortBlock) {
         const uint32_t k = load_key(src, idx);
+        if (src.drop && k == src.sentinel) continue;
         for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(k >> (8 * p)) & 255u], 1u);
     }
     __syncthreads();
@@ -260,7 +267,7 @@ k_radix_hist_all(KeySrc src, uint32_t n, int passes, uint32_t *ghist)
 }
 
 // exclusive scan of each pass's 256 digit totals (one block, thread = digit)
-__global__ void __launch_bounds__(256) k_radix_scan_all(uint32_t *ghist, int passes)
+__global__ void __launch_bounds__(256) k_radix_scan_all(uint32_t *ghist, int passes, uint32_t *n_dev)
 {
     __shared__ uint32_t s[256];
     for (int p = 0; p < passes; ++p) {
@@ -269,6 +276,7 @@ __global__ void __launch_bounds__(256) k_radix_scan_all(uint32_t *ghist, int pas
         if (threadIdx.x == 0) {
             uint32_t run = 0;
             for (int d = 0; d < 256; ++d) { uint32_t c = s[d]; s[d] = run; run += c; }
+            if (p == 0) *n_dev = run;          // entries that stay in the sort
         }
         __syncthreads();
         ghist[p * 256 + threadIdx.x] = s[threadIdx.x];
@@ -288,10 +296,11 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t *p, uint32_t v)
 }
 
 __global__ void __launch_bounds__(kSortBlock, TS_SORT_MIN_BLOCKS)
-k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n, int shift,
+k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n_in, const uint32_t *n_dev, int shift,
                  const uint32_t *digit_base, uint32_t *status, uint32_t *ticket, uint32_t *keys_out,
                  uint32_t *vals_out)
 {
+    const uint32_t n = n_dev ? __ldg(n_dev) : n_in;
     __shared__ uint32_t wcount[kWarps][256];
     __shared__ uint32_t gbase[256];
     __shared__ uint32_t warp_tot[kWarps];
@@ -314,7 +323,7 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
-        bool ok = idx < n;
+        bool ok = idx < n && !(src.drop && key[k] == src.sentinel);
         const uint32_t d = (key[k] >> shift) & 255u;
         uint32_t peers = __ballot_sync(0xFFFFFFFFu, ok);
         peers = ok ? peers : ~peers;
@@ -369,14 +378,16 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
-        if (idx < n) {
+        if (idx < n && !(src.drop && key[k] == src.sentinel)) {
             uint32_t pos = wcount[warp][(key[k] >> shift) & 255u] + off[k];
             skey[pos] = key[k];
             sval[pos] = ident_vals ? idx : __ldg(vals_in + idx);
         }
     }
     __syncthreads();
-    const uint32_t cnt = min((uint32_t)kSortTile, n - tile_base);
+    uint32_t cnt = 0;                       // elements of this tile that stay in the sort
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) cnt += warp_tot[w];
     for (uint32_t i = threadIdx.x; i < cnt; i += kSortBlock) {
         uint32_t k = skey[i];
         uint32_t pos = gbase[(k >> shift) & 255u] + i;
@@ -569,9 +580,10 @@ k_permute(const uint32_t *ids, const uint32_t *meta, const uint32_t *order, uint
 // enough to stay in L2, so every 32-byte sector of pred is written back to HBM
 // once, complete, instead of being read-modified-written eight times.
 __global__ void __launch_bounds__(256)
-k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long long slots_magic, uint32_t sentinel,
-       uint32_t v_lo, uint32_t v_hi, uint32_t seq_base, const uint32_t *last, uint32_t *pred)
+k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n_in, const uint32_t *n_dev, unsigned long long slots_magic,
+       uint32_t sentinel, uint32_t v_lo, uint32_t v_hi, uint32_t seq_base, const uint32_t *last, uint32_t *pred)
 {
+    const uint32_t n = n_dev ? __ldg(n_dev) : n_in;
     // four consecutive sorted entries per thread: two 16-byte streaming loads plus the
     // entry just before them, all issued up front
     const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
@@ -617,9 +629,10 @@ k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long lon
 
 // after all pred passes: the last slot of every player's run becomes the carried tail
 __global__ void __launch_bounds__(256)
-k_last_update(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long long slots_magic,
-              uint32_t sentinel, uint32_t seq_base, uint32_t *last)
+k_last_update(const uint32_t *keys, const uint32_t *vals, uint32_t n_in, const uint32_t *n_dev,
+              unsigned long long slots_magic, uint32_t sentinel, uint32_t seq_base, uint32_t *last)
 {
+    const uint32_t n = n_dev ? __ldg(n_dev) : n_in;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t k = __ldcs(keys + i);
@@ -711,26 +724,34 @@ int radix_onesweep_enabled()
 // LSD radix sort of n (key, val) pairs on the low `bits` bits.  Pass 0 reads
 // `src` (with identity values); results ping-pong between the two buffers.
 // Returns the index of the buffer holding the result (or <0).
-int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream, int sm_count)
+int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream, int sm_count,
+               const uint32_t **n_dev_out = nullptr)
 {
     const int passes = (bits + 7) / 8;
-    if (n >= (1u << 30) || passes > kMaxPasses || !radix_onesweep_enabled())
+    if (n_dev_out) *n_dev_out = nullptr;
+    if (n >= (1u << 30) || passes > kMaxPasses || !radix_onesweep_enabled()) {
+        if (src0.drop) {
+            ts_set_error("sharded linking needs the single-sweep sort (fewer than 2^30 slot entries per window)");
+            return TS_E_UNSUPPORTED;
+        }
         return radix_sort_3kernel(src0, n, bits, w, stream);
+    }
     const uint32_t n_tiles = (n + kSortTile - 1) / kSortTile;
-    uint32_t *ghist = w.totals, *ticket = w.totals + kMaxPasses * 256;
+    uint32_t *ghist = w.totals, *ticket = w.totals + kMaxPasses * 256, *n_dev = ticket + 1;
+    if (n_dev_out) *n_dev_out = n_dev;
     if (cudaMemsetAsync(w.totals, 0, kTotalsWords * 4, stream) != cudaSuccess) return ts_cuda_fail(cudaGetLastError(), "memset");
     k_radix_hist_all<<<sm_count * 8, kSortBlock, 0, stream>>>(src0, n, passes, ghist);
-    k_radix_scan_all<<<1, 256, 0, stream>>>(ghist, passes);
+    k_radix_scan_all<<<1, 256, 0, stream>>>(ghist, passes, n_dev);
     int cur = -1;
     for (int p = 0; p < passes; ++p) {
         KeySrc src = src0;
         const uint32_t *vals_in = nullptr;
-        if (p > 0) { src.keys = w.keys[cur]; src.from_ids = 0; vals_in = w.vals[cur]; }
+        if (p > 0) { src.keys = w.keys[cur]; src.from_ids = 0; src.drop = 0; vals_in = w.vals[cur]; }
         int dst = cur < 0 ? 0 : ((cur + 1) & 1);
         if (cudaMemsetAsync(w.hist, 0, (size_t)n_tiles * 256 * 4, stream) != cudaSuccess ||
             cudaMemsetAsync(ticket, 0, 4, stream) != cudaSuccess)
             return ts_cuda_fail(cudaGetLastError(), "memset");
-        k_radix_onesweep<<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n, p * 8, ghist + p * 256,
+        k_radix_onesweep<<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n, p == 0 ? nullptr : n_dev, p * 8, ghist + p * 256,
                                                              w.hist, ticket, w.keys[dst], w.vals[dst]);
         cur = dst;
     }
@@ -808,6 +829,8 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
+    src.owner_mask = src.owner_rank = src.owner_shift = 0;
+    src.drop = 0;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
     if (buf < 0) return buf;
 
@@ -857,6 +880,8 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     rsrc.sentinel = 0;
     rsrc.from_ids = 0;
     rsrc.slots_magic = 0ull;   // unused: keys are read as they are
+    rsrc.owner_mask = rsrc.owner_rank = rsrc.owner_shift = 0;
+    rsrc.drop = 0;
     buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s, ctx->sm_count);
     if (buf < 0) return buf;
     TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
@@ -879,9 +904,10 @@ extern "C" int64_t ts_link_workspace_bytes(int64_t n_matches, int32_t slots)
     return (int64_t)(4 * align_up(np * 4) + align_up((n_blocks * 256 + 256) * 4) + align_up(kTotalsWords * 4));
 }
 
-extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
-                            int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last,
-                            uint32_t *pred, void *workspace, int64_t workspace_bytes, void *stream)
+namespace {
+int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
+                   int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last, uint32_t *pred,
+                   void *workspace, int64_t workspace_bytes, void *stream, int32_t rank, int32_t n_shards)
 {
     if (seq_base < 0 || seq_base + n_matches >= 0xFFFFFFFFll) {
         ts_set_error("ts_link_pred: stream-wide match numbers must stay below 2^32 - 1");
@@ -923,10 +949,29 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
-    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
+    src.owner_mask = src.owner_rank = src.owner_shift = 0;
+    src.drop = 0;
+    // sharded: link only the players this rank owns, by local index; every other slot leaves
+    // the sort in pass 0 and keeps the fill value, so an element-wise MIN over the ranks'
+    // pred arrays assembles the complete links (owned entries are < 2^31 or TS_NONE = -1)
+    const bool sharded = n_shards > 1;
+    int shard_shift = 0;
+    while ((1 << shard_shift) < n_shards) ++shard_shift;
+    const int64_t local_players = sharded ? (n_players - rank + n_shards - 1) / n_shards : n_players;
+    if (sharded) {
+        src.owner_mask = (uint32_t)n_shards - 1u;
+        src.owner_rank = (uint32_t)rank;
+        src.owner_shift = (uint32_t)shard_shift;
+        src.sentinel = (uint32_t)local_players;
+        src.drop = 1;
+    }
+    const uint32_t *n_dev = nullptr;
+    int buf = radix_sort(src, np, bits_for((uint64_t)local_players), w, s, ctx->sm_count, &n_dev);
     if (buf < 0) return buf;
-    // slots that take no part (empty, gated match) read TS_NONE: the output is fully defined
-    TS_CUDA(cudaMemsetAsync(pred, 0xFF, (size_t)np * 4, s));
+    if (!sharded) n_dev = nullptr;
+    // slots that take no part (empty, gated match) read TS_NONE: the output is fully defined;
+    // sharded: slots of players owned elsewhere read 0x7F7F7F7F until the MIN over ranks
+    TS_CUDA(cudaMemsetAsync(pred, sharded ? 0x7F : 0xFF, (size_t)np * 4, s));
     // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2.
     // Every pass re-reads the sorted pairs, so this only pays for a handful of passes; a window
     // too large for that (more than 128 Mi slot entries) takes one pass and the read-modify-writes.
@@ -934,12 +979,34 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
     if (((uint64_t)np + range - 1) / range > 8) range = 0xFFFFFFFFu;
     for (uint64_t lo = 0; lo < np; lo += range) {
         uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);
-        k_pred<<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, src.slots_magic, (uint32_t)n_players,
-                                                (uint32_t)lo, hi, (uint32_t)seq_base, last, pred);
+        k_pred<<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic, src.sentinel,
+                                                  (uint32_t)lo, hi, (uint32_t)seq_base, last, pred);
     }
     if (last)
-        k_last_update<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, src.slots_magic,
-                                                       (uint32_t)n_players, (uint32_t)seq_base, last);
+        k_last_update<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic,
+                                                       src.sentinel, (uint32_t)seq_base, last);
     TS_CUDA(cudaGetLastError());
     return 0;
+}
+}  // namespace
+
+extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
+                            int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last,
+                            uint32_t *pred, void *workspace, int64_t workspace_bytes, void *stream)
+{
+    return link_pred_impl(ctx, ids, meta, n_matches, slots, n_players, mode_col, seq_base, last, pred, workspace,
+                          workspace_bytes, stream, 0, 1);
+}
+
+extern "C" int ts_link_pred_sharded(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches,
+                                    int32_t slots, int64_t n_players, const int8_t mode_col[16], int64_t seq_base,
+                                    uint32_t *last, uint32_t *pred, int32_t rank, int32_t n_shards, void *workspace,
+                                    int64_t workspace_bytes, void *stream)
+{
+    if (n_shards < 1 || n_shards > 16 || (n_shards & (n_shards - 1)) || rank < 0 || rank >= n_shards) {
+        ts_set_error("ts_link_pred_sharded: n_shards must be a power of two <= 16 and 0 <= rank < n_shards");
+        return TS_E_ARG;
+    }
+    return link_pred_impl(ctx, ids, meta, n_matches, slots, n_players, mode_col, seq_base, last, pred, workspace,
+                          workspace_bytes, stream, rank, n_shards);
 }

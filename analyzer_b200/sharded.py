@@ -97,6 +97,24 @@ class ShardedLadder(object):
                 ptr(ids), ptr(meta), ptr(pred), n, p, C.byref(out), lanes,
                 C.c_void_p(torch.cuda.current_stream().cuda_stream)))
 
+    def link(self, ids, meta, mode_cols=(-1, 0), data_group=None):
+        """Distributed linking: every rank links the players it owns, then one
+        element-wise MIN all-reduce assembles pred [N, P] on every rank."""
+        n, p = ids.shape
+        pred = torch.empty_like(ids)
+        nbytes = L.check(self.lib.ts_link_workspace_bytes(n, p))
+        ws = self.rater._workspace(nbytes)
+        cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
+        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+        with torch.cuda.device(self.device):
+            L.check(self.lib.ts_link_pred_sharded(
+                self.rater._ctx, ptr(ids), ptr(meta), n, p, self.n_players, (C.c_int8 * 16)(*cols), 0, None,
+                ptr(pred), self.rank, self.world, ptr(ws), ws.numel(),
+                C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+        if self.world > 1:
+            dist.all_reduce(pred, op=dist.ReduceOp.MIN, group=data_group if data_group is not None else self.group)
+        return pred
+
     def _barrier(self):
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)

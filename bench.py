@@ -495,8 +495,8 @@ def run_b200(a):
 
 def run_sharded(a):
     """One ladder, table sharded by player id over the ranks' GPUs; every rank
-    holds the match stream, computes the links (replicated: the distributed
-    sort is not built yet) and rates the tiles t with t % world == rank."""
+    holds the match stream, links the players it owns (one MIN all-reduce
+    assembles the links) and rates the tiles t with t % world == rank."""
     import torch
     import torch.distributed as dist
     from analyzer_b200 import engine, sharded
@@ -528,7 +528,7 @@ def run_sharded(a):
         dist.barrier()
         e0, e1 = ev(), ev()
         e0.record()
-        pred = rater.link_pred(ids_d, meta_d, u, [-1, 0])
+        pred = ladder.link(ids_d, meta_d, [-1, 0])      # owned players per rank + one MIN all-reduce
         e1.record()
         torch.cuda.synchronize()
         dist.barrier()
@@ -552,8 +552,9 @@ def run_sharded(a):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": workload_name(a) + ", table hash-sharded over %d GPUs (NVLink peer memory)" % world,
                            "seed": hex(SEED), "path": "stream-sharded",
-                           "note": "link phase replicated on every rank; rate phase split by warp tile, no inter-GPU "
-                                   "barrier or collective; rate_ms is wall clock between host barriers"},
+                           "note": "link phase: each rank sorts / links the players it owns, one MIN all-reduce; rate "
+                                   "phase split by warp tile, no inter-GPU barrier or collective; rate_ms is wall "
+                                   "clock between host barriers"},
                 "phases": {"schedule_ms": ms_link, "rate_ms": ms_rate, "rate_only_matches_per_s": n / (ms_rate * 1e-3)},
                 "nvlink": {"bytes_per_gpu_per_step": nv_bytes, "achieved_gbs_per_gpu": nv_bytes / (ms_rate * 1e-3) / 1e9,
                            "peak_gbs_per_direction": 770.0, "note": "remote row reads + writes; 770 GB/s = measured peer copy "

@@ -206,6 +206,16 @@ int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, cons
  * wherever they live.  vt_shards: host array of G device pointers (index rank
  * = own shard).  Shard size: 32 bytes * ceil((n_players - rank) / G).
  * No counterpart in the reference (single process, single thread). */
+/* Linking for the sharded ladder: rank r links only the players it owns (p %
+ * n_shards == r), sorted by local index, and leaves 0x7F7F7F7F in every slot of a
+ * player owned elsewhere; an element-wise MIN of the ranks' pred arrays (one
+ * all-reduce) yields the complete links, identical to ts_link_pred's.  `last`, if
+ * given, has one entry per OWNED player (local index).  Sort and scatter work
+ * shrink with 1 / n_shards; every rank still reads the whole id stream once. */
+int ts_link_pred_sharded(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
+                         int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last,
+                         uint32_t *pred, int32_t rank, int32_t n_shards, void *workspace, int64_t workspace_bytes,
+                         void *stream);
 int ts_shard_alloc(int device, int64_t bytes, void **ptr, void *handle64);
 int ts_shard_open(int device, const void *handle64, void **ptr);
 int ts_shard_close(void *ptr);

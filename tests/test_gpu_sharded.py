@@ -28,8 +28,12 @@ def _worker(rank, world, port, results):
         gen = engine.make_gen(seed, u, slots=slots, mode=1, p_draw=0.02, p_afk=0.02, zipf=zipf)
         ids, meta = engine.gen_matches(gen, 0, n, dev)
         full = engine.gen_table(seed, 0, u, dev).reshape(u, 2)
-        pred = r.link_pred(ids, meta, u, [-1, 0])
         ladder = sharded.ShardedLadder(r, u, rank, world)
+        single_pred = r.link_pred(ids, meta, u, [-1, 0])
+        pred = ladder.link(ids, meta, [-1, 0])              # owned players only + MIN all-reduce
+        live = single_pred != pred
+        # identical on every slot that takes part; unused slots read TS_NONE vs the fill value
+        ok = ok and bool(((single_pred == -1) & (pred == 0x7F7F7F7F))[live].all())
         mine = sharded.split_table(full, rank, world)
         ladder.rate(mine, ids, meta, pred, mode=1)
         errs = r.error_count()
