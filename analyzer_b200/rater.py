@@ -109,111 +109,140 @@ class _Batch(object):
 def ingest(matches):
     """Object graphs -> columns.  Every distinct Player object gets a row of the
     batch-local table (NaN = attribute is None).  Mirrors the reads of
-    rater.py:70-130 without touching the objects."""
+    rater.py:70-130 without touching the objects.  Written for speed: this and
+    _write_back are what bounds the object API (the GPU side is microseconds)."""
     b = _Batch()
-    b.matches = list(matches)
+    b.matches = matches = list(matches)
     index, players = {}, []
-    n = len(b.matches)
+    n = len(matches)
     widest = 3
-    for match in b.matches:
+    for match in matches:
         for roster in match.rosters[:2]:
-            widest = max(widest, len(roster.participants))
+            k = len(roster.participants)
+            if k > widest:
+                widest = k
     if widest > 5:
         raise ValueError("rosters of more than 5 participants are not supported by the kernel")
     slots = 6 if widest <= 3 else 10
     half = slots // 2
-    ids = np.full((n, slots), L.EMPTY_SLOT, dtype=np.uint32)
-    meta = np.zeros(n, dtype=np.uint32)
+    empty = L.EMPTY_SLOT
+    ids = [empty] * (n * slots)                 # plain lists: element stores into numpy arrays are slow
+    meta = [0] * n
     slot_parts = [None] * n
     need_seed = set()
-    for m, match in enumerate(b.matches):
-        mode = _MODE_INDEX.get(match.game_mode, L.MODE_UNSUPPORTED)
-        bits = mode << L.META_MODE_SHIFT
-        if mode == L.MODE_UNSUPPORTED:
+    modes_seen = set()
+    mode_index, unsupported, shift = _MODE_INDEX, L.MODE_UNSUPPORTED, L.META_MODE_SHIFT
+    for m, match in enumerate(matches):
+        mode = mode_index.get(match.game_mode, unsupported)
+        bits = mode << shift
+        if mode == unsupported:
             meta[m] = bits
             continue
-        if len(match.rosters) != 2:
+        rosters = match.rosters
+        if len(rosters) != 2:
             bits |= L.META_INVALID
         for part in match.participants:          # rater.py:95-100 (stops at the first AFK)
             if part.went_afk == 1:
                 bits |= L.META_AFK
                 break
-        gated = bits & (L.META_AFK | L.META_INVALID)
         parts = []
-        if not gated:
-            for t, roster in enumerate(match.rosters):
+        if not bits & (L.META_AFK | L.META_INVALID):
+            modes_seen.add(mode)
+            base = m * slots
+            for t, roster in enumerate(rosters):
                 if roster.winner:
                     bits |= (L.META_WIN_A << t)
-                for k, part in enumerate(roster.participants):
+                s = t * half
+                for part in roster.participants:
                     player = part.player[0]
-                    row = index.get(id(player))
+                    key = id(player)
+                    row = index.get(key)
                     if row is None:
-                        row = index[id(player)] = len(players)
+                        row = index[key] = len(players)
                         players.append(player)
-                    ids[m, t * half + k] = row
-                    parts.append((t * half + k, part))
-                    if player.trueskill_mu is None:
-                        need_seed.add(row)
+                        if player.trueskill_mu is None:
+                            need_seed.add(row)
+                    ids[base + s] = row
+                    parts.append((s, part, player))
+                    s += 1
         meta[m] = bits
         slot_parts[m] = parts
     u = max(len(players), 1)
     table = np.full((u, 8, 2), np.nan)
     seed = np.full((u, 2), np.nan)
-    for row, player in enumerate(players):
-        if player.trueskill_mu is not None:
-            table[row, 0] = (float(player.trueskill_mu), float(player.trueskill_sigma))
-        for mi, name in enumerate(MODE_NAMES):
-            mu = getattr(player, _MODE_COLUMN[name] + "_mu", None)
-            if mu is not None:
-                table[row, 1 + mi] = (float(mu), float(getattr(player, _MODE_COLUMN[name] + "_sigma")))
-        if row in need_seed:
-            seed[row] = get_trueskill_seed(player)
-    b.ids, b.meta, b.table, b.seed = ids, meta, table, seed
+    # shared pair of every player; queue pairs only of the modes that are rated in this batch
+    sh = [(float(p.trueskill_mu), float(p.trueskill_sigma)) if p.trueskill_mu is not None else (np.nan, np.nan)
+          for p in players]
+    if players:
+        table[:len(players), 0] = sh
+    for mi in sorted(modes_seen):
+        mu_col, sg_col = _MODE_COLUMN[MODE_NAMES[mi]] + "_mu", _MODE_COLUMN[MODE_NAMES[mi]] + "_sigma"
+        col = []
+        for p in players:
+            mu = getattr(p, mu_col, None)
+            col.append((float(mu), float(getattr(p, sg_col))) if mu is not None else (np.nan, np.nan))
+        if players:
+            table[:len(players), 1 + mi] = col
+    for row in need_seed:
+        seed[row] = get_trueskill_seed(players[row])
+    b.ids = np.array(ids, dtype=np.uint32).reshape(n, slots)
+    b.meta = np.array(meta, dtype=np.uint32)
+    b.table, b.seed = table, seed
     b.players, b.slot_parts, b.index, b.slots = players, slot_parts, index, slots
     return b
 
 
 def _write_back(b, res):
     """Columns -> attributes, exactly the stores of rater.py:96-106,141,151-169."""
-    status = res["status"]
+    status = res["status"].tolist()
+    quality = res["quality"].tolist()
+    o_sh, o_de, o_qu = res["out_shared"].tolist(), res["out_delta"].tolist(), res["out_queue"].tolist()
+    meta = b.meta.tolist()
+    info, error = logger.isEnabledFor(logging.INFO), logger.isEnabledFor(logging.ERROR)
     for m, match in enumerate(b.matches):
-        st = int(status[m])
+        st = status[m]
         if st == L.ST_SKIP_MODE:
-            logger.info("got unsupported game mode %s", match.game_mode)
+            if info:
+                logger.info("got unsupported game mode %s", match.game_mode)
             continue
-        if st in (L.ST_AFK, L.ST_INVALID):
-            if st == L.ST_INVALID or len(match.rosters) != 2:
+        if st == L.ST_AFK or st == L.ST_INVALID:
+            if error and (st == L.ST_INVALID or len(match.rosters) != 2):
                 logger.error("got an invalid matchup %s", match.api_id)
-            if int(b.meta[m]) & L.META_AFK:
+            if info and meta[m] & L.META_AFK:
                 logger.info("got an afk matchup %s", match.api_id)
             match.trueskill_quality = 0
             for part in match.participants:
                 part.participant_items[0].any_afk = True
             continue
-        logger.info("got a valid matchup %s", match.api_id)
+        if info:
+            logger.info("got a valid matchup %s", match.api_id)
         col = _MODE_COLUMN[match.game_mode]
-        match.trueskill_quality = float(res["quality"][m])
+        mu_col, sg_col = col + "_mu", col + "_sigma"
+        match.trueskill_quality = quality[m]
         for part in match.participants:
             part.participant_items[0].any_afk = False
+        sh_m, de_m, qu_m = o_sh[m], o_de[m], o_qu[m]
+        parts = b.slot_parts[m]
         seen = set()
-        for s, part in b.slot_parts[m]:
-            player = part.player[0]
-            mu, sg = float(res["out_shared"][m, s, 0]), float(res["out_shared"][m, s, 1])
+        for s, part, player in parts:
+            mu, sg = sh_m[s]
             # a player listed twice in one match (worker_test.py:130-131) has already
             # been updated when the reference reaches the second listing: delta 0
-            part.trueskill_delta = float(res["out_delta"][m, s]) if id(player) not in seen else 0.0
+            key = id(player)
             if player.trueskill_mu is None:
                 part.trueskill_delta = 0
-            seen.add(id(player))
+            else:
+                part.trueskill_delta = de_m[s] if key not in seen else 0.0
+            seen.add(key)
             player.trueskill_mu = part.trueskill_mu = mu
             player.trueskill_sigma = part.trueskill_sigma = sg
-        for s, part in b.slot_parts[m]:
-            player, items = part.player[0], part.participant_items[0]
-            mu, sg = float(res["out_queue"][m, s, 0]), float(res["out_queue"][m, s, 1])
-            setattr(player, col + "_mu", mu)
-            setattr(items, col + "_mu", mu)
-            setattr(player, col + "_sigma", sg)
-            setattr(items, col + "_sigma", sg)
+        for s, part, player in parts:
+            items = part.participant_items[0]
+            mu, sg = qu_m[s]
+            setattr(player, mu_col, mu)
+            setattr(items, mu_col, mu)
+            setattr(player, sg_col, sg)
+            setattr(items, sg_col, sg)
 
 
 def rate_matches(matches, device=0):
