@@ -383,7 +383,7 @@ extern "C" int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_s
     cudaStream_t s = (cudaStream_t)stream;
     const bool shared = table->shared_col >= 0;
     int lanes = lanes_per_match;
-    if (lanes == 0) lanes = 2;   // one lane per team: see DESIGN.md for the measurements
+    if (lanes == 0) lanes = slots == 6 ? 2 : 8;   // 3v3: one lane per team; 5v5: two lanes hold three slots at most
     if (slots == 6) return shared ? dispatch_l<6, true>(ctx, a, lanes, s) : dispatch_l<6, false>(ctx, a, lanes, s);
     return shared ? dispatch_l<10, true>(ctx, a, lanes, s) : dispatch_l<10, false>(ctx, a, lanes, s);
 }

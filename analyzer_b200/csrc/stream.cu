@@ -463,7 +463,7 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
     a.ctrl = ctx->d_ctrl;
     const int64_t u = table->n_players;
     if (flags & TS_STREAM_LOAD) k_vt_load<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, a.vt, u);
-    int lanes = lanes_per_match ? lanes_per_match : 2;
+    int lanes = lanes_per_match ? lanes_per_match : (slots == 6 ? 2 : 8);   // measured: DESIGN.md 3.2
     a.n_shards = 1; a.shard_shift = 0; a.rank = 0;
     for (int i = 0; i < kMaxShards; ++i) a.shards[i] = nullptr;
     TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
@@ -592,6 +592,6 @@ extern "C" int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_
     for (int i = 0; i < n_shards; ++i)
         if (!a.shards[i]) { ts_set_error("ts_rate_stream_sharded: shard %d not mapped", i); return TS_E_ARG; }
     TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
-    int lanes = lanes_per_match ? lanes_per_match : 2;
+    int lanes = lanes_per_match ? lanes_per_match : (slots == 6 ? 2 : 8);   // measured: DESIGN.md 3.2
     return slots == 6 ? dispatch_l<6, true>(ctx, a, lanes, s) : dispatch_l<10, true>(ctx, a, lanes, s);
 }
