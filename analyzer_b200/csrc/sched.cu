@@ -295,6 +295,7 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t *p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+template <bool DROP>      // DROP: sentinel keys leave the sort in this pass (sharded linking, pass 0)
 __global__ void __launch_bounds__(kSortBlock, TS_SORT_MIN_BLOCKS)
 k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n_in, const uint32_t *n_dev, int shift,
                  const uint32_t *digit_base, uint32_t *status, uint32_t *ticket, uint32_t *keys_out,
@@ -323,7 +324,7 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
-        bool ok = idx < n && !(src.drop && key[k] == src.sentinel);
+        bool ok = idx < n && !(DROP && key[k] == src.sentinel);
         const uint32_t d = (key[k] >> shift) & 255u;
         uint32_t peers = __ballot_sync(0xFFFFFFFFu, ok);
         peers = ok ? peers : ~peers;
@@ -378,16 +379,19 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
-        if (idx < n && !(src.drop && key[k] == src.sentinel)) {
+        if (idx < n && !(DROP && key[k] == src.sentinel)) {
             uint32_t pos = wcount[warp][(key[k] >> shift) & 255u] + off[k];
             skey[pos] = key[k];
             sval[pos] = ident_vals ? idx : __ldg(vals_in + idx);
         }
     }
     __syncthreads();
-    uint32_t cnt = 0;                       // elements of this tile that stay in the sort
+    uint32_t cnt = tile_base < n ? min((uint32_t)kSortTile, n - tile_base) : 0u;
+    if (DROP) {                             // only the elements of this tile that stay in the sort
+        cnt = 0;
 #pragma unroll
-    for (int w = 0; w < kWarps; ++w) cnt += warp_tot[w];
+        for (int w = 0; w < kWarps; ++w) cnt += warp_tot[w];
+    }
     for (uint32_t i = threadIdx.x; i < cnt; i += kSortBlock) {
         uint32_t k = skey[i];
         uint32_t pos = gbase[(k >> shift) & 255u] + i;
@@ -751,8 +755,14 @@ int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStrea
         if (cudaMemsetAsync(w.hist, 0, (size_t)n_tiles * 256 * 4, stream) != cudaSuccess ||
             cudaMemsetAsync(ticket, 0, 4, stream) != cudaSuccess)
             return ts_cuda_fail(cudaGetLastError(), "memset");
-        k_radix_onesweep<<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n, p == 0 ? nullptr : n_dev, p * 8, ghist + p * 256,
-                                                             w.hist, ticket, w.keys[dst], w.vals[dst]);
+        if (p == 0 && src0.drop)
+            k_radix_onesweep<true><<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, 1, n, nullptr, 0, ghist, w.hist, ticket,
+                                                                       w.keys[dst], w.vals[dst]);
+        else
+            k_radix_onesweep<false><<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n,
+                                                                        (p > 0 && src0.drop) ? n_dev : nullptr, p * 8,
+                                                                        ghist + p * 256, w.hist, ticket, w.keys[dst],
+                                                                        w.vals[dst]);
         cur = dst;
     }
     cudaError_t e = cudaGetLastError();
