@@ -137,14 +137,54 @@ def cpu_rate_match_rate(ids, meta, seconds):
     return done / (time.perf_counter() - t0), done
 
 
+class _Row(object):
+    """ORM-like row: attributes only (the shape worker_test.py:6-63 fakes)."""
+
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+
+_QUEUE_COLS = ["trueskill_" + m for m in ("casual", "ranked", "blitz", "br", "5v5_casual", "5v5_ranked")]
+
+
+def _object_graphs(ids, meta, n_players):
+    """Match / roster / participant / player graphs of a 'ranked' stream; players are shared
+    between matches like in a SQLAlchemy session's identity map (worker.py:176-192)."""
+    def player(i):
+        p = _Row(api_id=str(i), skill_tier=i % 30, rank_points_ranked=None, rank_points_blitz=None,
+                 trueskill_mu=None, trueskill_sigma=None)
+        for c in _QUEUE_COLS:
+            setattr(p, c + "_mu", None)
+            setattr(p, c + "_sigma", None)
+        return p
+
+    players = [player(i) for i in range(n_players)]
+    half = ids.shape[1] // 2
+    out = []
+    for m in range(len(ids)):
+        rosters = []
+        for t in range(2):
+            parts = []
+            for s in range(t * half, (t + 1) * half):
+                items = _Row(api_id="", any_afk=False)
+                for c in _QUEUE_COLS:
+                    setattr(items, c + "_mu", None)
+                    setattr(items, c + "_sigma", None)
+                parts.append(_Row(api_id="", went_afk=0, participant_items=[items], player=[players[int(ids[m, s])]],
+                                  trueskill_mu=None, trueskill_sigma=None, trueskill_delta=None))
+            rosters.append(_Row(api_id="", winner=bool(int(meta[m]) & (1 << t)), participants=parts))
+        out.append(_Row(api_id=str(m), game_mode="ranked", rosters=rosters,
+                        participants=[p for r in rosters for p in r.participants], trueskill_quality=None))
+    return out
+
+
 def object_api_rate(ids_d, meta_d, n=5000):
     """The drop-in object API: analyzer_b200.rater.rate_matches on ORM-like object
     graphs (the shape worker.py:176-192 hands to rate_match), against the port's
-    rate_match loop on the same graphs.  Ingest and write-back are Python."""
+    rate_match loop on the same kind of graphs.  Ingest and write-back are Python."""
     import logging
     import numpy as np
     from analyzer_b200 import rater as gpu_rater
-    from oracle import rater_port as rp
     gpu_rater.logger.setLevel(logging.ERROR)
     ids = ids_d[:n].cpu().numpy().view(np.uint32) % 3000        # 3000 players: chains inside the batch
     meta = meta_d[:n].cpu().numpy().view(np.uint32)
@@ -154,22 +194,18 @@ def object_api_rate(ids_d, meta_d, n=5000):
             while int(row[k]) in seen:
                 row[k] = (int(row[k]) + 1) % 3000
             seen.add(int(row[k]))
-
-    def graphs():
-        players = {i: rp.new_player(skill_tier=i % 30) for i in range(3000)}
-        return rp.matches_from_columns(ids, meta, players)
-
-    gpu_rater.rate_matches(graphs()[:64])                        # warm-up (context, first launches)
-    g = graphs()
+    gpu_rater.rate_matches(_object_graphs(ids[:64], meta[:64], 3000))      # warm-up (context, first launches)
+    g = _object_graphs(ids, meta, 3000)
     t0 = time.perf_counter()
     gpu_rater.rate_matches(g)
     dt_gpu = time.perf_counter() - t0
-    g2 = graphs()[:400]
+    # reference loop on the same graphs (the oracle is used here only as the CPU baseline / checker)
+    from oracle import rater_port as rp
+    g2 = _object_graphs(ids[:400], meta[:400], 3000)
     t0 = time.perf_counter()
     for m in g2:
         rp.rate_match(m)
     dt_cpu = (time.perf_counter() - t0) / len(g2)
-    # same answer on the shared prefix
     err = max(abs(a.participants[0].trueskill_mu - b.participants[0].trueskill_mu)
               for a, b in zip(g[:400], g2) if b.participants[0].trueskill_mu is not None)
     return {"rate_matches_per_s": n / dt_gpu, "batch": n, "reference_loop_per_s": 1.0 / dt_cpu,
