@@ -10,7 +10,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libtsrate.so")
-SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "static_sched.cu"]
+SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "stream_pair.cu", "static_sched.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-shared", "-Xcompiler", "-fPIC"]
 
@@ -66,7 +66,7 @@ def sources():
 def build(force=False, verbose=False):
     """Compile the CUDA library in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
     srcs = sources()
-    deps = srcs + [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "vw.cuh"), os.path.join(CSRC, "vtable.inc"),
+    deps = srcs + [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "vw.cuh"), os.path.join(CSRC, "vtable.inc"), os.path.join(CSRC, "stream_common.cuh"),
                    os.path.join(os.path.dirname(_HERE), "include", "tsrate.h")]
     if not force and os.path.exists(LIB_PATH) and \
             all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(d) for d in deps):

@@ -25,13 +25,11 @@
 //
 // Single-pair ladders only (table.row_pairs == 1, shared_col == -1): the
 // faithful shared + queue layout keeps using ts_rate.
-#include <stdlib.h>
-#include <string.h>
-
-#include "common.cuh"
-#include "vw.cuh"
+#include "stream_common.cuh"
 
 namespace {
+
+using namespace tsstream;
 
 constexpr int kBlock = 256;
 #ifndef TS_STREAM_MIN_BLOCKS
@@ -62,48 +60,6 @@ struct StreamArgs {
     unsigned long long *ctrl;
 };
 
-// SYS = rows may live in a peer GPU's memory: system scope (peer accesses bypass the local L2)
-template <bool SYS = false>
-__device__ __forceinline__ void ld_row(const unsigned long long *row, unsigned long long (&w)[4])
-{
-    if (SYS) {
-        asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(row) : "memory");
-        asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(row + 2) : "memory");
-    } else {
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(row) : "memory");
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(row + 2) : "memory");
-    }
-}
-template <bool SYS = false>
-__device__ __forceinline__ void st_row(unsigned long long *row, double mu, double sigma, uint32_t ver)
-{
-    const unsigned long long v = (unsigned long long)ver << 32;
-    const unsigned long long m = (unsigned long long)__double_as_longlong(mu);
-    const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
-    unsigned long long w0 = (m & 0xFFFFFFFFull) | v, w1 = (m >> 32) | v;
-    unsigned long long w2 = (s & 0xFFFFFFFFull) | v, w3 = (s >> 32) | v;
-    if (SYS) {
-        asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"(w0), "l"(w1) : "memory");
-        asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"(w2), "l"(w3) : "memory");
-    } else {
-        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"(w0), "l"(w1) : "memory");
-        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"(w2), "l"(w3) : "memory");
-    }
-}
-__device__ __forceinline__ bool row_has_version(const unsigned long long (&w)[4], uint32_t ver)
-{
-    return (uint32_t)(w[0] >> 32) == ver && (uint32_t)(w[1] >> 32) == ver && (uint32_t)(w[2] >> 32) == ver &&
-           (uint32_t)(w[3] >> 32) == ver;
-}
-__device__ __forceinline__ double row_mu(const unsigned long long (&w)[4])
-{
-    return __longlong_as_double((long long)((w[0] & 0xFFFFFFFFull) | (w[1] << 32)));
-}
-__device__ __forceinline__ double row_sigma(const unsigned long long (&w)[4])
-{
-    return __longlong_as_double((long long)((w[2] & 0xFFFFFFFFull) | (w[3] << 32)));
-}
-
 template <bool SHARDED>
 __device__ __forceinline__ unsigned long long *row_of(const StreamArgs &a, uint32_t pid)
 {
@@ -112,18 +68,6 @@ __device__ __forceinline__ unsigned long long *row_of(const StreamArgs &a, uint3
 }
 
 using tsvw::trunc_vw;
-
-__device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)
-{
-    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_4(void *smem, const void *gmem)
-{
-    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // per-warp staging buffers: a warp owns W = 32 / L consecutive matches at a time
 template <int P, int W>
@@ -144,21 +88,6 @@ __device__ __forceinline__ void stage_warp_tile(WarpStage<P, W> &st, int b, cons
         cp_async_8(&st.pred[b][2 * i], src_p + 2 * i);
     }
     for (uint32_t i = wl; i < cnt; i += 32) cp_async_4(&st.meta[b][i], a.meta + base + i);
-}
-
-template <int L>
-__device__ __forceinline__ double group_sum(double x, uint32_t gmask)
-{
-#pragma unroll
-    for (int o = L / 2; o > 0; o >>= 1) x += __shfl_xor_sync(gmask, x, o, L);
-    return x;
-}
-template <int L>
-__device__ __forceinline__ uint32_t group_sum_u32(uint32_t x, uint32_t gmask)
-{
-#pragma unroll
-    for (int o = L / 2; o > 0; o >>= 1) x += __shfl_xor_sync(gmask, x, o, L);
-    return x;
 }
 
 // Warps are the unit of work: warp w of the grid takes the tiles w, w + n_warps,
@@ -343,35 +272,6 @@ __global__ void __launch_bounds__(256) k_vt_store(const unsigned long long *vt, 
     reinterpret_cast<double2 *>(table)[i] = make_double2(row_mu(w), row_sigma(w));
 }
 
-int stream_sleep_ns()
-{
-    static int ns = -1;
-    if (ns < 0) {
-        const char *e = getenv("TSRATE_STREAM_SLEEP_NS");
-        ns = e ? atoi(e) : 20;
-        if (ns < 0) ns = 0;
-    }
-    return ns;
-}
-
-int stream_max_spins()
-{
-    const char *e = getenv("TSRATE_STREAM_MAX_SPINS");     // read every call: tests lower it
-    long v = e ? atol(e) : (1l << 24);
-    return (int)(v < 1024 ? 1024 : v);
-}
-
-int stream_blocks_per_sm_cap()
-{
-    static int cap = -1;
-    if (cap < 0) {
-        const char *e = getenv("TSRATE_STREAM_BLOCKS_PER_SM");
-        cap = e ? atoi(e) : 4;
-        if (cap < 1) cap = 1;
-    }
-    return cap;
-}
-
 template <int P, int L, bool SHARDED>
 int launch_stream(ts_ctx *ctx, const StreamArgs &args, cudaStream_t stream)
 {
@@ -403,7 +303,12 @@ int dispatch_l(ts_ctx *ctx, const StreamArgs &a, int lanes, cudaStream_t s)
 
 }  // namespace
 
-extern "C" int64_t ts_rate_stream_workspace_bytes(int64_t n_players) { return n_players < 0 ? TS_E_ARG : n_players * 32; }
+// 64 bytes per player covers both row formats (one pair: 32, shared + queue pair: 64)
+extern "C" int64_t ts_rate_stream_workspace_bytes(int64_t n_players) { return n_players < 0 ? TS_E_ARG : n_players * 64; }
+
+int ts_rate_stream_pair_impl(ts_ctx *ctx, const ts_table *table, int qcol, const uint32_t *ids, const uint32_t *meta,
+                             const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
+                             const ts_outputs *outputs, int32_t lanes_per_match, void *workspace, cudaStream_t s);
 
 extern "C" int ts_stream_stalled(ts_ctx *ctx, void *stream)
 {
@@ -427,8 +332,20 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
         ts_set_error("ts_rate_stream: null argument");
         return TS_E_ARG;
     }
-    if (table->row_pairs != 1 || table->shared_col >= 0) {
-        ts_set_error("ts_rate_stream: single-pair ladder tables only (row_pairs == 1, shared_col == -1); use ts_rate");
+    // layouts: one pair per player (row_pairs == 1, shared_col == -1), or shared pair + ONE queue column
+    int qcol = -1;
+    bool one_queue = true;
+    for (int i = 0; i < 6; ++i) {
+        const int c = table->mode_col[i];
+        if (c < 0) continue;
+        if (c >= table->row_pairs || c == table->shared_col) { ts_set_error("ts_rate_stream: bad mode_col[%d]", i); return TS_E_ARG; }
+        if (qcol >= 0 && c != qcol) one_queue = false;
+        qcol = c;
+    }
+    const bool pair = table->shared_col >= 0;
+    if (pair ? (!one_queue || qcol < 0 || table->shared_col >= table->row_pairs) : (table->row_pairs != 1)) {
+        ts_set_error("ts_rate_stream: the table must be a single-pair ladder (row_pairs == 1, shared_col == -1) or a "
+                     "shared pair plus ONE queue column; batches rating several queue columns use ts_rate");
         return TS_E_UNSUPPORTED;
     }
     if (slots != 6 && slots != 10) {
@@ -439,13 +356,16 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
         ts_set_error("ts_rate_stream: n_matches outside [0, 2^32 - 1)");
         return TS_E_ARG;
     }
-    if (workspace_bytes < table->n_players * 32) {
+    if (workspace_bytes < table->n_players * (pair ? 64 : 32)) {
         ts_set_error("ts_rate_stream: workspace too small (%lld < %lld bytes)", (long long)workspace_bytes,
-                     (long long)table->n_players * 32);
+                     (long long)table->n_players * (pair ? 64 : 32));
         return TS_E_WORKSPACE;
     }
     TS_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
+    if (pair)
+        return ts_rate_stream_pair_impl(ctx, table, qcol, ids, meta, pred, n_matches, slots, seq_base, flags, outputs,
+                                        lanes_per_match, workspace, s);
     StreamArgs a;
     a.prm = ctx->params;
     a.vt = (unsigned long long *)workspace;

@@ -323,6 +323,15 @@ class Rater(object):
         # (16-byte rows, no versioned copy of the table).  Measured crossover, DESIGN.md 4.
         stream = path == "stream" or (path == "auto" and shared_col < 0 and tab_t.shape[1] == 1
                                        and p in (6, 10) and n > 0 and n * p >= 2 * tab_t.shape[0])
+        mode_cols = list(mode_cols)
+        if path == "auto" and shared_col >= 0 and p in (6, 10) and n * p >= 2 * tab_t.shape[0]:
+            # shared + queue layout: streamable when the batch rates one queue column only
+            bits = torch.unique((meta_t >> L.META_MODE_SHIFT) & 15).tolist() if n <= 4_000_000 else None
+            if bits is not None:
+                rated = [m for m in bits if m < len(mode_cols) and m < N_MODES and mode_cols[m] >= 0]
+                if len(rated) == 1:
+                    mode_cols = [c if i == rated[0] else -1 for i, c in enumerate(mode_cols)]
+                    stream = True
         if windows is None:
             # ~1M matches per window, at most 8: enough to hide all but the last window's
             # link + rate behind the PCIe copy of the stream

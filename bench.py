@@ -137,6 +137,50 @@ def cpu_rate_match_rate(ids, meta, seconds):
     return done / (time.perf_counter() - t0), done
 
 
+def faithful_rate(rater, engine, ids_d, meta_d, table0, u, lanes):
+    """The reference's own semantics on the same stream (K = 2: shared pair + queue pair per
+    player, quality, two rate() per match -- rater.py:108-169), HBM-resident: every player
+    starts with a stored shared rating and a NULL queue rating."""
+    import torch
+    dev = ids_d.device
+    n, p = ids_d.shape
+    mode = int((int(meta_d[0]) >> 4) & 15)
+    cols = [-1] * 6
+    cols[mode] = 1
+    tab0 = torch.full((u, 2, 2), float("nan"), dtype=torch.float64, device=dev)
+    tab0[:, 0] = table0.reshape(u, 2)
+    tab = tab0.clone()
+    pt = engine.PlayerTable(tab, 0, cols)
+    out = {}
+    for path in ("stream", "rounds"):
+        best = None
+        for it in range(3):
+            tab.copy_(tab0)
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            e0.record()
+            if path == "stream":
+                pred = rater.link_pred_windows(ids_d, meta_d, u, pt.mode_cols)
+                e1.record()
+                rater.rate_stream(pt, ids_d, meta_d, pred, None, lanes)
+            else:
+                sch = rater.schedule(ids_d, meta_d, u, pt.mode_cols)
+                e1.record()
+                rater.rate(pt, sch, None, lanes)
+            e2.record()
+            torch.cuda.synchronize()
+            t = (e0.elapsed_time(e1), e1.elapsed_time(e2))
+            if best is None or sum(t) < sum(best):
+                best = t
+        out[path] = {"schedule_ms": best[0], "rate_ms": best[1], "matches_per_s": n / (sum(best) * 1e-3)}
+        out[path + "_table"] = tab.clone()
+    diff = float((out.pop("stream_table") - out.pop("rounds_table")).abs().max())
+    assert diff < 1e-9, diff
+    assert rater.error_count() == 0
+    out["algorithmic_bytes_per_match"] = rate_bytes_per_match(p, 2)
+    out["note"] = "shared + queue pair per player (K = 2), best of 3, no per-participant outputs; both paths agree"
+    return out
+
+
 class _Row(object):
     """ORM-like row: attributes only (the shape worker_test.py:6-63 fakes)."""
 
@@ -500,6 +544,11 @@ def run_b200(a):
     }
     if e2e:
         line["e2e"] = e2e
+    if world == 1 and p in (6, 10):
+        try:
+            line["faithful"] = faithful_rate(rater, engine, ids_d, meta_d, table0, u, a.lanes)
+        except Exception as exc:
+            line["faithful"] = {"error": repr(exc)}
     if world == 1 and not a.no_cpu_baseline:
         try:
             line["object_api"] = object_api_rate(ids_d, meta_d)

@@ -155,16 +155,20 @@ int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_sorted,
             const ts_sched_info *info, int64_t n_matches, int32_t slots,
             const ts_outputs *outputs, int32_t lanes_per_match, void *stream);
 
-/* Streaming (dataflow) form of the same path for single-pair ladders
- * (table.row_pairs == 1, shared_col == -1): no rounds, no barriers.
+/* Streaming (dataflow) form of the same path: no rounds, no barriers.  Tables:
+ * a single-pair ladder (row_pairs == 1, shared_col == -1), or the reference's
+ * shared pair plus ONE queue column (shared_col >= 0 and every rated mode's
+ * mode_col naming the same column; then quality, shared / delta / queue outputs
+ * and the NULL fallbacks of rater.py:115-130 are all produced).  A batch that
+ * rates several queue columns goes through ts_schedule + ts_rate.
  * ts_link_pred does the first half of the scheduler only -- radix sort by
  * player id and chain linking -- and writes pred[N][P]: for every slot the
  * stream-wide number of that player's previous rated match (TS_NONE if none,
  * and for empty slots and gated matches).  ts_rate_stream then rates
  * the matches in stream order (worker.py:192), each match waiting until its
  * players' rows carry the version pred names.  Results are identical to
- * ts_schedule + ts_rate.  ids / meta are in ORIGINAL order; outputs (quality,
- * out_queue, status) too.  workspace: ts_rate_stream_workspace_bytes(U).
+ * ts_schedule + ts_rate.  ids / meta are in ORIGINAL order; outputs too.
+ * workspace: ts_rate_stream_workspace_bytes(U).
  *
  * Windows (worker.py:18-20 micro-batches; ladders beyond 2^32 slot entries):
  * a stream is processed window after window by passing seq_base = number of

@@ -127,14 +127,63 @@ def test_stream_errors_do_not_stall_successors(eng, c_oracle):
     r.close()
 
 
-def test_stream_rejects_faithful_layout(eng):
+def test_stream_rejects_several_queue_columns(eng):
+    """The 8-pair table with all six modes enabled has one queue chain per mode: not streamable."""
     from analyzer_b200._lib import TsError
     r = eng.Rater(eng.Env(), 0)
     ptab = eng.PlayerTable.faithful(8, torch.device("cuda", 0))
     ids = torch.zeros((1, 6), dtype=torch.int32, device="cuda")
     meta = torch.zeros((1,), dtype=torch.int32, device="cuda")
-    with pytest.raises(TsError, match="single-pair ladder"):
+    with pytest.raises(TsError, match="ONE queue column"):
         r.rate_stream(ptab, ids, meta, ids.clone())
+    r.close()
+
+
+@pytest.mark.parametrize("slots,lanes,layout", [(6, 0, "pair"), (6, 4, "faithful"), (10, 0, "pair"), (10, 2, "faithful"),
+                                                 (6, 1, "pair"), (6, 32, "pair")])
+def test_stream_shared_plus_queue_vs_oracle_and_rounds(eng, c_oracle, slots, lanes, layout):
+    """Reference-faithful semantics in stream order: shared + one queue pair per player,
+    NULLs and seeds, quality / shared / delta / queue outputs -- against the sequential
+    float128 oracle and against the round-based kernel."""
+    dev = torch.device("cuda", 0)
+    n, n_players, seed = 60_000, 1_500, 0xA11CE0FA + slots + lanes
+    rng = np.random.default_rng(seed)
+    r = eng.Rater(eng.Env(), 0)
+    gd = eng.make_gen(seed, n_players, slots=slots, mode=2, p_draw=0.05, p_afk=0.03, zipf=(slots == 10))
+    ids_d, meta_d = eng.gen_matches(gd, 0, n, dev)
+    cols_n = 2 if layout == "pair" else 8
+    shared_col, qcol = (0, 1) if layout == "pair" else (0, 3)
+    mode_cols = [-1, -1, qcol]                   # only mode 2 (blitz) is rated
+    table = np.full((n_players, cols_n, 2), np.nan)
+    has_shared = rng.random(n_players) < 0.6
+    table[has_shared, shared_col, 0] = rng.normal(1500, 400, has_shared.sum())
+    table[has_shared, shared_col, 1] = rng.uniform(80, 600, has_shared.sum())
+    has_queue = rng.random(n_players) < 0.3
+    table[has_queue, qcol, 0] = rng.normal(1400, 400, has_queue.sum())
+    table[has_queue, qcol, 1] = rng.uniform(80, 600, has_queue.sum())
+    seeds = np.stack([rng.normal(1700, 300, n_players), rng.uniform(300, 500, n_players)], 1)
+    want = table.copy()
+    out = c_oracle.rate_sequential(c_oracle.make_params(), _u32(ids_d), _u32(meta_d), want, shared_col, mode_cols,
+                                   seed=seeds, quad=True, want_outputs=True)
+    assert out["errors"] == 0
+    tab_a, tab_b, seed_d = _dev(table), _dev(table), _dev(seeds)
+    pa, pb = eng.PlayerTable(tab_a, shared_col, mode_cols, seed_d), eng.PlayerTable(tab_b, shared_col, mode_cols, seed_d)
+    outs_a, outs_b = r.alloc_outputs(n, slots), r.alloc_outputs(n, slots)
+    pred = r.link_pred(ids_d, meta_d, n_players, pa.mode_cols)
+    r.rate_stream(pa, ids_d, meta_d, pred, outs_a, lanes)
+    r.rate(pb, r.schedule(ids_d, meta_d, n_players, pb.mode_cols), outs_b, lanes)
+    assert r.error_count() == 0
+    for got in (tab_a.cpu().numpy(), tab_b.cpu().numpy()):
+        assert np.array_equal(np.isnan(got), np.isnan(want))
+        assert np.nanmax(np.abs(got - want)) < TOL
+    st = outs_a["status"].cpu().numpy()
+    assert np.array_equal(st, out["status"])
+    rated = st == 0
+    assert np.abs(outs_a["quality"].cpu().numpy()[rated] - out["quality"][rated]).max() < 1e-12
+    for key, tol in (("out_shared", TOL), ("out_queue", TOL), ("out_delta", 2 * TOL)):
+        g, w = outs_a[key].cpu().numpy()[rated], out[key][rated]
+        assert np.array_equal(np.isnan(g), np.isnan(w)), key
+        assert np.nanmax(np.abs(g - w)) < tol, key
     r.close()
 
 
