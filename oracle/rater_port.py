@@ -52,18 +52,18 @@ _MODE_TO_COLUMN = dict(MODE_COLUMNS)
 
 
 def build_vst_points():
-    """rater.py:13-27 -- tier (-1..29) -> average skill-tier points."""
+    """rater.py:13-27 -- tier (-1..29) -> average skill-tier points: tiers -1 and 0
+    are worth 1 point; above that the table is piecewise linear in (c + 0.5), c
+    counted from the last tier of the previous segment, with segment lengths
+    11, 4, 9, 3, 2 and slopes 109 1/11, 50, 66 2/3, 133 1/3, 200."""
     pts = {-1: 1, 0: 1}
-    for c in range(1, 12):
-        pts[c] = (109 + 1 / 11) * (c + 0.5)
-    for c in range(1, 5):
-        pts[11 + c] = pts[11] + 50 * (c + 0.5)
-    for c in range(1, 10):
-        pts[15 + c] = pts[15] + (66 + 2 / 3) * (c + 0.5)
-    for c in range(1, 4):
-        pts[24 + c] = pts[24] + (133 + 1 / 3) * (c + 0.5)
-    for c in range(1, 3):
-        pts[27 + c] = pts[27] + 200 * (c + 0.5)
+    segments = ((11, 109 + 1 / 11), (4, 50), (9, 66 + 2 / 3), (3, 133 + 1 / 3), (2, 200))
+    top = 0                     # last tier of the previous segment
+    for length, slope in segments:
+        offset = pts[top] if top else 0
+        for c in range(1, length + 1):
+            pts[top + c] = offset + slope * (c + 0.5)
+        top += length
     return pts
 
 
