@@ -54,6 +54,7 @@ struct KeySrc {
     // drop: sentinel keys leave the sort in pass 0 (the later passes see only *n_dev entries).
     uint32_t owner_mask, owner_rank, owner_shift;
     int drop;
+    uint32_t rated_mask;   // bit m set: game mode m is rated (a register test instead of indexing modes.col)
 };
 
 __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
@@ -61,7 +62,9 @@ __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
     uint32_t k = __ldg(src.keys + idx);
     if (src.from_ids) {
         uint32_t m = __ldg(src.meta + (uint32_t)__umul64hi((unsigned long long)idx, src.slots_magic));
-        if (k == TS_EMPTY_SLOT || meta_is_gated(m, src.modes.col) || (k & src.owner_mask) != src.owner_rank) k = src.sentinel;
+        const bool gated = ((src.rated_mask >> ((m >> TS_META_MODE_SHIFT) & 15u)) & 1u) == 0u ||
+                           (m & (TS_META_AFK | TS_META_INVALID)) != 0u;
+        if (k == TS_EMPTY_SLOT || gated || (k & src.owner_mask) != src.owner_rank) k = src.sentinel;
         else k >>= src.owner_shift;
     }
     return k;
@@ -369,6 +372,7 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
             const uint32_t v = ld_relaxed_u32(status + (size_t)(j - 1) * 256 + d);
             if (v & kStPrefix) { excl += v & kStMask; break; }
             if (v & kStCount) { excl += v & kStMask; --j; }
+            else __nanosleep(40);          // the tile before has not published yet: do not hog the issue slots
         }
         if (tile > 0) st_relaxed_u32(row + d, (excl + run) | kStPrefix);
         gbase[d] = __ldg(digit_base + d) + excl - dstart;
@@ -841,6 +845,8 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
     src.owner_mask = src.owner_rank = src.owner_shift = 0;
     src.drop = 0;
+    src.rated_mask = 0;
+    for (int i = 0; i < 6; ++i) if (src.modes.col[i] >= 0) src.rated_mask |= 1u << i;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
     if (buf < 0) return buf;
 
@@ -892,6 +898,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     rsrc.slots_magic = 0ull;   // unused: keys are read as they are
     rsrc.owner_mask = rsrc.owner_rank = rsrc.owner_shift = 0;
     rsrc.drop = 0;
+    rsrc.rated_mask = 0;
     buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s, ctx->sm_count);
     if (buf < 0) return buf;
     TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
@@ -961,6 +968,8 @@ int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
     src.owner_mask = src.owner_rank = src.owner_shift = 0;
     src.drop = 0;
+    src.rated_mask = 0;
+    for (int i = 0; i < 6; ++i) if (src.modes.col[i] >= 0) src.rated_mask |= 1u << i;
     // sharded: link only the players this rank owns, by local index; every other slot leaves
     // the sort in pass 0 and keeps the fill value, so an element-wise MIN over the ranks'
     // pred arrays assembles the complete links (owned entries are < 2^31 or TS_NONE = -1)
