@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
     const double tau2 = a.prm.tau * a.prm.tau;
     const double beta2 = a.prm.beta * a.prm.beta;
     const double tb2 = tau2 + beta2;
+    const double margin_full = a.prm.draw_margin[P];
     const uint32_t n_rounds = __ldcg(&a.info->n_rounds);
     const bool want_order = a.out.quality || a.out.out_shared || a.out.out_delta || a.out.out_queue || a.out.status;
     unsigned long long generation = 0;
@@ -234,7 +235,7 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
             const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
             int status = TS_ST_OK;
             if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
-            const double margin = a.prm.draw_margin[n];
+            const double margin = n == P ? margin_full : a.prm.draw_margin[n];   // ragged teams are rare
 
             double v_s = 0.0, w_s = 0.0, rc_s = 0.0, v_q, w_q;
             if (SHARED) {

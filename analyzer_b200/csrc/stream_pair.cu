@@ -76,6 +76,10 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
     const double tau2 = a.prm.tau * a.prm.tau;
     const double beta2 = a.prm.beta * a.prm.beta;
     const double tb2 = tau2 + beta2;
+    const double margin_full = a.prm.draw_margin[P];
+    uint32_t rated_mask = 0;
+#pragma unroll
+    for (int i = 0; i < 6; ++i) rated_mask |= a.modes.col[i] >= 0 ? (1u << i) : 0u;
     const uint32_t n_tiles = (a.n_matches + W - 1) / W;
     const uint32_t stride = gridDim.x * kWarps;
     const uint32_t first_tile = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
@@ -93,7 +97,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
         const uint32_t m = base + grp;
         const uint32_t meta = (uint32_t)grp < cnt ? stage.meta[cur][grp] : (15u << TS_META_MODE_SHIFT);
         const uint32_t mode = (meta >> TS_META_MODE_SHIFT) & 15u;
-        const bool skip_mode = mode >= 6u || a.modes.col[mode & 7u] < 0;
+        const bool skip_mode = ((rated_mask >> mode) & 1u) == 0u;
         const bool gated = skip_mode || (meta & (TS_META_AFK | TS_META_INVALID)) != 0u;
         const bool live = (uint32_t)grp < cnt && !gated;
         if ((uint32_t)grp < cnt && gated && lane == 0) {     // rater.py:83-85,102-106: outputs only
@@ -179,7 +183,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
                     const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
                     int status = TS_ST_OK;
                     if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
-                    const double margin = a.prm.draw_margin[n];
+                    const double margin = n == P ? margin_full : a.prm.draw_margin[n];   // ragged teams are rare: no indexed load on the hot path
                     double v_s = 0.0, w_s = 0.0, v_q = 0.0, w_q = 0.0;
                     const double rc_s = rsqrt(c2_s), rc_q = rsqrt(c2_q);
                     if (status == TS_ST_OK &&
