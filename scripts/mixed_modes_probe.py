@@ -1,0 +1,57 @@
+"""A worker.py-like batch at config-2 size: 10M 3v3 matches over 1M players whose game
+mode varies from match to match (40 % ranked, 30 % casual, 20 % blitz, 10 % br), rated
+against the faithful 8-pair table.  Both paths, each phase timed on the device."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from analyzer_b200 import engine
+from analyzer_b200 import _lib as L
+
+n, u = int(os.environ.get("N", 10_000_000)), int(os.environ.get("U", 1_000_000))
+dev = torch.device("cuda", 0)
+r = engine.Rater(engine.Env(), 0)
+gen = engine.make_gen(0xA11CE002, u, slots=6, mode=1)
+ids, meta = engine.gen_matches(gen, 0, n, dev)
+g = torch.Generator(device=dev)
+g.manual_seed(7)
+x = torch.rand(n, device=dev, generator=g)
+mode = torch.where(x < 0.4, 1, torch.where(x < 0.7, 0, torch.where(x < 0.9, 2, 3))).to(torch.int32)
+meta = (meta & ~0xF0) | (mode << 4)
+one = engine.gen_table(0xA11CE002, 0, u, dev)
+tab0 = torch.full((u, 8, 2), float("nan"), dtype=torch.float64, device=dev)
+tab0[:, 0] = one[:, 0]                       # shared stored, queues NULL (first touch copies the shared pair)
+tab = tab0.clone()
+pt = engine.PlayerTable(tab, 0, [1, 2, 3, 4, 5, 6])
+ev = lambda: torch.cuda.Event(enable_timing=True)
+
+
+def timed(fn, reps=3):
+    best = 1e9
+    for _ in range(reps):
+        tab.copy_(tab0)
+        e0, e1 = ev(), ev()
+        e0.record()
+        fn()
+        e1.record()
+        torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    return best
+
+
+state = {}
+t_link = timed(lambda: state.__setitem__("links", r.link_pred_queues(ids, meta, u, pt.mode_cols)))
+pred, pred_q = state["links"]
+print("link (two arrays): %.3f ms" % t_link, flush=True)
+for lanes in (2, 4):
+    t = timed(lambda: r.rate_stream(pt, ids, meta, pred, None, lanes, pred_queue=pred_q))
+    print("stream lanes=%d: rate %.3f ms, link + rate %.3f ms, %.3g matches/s" % (lanes, t, t + t_link, n / (t + t_link) * 1e3),
+          flush=True)
+ref = tab.clone()
+t_sched = timed(lambda: state.__setitem__("sch", r.schedule(ids, meta, u, pt.mode_cols)))
+sch = state["sch"]
+t = timed(lambda: r.rate(pt, sch, None, 2))
+print("rounds: schedule %.3f ms (R = %d), rate %.3f ms, total %.3f ms, %.3g matches/s" % (
+    t_sched, sch.n_rounds, t, t + t_sched, n / (t + t_sched) * 1e3), flush=True)
+d = (torch.nan_to_num(tab, nan=0.0) - torch.nan_to_num(ref, nan=0.0)).abs().max().item()
+print("max |stream - rounds| = %.3g, NaN pattern equal: %s, errors %d" % (
+    d, bool(torch.equal(torch.isnan(tab), torch.isnan(ref))), r.error_count()))
