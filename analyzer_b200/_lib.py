@@ -27,7 +27,7 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_reset_errors", "ts_gen_matches", "ts_gen_table",
            "ts_schedule_static", "ts_schedule_static_max_slot_entries",
            "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream",
-           "ts_stream_stalled", "ts_link_pred_queues", "ts_rate_stream_queues_workspace_bytes", "ts_rate_stream_queues",
+           "ts_stream_stalled", "ts_rate_stream_table_workspace_bytes",
            "ts_seed_table", "ts_link_pred_sharded", "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_rate_stream_sharded"]
 
 
@@ -120,14 +120,8 @@ def lib():
         L.ts_rate_stream.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p,
                                      C.c_int64, C.c_int32, C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32,
                                      C.c_void_p, C.c_int64, C.c_void_p]
-        L.ts_link_pred_queues.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
-                                          C.POINTER(C.c_int8), C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                          C.c_void_p, C.c_int64, C.c_void_p]
-        L.ts_rate_stream_queues_workspace_bytes.restype = C.c_int64
-        L.ts_rate_stream_queues_workspace_bytes.argtypes = [C.c_int64, C.c_int32]
-        L.ts_rate_stream_queues.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
-                                            C.c_int64, C.c_int32, C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32,
-                                            C.c_void_p, C.c_int64, C.c_void_p]
+        L.ts_rate_stream_table_workspace_bytes.restype = C.c_int64
+        L.ts_rate_stream_table_workspace_bytes.argtypes = [C.POINTER(TsTable)]
         L.ts_link_pred_sharded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
                                            C.POINTER(C.c_int8), C.c_int64, C.c_void_p, C.c_void_p, C.c_int32,
                                            C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]

@@ -55,10 +55,6 @@ struct KeySrc {
     uint32_t owner_mask, owner_rank, owner_shift;
     int drop;
     uint32_t rated_mask;   // bit m set: game mode m is rated (a register test instead of indexing modes.col)
-    // tagged keys (linking for several queue columns): key = player << 3 | table column of the
-    // match's game mode; the sort skips the tag bits, so runs stay per player in stream order
-    uint32_t tag_shift;    // 0 or 3
-    uint32_t col_nibbles;  // 4 bits per game mode: its table column
 };
 
 __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
@@ -69,10 +65,7 @@ __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
         const bool gated = ((src.rated_mask >> ((m >> TS_META_MODE_SHIFT) & 15u)) & 1u) == 0u ||
                            (m & (TS_META_AFK | TS_META_INVALID)) != 0u;
         if (k == TS_EMPTY_SLOT || gated || (k & src.owner_mask) != src.owner_rank) k = src.sentinel;
-        else {
-            k >>= src.owner_shift;
-            if (src.tag_shift) k = (k << 3) | ((src.col_nibbles >> (((m >> TS_META_MODE_SHIFT) & 7u) * 4u)) & 7u);
-        }
+        else k >>= src.owner_shift;
     }
     return k;
 }
@@ -267,7 +260,7 @@ k_radix_hist_all(KeySrc src, uint32_t n, int passes, uint32_t *ghist)
     for (uint32_t idx = blockIdx.x * kSortBlock + threadIdx.x; idx < n; idx += gridDim.x * kSortBlock) {
         const uint32_t k = load_key(src, idx);
         if (src.drop && k == src.sentinel) continue;
-        for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(k >> (8 * p + src.tag_shift)) & 255u], 1u);
+        for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(k >> (8 * p)) & 255u], 1u);
     }
     __syncthreads();
     for (int i = threadIdx.x; i < passes * 256; i += kSortBlock) {
@@ -594,16 +587,10 @@ k_permute(const uint32_t *ids, const uint32_t *meta, const uint32_t *order, uint
 // slot index is random; it is done in passes over destination ranges small
 // enough to stay in L2, so every 32-byte sector of pred is written back to HBM
 // once, complete, instead of being read-modified-written eight times.
-// TAGGED (keys = player << 3 | queue column, sorted by player): also pred_q[v] = the
-// previous rated match of the same player in the same queue column -- the version the
-// player's queue pair carries when this match may read it (rater.py:124-130).
-template <bool TAGGED>
 __global__ void __launch_bounds__(256)
 k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n_in, const uint32_t *n_dev, unsigned long long slots_magic,
-       uint32_t sentinel, uint32_t v_lo, uint32_t v_hi, uint32_t seq_base, const uint32_t *last, uint32_t *pred,
-       const uint32_t *last_q, uint32_t *pred_q)
+       uint32_t sentinel, uint32_t v_lo, uint32_t v_hi, uint32_t seq_base, const uint32_t *last, uint32_t *pred)
 {
-    constexpr int T = TAGGED ? 3 : 0;
     const uint32_t n = n_dev ? __ldg(n_dev) : n_in;
     // four consecutive sorted entries per thread: two 16-byte streaming loads plus the
     // entry just before them, all issued up front
@@ -629,16 +616,13 @@ k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n_in, const uint32_t
     for (int j = 1; j <= 4; ++j) {
         const uint32_t i = i0 + j - 1;
         if (i >= n || v[j] < v_lo || v[j] >= v_hi || k[j] >= sentinel) continue;   // other pass / empty slot / gated match
-        const uint32_t player = k[j] >> T;
         const uint32_t m = (uint32_t)__umul64hi((unsigned long long)v[j], slots_magic);
-        const bool same_player = (k[j - 1] >> T) == player;
-        const uint32_t m_before = (uint32_t)__umul64hi((unsigned long long)v[j - 1], slots_magic);
         uint32_t pm = TS_NONE;      // local index of the previous match in this window
-        if (same_player) {
-            pm = m_before;
+        if (k[j - 1] == k[j]) {
+            pm = (uint32_t)__umul64hi((unsigned long long)v[j - 1], slots_magic);
             if (pm == m) {          // the player is listed twice in this match: walk back to a different match
                 pm = TS_NONE;
-                for (uint32_t q = i - 1; q > 0 && (__ldcs(keys + q - 1) >> T) == player; --q) {
+                for (uint32_t q = i - 1; q > 0 && __ldcs(keys + q - 1) == k[j]; --q) {
                     uint32_t mq = (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + q - 1), slots_magic);
                     if (mq != m) { pm = mq; break; }
                 }
@@ -646,52 +630,23 @@ k_pred(const uint32_t *keys, const uint32_t *vals, uint32_t n_in, const uint32_t
         }
         // stream-wide match numbers; a player's first match of this window continues the
         // chain at the tail carried over from earlier windows
-        pred[v[j]] = pm != TS_NONE ? seq_base + pm : (last ? __ldg(last + player) : TS_NONE);
-        if (TAGGED) {
-            uint32_t qm = TS_NONE;
-            if (k[j - 1] == k[j] && m_before != m) {
-                qm = m_before;      // the usual case: the player's previous match was in the same queue
-            } else if (same_player) {
-                // walk back over the player's run to the nearest entry of this queue column
-                for (uint32_t q = i - 1; q > 0; --q) {
-                    const uint32_t kq = __ldg(keys + q - 1);
-                    if ((kq >> T) != player) break;
-                    if (kq != k[j]) continue;
-                    uint32_t mq = (uint32_t)__umul64hi((unsigned long long)__ldg(vals + q - 1), slots_magic);
-                    if (mq != m) { qm = mq; break; }
-                }
-            }
-            pred_q[v[j]] = qm != TS_NONE ? seq_base + qm : (last_q ? __ldg(last_q + k[j]) : TS_NONE);
-        }
+        pm = pm != TS_NONE ? seq_base + pm : (last ? __ldg(last + k[j]) : TS_NONE);
+        pred[v[j]] = pm;
     }
 }
 
 // after all pred passes: the last slot of every player's run becomes the carried tail
-// (TAGGED: and the last slot of every (player, queue column) the tail of that column)
-template <bool TAGGED>
 __global__ void __launch_bounds__(256)
 k_last_update(const uint32_t *keys, const uint32_t *vals, uint32_t n_in, const uint32_t *n_dev,
-              unsigned long long slots_magic, uint32_t sentinel, uint32_t seq_base, uint32_t *last, uint32_t *last_q)
+              unsigned long long slots_magic, uint32_t sentinel, uint32_t seq_base, uint32_t *last)
 {
-    constexpr int T = TAGGED ? 3 : 0;
     const uint32_t n = n_dev ? __ldg(n_dev) : n_in;
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t k = __ldcs(keys + i);
     if (k >= sentinel) return;
-    const uint32_t player = k >> T;
-    const uint32_t seq = seq_base + (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + i), slots_magic);
-    const uint32_t k_next = i + 1 < n ? __ldcs(keys + i + 1) : ~k;
-    if (last && (k_next >> T) != player) last[player] = seq;
-    if (TAGGED && last_q) {
-        bool tail = true;       // no later entry of this player's run has the same queue column
-        for (uint32_t q = i + 1; q < n; ++q) {
-            const uint32_t kq = __ldg(keys + q);
-            if ((kq >> T) != player) break;
-            if (kq == k) { tail = false; break; }
-        }
-        if (tail) last_q[k] = seq;
-    }
+    if (i + 1 < n && __ldcs(keys + i + 1) == k) return;
+    last[k] = seq_base + (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + i), slots_magic);
 }
 
 struct Workspace {
@@ -756,10 +711,10 @@ int radix_sort_3kernel(const KeySrc &src0, uint32_t n, int bits, Workspace &w, c
         if (p > 0) { src.keys = w.keys[cur]; src.from_ids = 0; vals_in = w.vals[cur]; }
         int dst = (cur + 1) & 1;
         if (cur < 0) dst = 0;
-        k_radix_hist<<<n_blocks, kSortBlock, 0, stream>>>(src, n, p * 8 + (int)src0.tag_shift, w.hist, n_blocks);
+        k_radix_hist<<<n_blocks, kSortBlock, 0, stream>>>(src, n, p * 8, w.hist, n_blocks);
         k_radix_scan_rows<<<256, 1024, 0, stream>>>(w.hist, n_blocks, w.totals);
         k_radix_scan_totals<<<1, 256, 0, stream>>>(w.totals);
-        k_radix_scatter<<<n_blocks, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n, p * 8 + (int)src0.tag_shift, w.hist,
+        k_radix_scatter<<<n_blocks, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n, p * 8, w.hist,
                                                              w.totals, n_blocks, w.keys[dst], w.vals[dst]);
         cur = dst;
     }
@@ -805,11 +760,11 @@ int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStrea
             cudaMemsetAsync(ticket, 0, 4, stream) != cudaSuccess)
             return ts_cuda_fail(cudaGetLastError(), "memset");
         if (p == 0 && src0.drop)
-            k_radix_onesweep<true><<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, 1, n, nullptr, (int)src0.tag_shift, ghist, w.hist, ticket,
+            k_radix_onesweep<true><<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, 1, n, nullptr, 0, ghist, w.hist, ticket,
                                                                        w.keys[dst], w.vals[dst]);
         else
             k_radix_onesweep<false><<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n,
-                                                                        (p > 0 && src0.drop) ? n_dev : nullptr, p * 8 + (int)src0.tag_shift,
+                                                                        (p > 0 && src0.drop) ? n_dev : nullptr, p * 8,
                                                                         ghist + p * 256, w.hist, ticket, w.keys[dst],
                                                                         w.vals[dst]);
         cur = dst;
@@ -891,7 +846,6 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     src.owner_mask = src.owner_rank = src.owner_shift = 0;
     src.drop = 0;
     src.rated_mask = 0;
-    src.tag_shift = src.col_nibbles = 0;
     for (int i = 0; i < 6; ++i) if (src.modes.col[i] >= 0) src.rated_mask |= 1u << i;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
     if (buf < 0) return buf;
@@ -945,7 +899,6 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     rsrc.owner_mask = rsrc.owner_rank = rsrc.owner_shift = 0;
     rsrc.drop = 0;
     rsrc.rated_mask = 0;
-    rsrc.tag_shift = rsrc.col_nibbles = 0;
     buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s, ctx->sm_count);
     if (buf < 0) return buf;
     TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
@@ -971,8 +924,7 @@ extern "C" int64_t ts_link_workspace_bytes(int64_t n_matches, int32_t slots)
 namespace {
 int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
                    int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last, uint32_t *pred,
-                   void *workspace, int64_t workspace_bytes, void *stream, int32_t rank, int32_t n_shards,
-                   bool tagged = false, uint32_t *last_q = nullptr, uint32_t *pred_q = nullptr)
+                   void *workspace, int64_t workspace_bytes, void *stream, int32_t rank, int32_t n_shards)
 {
     if (seq_base < 0 || seq_base + n_matches >= 0xFFFFFFFFll) {
         ts_set_error("ts_link_pred: stream-wide match numbers must stay below 2^32 - 1");
@@ -986,14 +938,6 @@ int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64
         (uint64_t)n_matches * (uint64_t)slots >= 0xFFFF0000ull || n_players < 1 || n_players >= 0xFFFFFFFFll) {
         ts_set_error("ts_link_pred: bad sizes (n_matches * slots must stay below 2^32 - 2^16)");
         return TS_E_ARG;
-    }
-    if (tagged) {
-        if (n_players >= (1ll << 29) || n_shards > 1) {
-            ts_set_error("ts_link_pred_queues: at most 2^29 - 1 players, one GPU");
-            return TS_E_UNSUPPORTED;
-        }
-        for (int i = 0; i < 6; ++i)
-            if (mode_col[i] > 7) { ts_set_error("ts_link_pred_queues: queue columns must be below 8"); return TS_E_ARG; }
     }
     if (n_matches == 0) return 0;
     if (workspace_bytes < ts_link_workspace_bytes(n_matches, slots)) {
@@ -1025,13 +969,7 @@ int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64
     src.owner_mask = src.owner_rank = src.owner_shift = 0;
     src.drop = 0;
     src.rated_mask = 0;
-    src.tag_shift = src.col_nibbles = 0;
     for (int i = 0; i < 6; ++i) if (src.modes.col[i] >= 0) src.rated_mask |= 1u << i;
-    if (tagged) {
-        src.tag_shift = 3;
-        for (int i = 0; i < 6; ++i) if (src.modes.col[i] >= 0) src.col_nibbles |= (uint32_t)src.modes.col[i] << (4 * i);
-        src.sentinel = (uint32_t)n_players << 3;
-    }
     // sharded: link only the players this rank owns, by local index; every other slot leaves
     // the sort in pass 0 and keeps the fill value, so an element-wise MIN over the ranks'
     // pred arrays assembles the complete links (owned entries are < 2^31 or TS_NONE = -1)
@@ -1056,27 +994,16 @@ int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64
     // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2.
     // Every pass re-reads the sorted pairs, so this only pays for a handful of passes; a window
     // too large for that (more than 128 Mi slot entries) takes one pass and the read-modify-writes.
-    // (two link arrays: half the range)
-    uint32_t range = tagged ? 8u << 20 : 16u << 20;
-    if (tagged) TS_CUDA(cudaMemsetAsync(pred_q, 0xFF, (size_t)np * 4, s));
+    uint32_t range = 16u << 20;
     if (((uint64_t)np + range - 1) / range > 8) range = 0xFFFFFFFFu;
     for (uint64_t lo = 0; lo < np; lo += range) {
         uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);
-        if (tagged)
-            k_pred<true><<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic,
-                                                            src.sentinel, (uint32_t)lo, hi, (uint32_t)seq_base, last,
-                                                            pred, last_q, pred_q);
-        else
-            k_pred<false><<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic,
-                                                             src.sentinel, (uint32_t)lo, hi, (uint32_t)seq_base, last,
-                                                             pred, nullptr, nullptr);
+        k_pred<<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic, src.sentinel,
+                                                  (uint32_t)lo, hi, (uint32_t)seq_base, last, pred);
     }
-    if (tagged && (last || last_q))
-        k_last_update<true><<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic,
-                                                             src.sentinel, (uint32_t)seq_base, last, last_q);
-    else if (last)
-        k_last_update<false><<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic,
-                                                              src.sentinel, (uint32_t)seq_base, last, nullptr);
+    if (last)
+        k_last_update<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic,
+                                                       src.sentinel, (uint32_t)seq_base, last);
     TS_CUDA(cudaGetLastError());
     return 0;
 }
@@ -1101,21 +1028,4 @@ extern "C" int ts_link_pred_sharded(ts_ctx *ctx, const uint32_t *ids, const uint
     }
     return link_pred_impl(ctx, ids, meta, n_matches, slots, n_players, mode_col, seq_base, last, pred, workspace,
                           workspace_bytes, stream, rank, n_shards);
-}
-
-extern "C" int ts_link_pred_queues(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches,
-                                   int32_t slots, int64_t n_players, const int8_t mode_col[16], int64_t seq_base,
-                                   uint32_t *last, uint32_t *last_queue, uint32_t *pred, uint32_t *pred_queue,
-                                   void *workspace, int64_t workspace_bytes, void *stream)
-{
-    if (n_matches > 0 && !pred_queue) {
-        ts_set_error("ts_link_pred_queues: null argument");
-        return TS_E_ARG;
-    }
-    if ((last == nullptr) != (last_queue == nullptr)) {
-        ts_set_error("ts_link_pred_queues: carried tails come in pairs (last and last_queue, or neither)");
-        return TS_E_ARG;
-    }
-    return link_pred_impl(ctx, ids, meta, n_matches, slots, n_players, mode_col, seq_base, last, pred, workspace,
-                          workspace_bytes, stream, 0, 1, true, last_queue, pred_queue);
 }

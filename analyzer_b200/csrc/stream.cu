@@ -307,8 +307,39 @@ int dispatch_l(ts_ctx *ctx, const StreamArgs &a, int lanes, cudaStream_t s)
 
 }  // namespace
 
-// 64 bytes per player covers both row formats (one pair: 32, shared + queue pair: 64)
+// 64 bytes per player covers two row formats (one pair: 32, shared + one queue pair: 64)
 extern "C" int64_t ts_rate_stream_workspace_bytes(int64_t n_players) { return n_players < 0 ? TS_E_ARG : n_players * 64; }
+
+int64_t ts_rate_stream_queues_row_bytes(const ts_table *table);
+int ts_rate_stream_queues_impl(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
+                               const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
+                               const ts_outputs *outputs, int32_t lanes_per_match, void *workspace, cudaStream_t s);
+
+namespace {
+// rated queue columns of a table: how many distinct ones, and the last one seen
+int rated_queue_columns(const ts_table *table, int *last_col)
+{
+    uint32_t seen = 0;
+    int n = 0;
+    for (int i = 0; i < 6; ++i) {
+        const int c = table->mode_col[i];
+        if (c < 0 || c > 15) continue;
+        if (!((seen >> c) & 1u)) { seen |= 1u << c; ++n; }
+        if (last_col) *last_col = c;
+    }
+    return n;
+}
+}  // namespace
+
+// any layout ts_rate_stream takes: 32 (one pair), 64 (shared + one queue) or 64 + 32 per rated
+// queue column (shared + several queues) bytes per player
+extern "C" int64_t ts_rate_stream_table_workspace_bytes(const ts_table *table)
+{
+    if (!table || table->n_players < 0) return TS_E_ARG;
+    if (table->shared_col < 0) return table->n_players * 32;
+    if (rated_queue_columns(table, nullptr) <= 1) return table->n_players * 64;
+    return table->n_players * ts_rate_stream_queues_row_bytes(table);
+}
 
 int ts_rate_stream_pair_impl(ts_ctx *ctx, const ts_table *table, int qcol, const uint32_t *ids, const uint32_t *meta,
                              const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
@@ -336,20 +367,20 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
         ts_set_error("ts_rate_stream: null argument");
         return TS_E_ARG;
     }
-    // layouts: one pair per player (row_pairs == 1, shared_col == -1), or shared pair + ONE queue column
-    int qcol = -1;
-    bool one_queue = true;
+    // layouts: one pair per player (row_pairs == 1, shared_col == -1), or a shared pair plus queue columns
     for (int i = 0; i < 6; ++i) {
         const int c = table->mode_col[i];
-        if (c < 0) continue;
-        if (c >= table->row_pairs || c == table->shared_col) { ts_set_error("ts_rate_stream: bad mode_col[%d]", i); return TS_E_ARG; }
-        if (qcol >= 0 && c != qcol) one_queue = false;
-        qcol = c;
+        if (c >= 0 && (c >= table->row_pairs || c > 15 || c == table->shared_col)) {
+            ts_set_error("ts_rate_stream: bad mode_col[%d]", i);
+            return TS_E_ARG;
+        }
     }
+    int qcol = -1;
+    const int n_queues = rated_queue_columns(table, &qcol);
     const bool pair = table->shared_col >= 0;
-    if (pair ? (!one_queue || qcol < 0 || table->shared_col >= table->row_pairs) : (table->row_pairs != 1)) {
+    if (pair ? (n_queues < 1 || table->shared_col >= table->row_pairs) : (table->row_pairs != 1)) {
         ts_set_error("ts_rate_stream: the table must be a single-pair ladder (row_pairs == 1, shared_col == -1) or a "
-                     "shared pair plus ONE queue column; batches rating several queue columns use ts_rate");
+                     "shared pair plus at least one rated queue column");
         return TS_E_UNSUPPORTED;
     }
     if (slots != 6 && slots != 10) {
@@ -360,13 +391,16 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
         ts_set_error("ts_rate_stream: n_matches outside [0, 2^32 - 1)");
         return TS_E_ARG;
     }
-    if (workspace_bytes < table->n_players * (pair ? 64 : 32)) {
+    if (workspace_bytes < ts_rate_stream_table_workspace_bytes(table)) {
         ts_set_error("ts_rate_stream: workspace too small (%lld < %lld bytes)", (long long)workspace_bytes,
-                     (long long)table->n_players * (pair ? 64 : 32));
+                     (long long)ts_rate_stream_table_workspace_bytes(table));
         return TS_E_WORKSPACE;
     }
     TS_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
+    if (pair && n_queues > 1)
+        return ts_rate_stream_queues_impl(ctx, table, ids, meta, pred, n_matches, slots, seq_base, flags, outputs,
+                                          lanes_per_match, workspace, s);
     if (pair)
         return ts_rate_stream_pair_impl(ctx, table, qcol, ids, meta, pred, n_matches, slots, seq_base, flags, outputs,
                                         lanes_per_match, workspace, s);

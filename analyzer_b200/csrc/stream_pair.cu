@@ -11,13 +11,23 @@
 // all eight carry the number of the last match that wrote the row; both pairs are
 // always read and written together, so one version covers them.
 //
-// MULTI (ts_rate_stream_queues): the batch rates matches of several game modes against
-// a table with several queue columns (the faithful 8-pair row).  A player's shared
-// pair is rewritten by every match of the player, a queue pair only by the matches
-// of that queue, so the two carry different versions: the workspace mirrors the
-// table (row_pairs x 4 words per player, every pair with its own version) and a
-// slot waits for its shared pair at pred (previous match of the player) and for its
-// queue pair at pred_queue (previous match of the player in the same queue column).
+// MULTI: the batch rates matches of several game modes against a table with several
+// queue columns (the faithful 8-pair row; worker.py:176-192 rates all modes in one
+// chronological stream).  A player's shared pair is rewritten by every match of the
+// player, a queue pair only by the matches of that queue, so a queue pair cannot carry
+// the number of the player's previous match.  Instead every queue pair carries an
+// ORDINAL -- how many matches of that queue have written it -- and the ordinals of all
+// of a player's queues travel with the shared pair:
+//   words 0..3   shared pair, version = last match of the player            (as above)
+//   words 4..5   ordinals of queues 0..2 | 3..5, 10 bits each, same version
+//   words 8+4j.. pair of queue j (compact index over the rated columns), version =
+//                its ordinal
+// A slot reads the three pieces in one poll: shared and ordinals must carry pred, the
+// queue pair must carry the ordinal the second word names.  The match then writes the
+// queue pair under ordinal + 1, and shared pair and ordinals under its own number.
+// No second link array, no fence: every 8-byte word still validates itself.  The queue
+// pair's 10-bit tag distinguishes ordinal k from k - 1 (and anything less than 1024
+// writes older); a load at gpu scope cannot be staler than that, L2 holds the one copy.
 #include "stream_common.cuh"
 
 namespace {
@@ -29,16 +39,14 @@ constexpr int kBlock = 256;
 
 struct PairArgs {
     ts_params prm;
-    unsigned long long *vt;       // 8 words per player
+    unsigned long long *vt;       // row_words words per player
     const double *seed;
-    ModeCols modes;               // >= 0: the mode is rated (all rated modes share the one queue column)
+    ModeCols modes;               // >= 0: the mode is rated
     const uint32_t *ids;
     const uint32_t *meta;
     const uint32_t *pred;
-    const uint32_t *pred_q;       // MULTI only
-    uint32_t row_words;           // words per player row: 8, MULTI: 4 * row_pairs
-    uint32_t shared_word;         // word offset of the shared pair in a row: 0, MULTI: 4 * shared_col
-    uint32_t col_nibbles;         // MULTI: 4 bits per game mode, its table column
+    uint32_t row_words;           // words per player row: 8, MULTI: 8 + 4 * (rated queue columns)
+    uint32_t queue_nibbles;       // MULTI: 4 bits per game mode, the compact index of its queue column
     uint32_t n_matches;
     uint32_t seq_base;
     uint32_t sleep_ns;
@@ -47,16 +55,27 @@ struct PairArgs {
     unsigned long long *ctrl;
 };
 
-template <int P, int W, bool MULTI>
+constexpr uint32_t kOrdMask = 1023u;
+
+__device__ __forceinline__ void ld_ord(const unsigned long long *p, unsigned long long (&w)[2])
+{
+    asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(p) : "memory");
+}
+__device__ __forceinline__ void st_ord(unsigned long long *p, uint32_t lo, uint32_t hi, uint32_t ver)
+{
+    const unsigned long long v = (unsigned long long)ver << 32;
+    asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v | lo), "l"(v | hi) : "memory");
+}
+
+template <int P, int W>
 struct WarpStage {
     uint32_t ids[2][W * P];
     uint32_t pred[2][W * P];
-    uint32_t pred_q[2][MULTI ? W * P : 2];
     uint32_t meta[2][W];
 };
 
-template <int P, int W, bool MULTI>
-__device__ __forceinline__ void stage_warp_tile(WarpStage<P, W, MULTI> &st, int b, const PairArgs &a, uint32_t tile, int wl)
+template <int P, int W>
+__device__ __forceinline__ void stage_warp_tile(WarpStage<P, W> &st, int b, const PairArgs &a, uint32_t tile, int wl)
 {
     const uint32_t base = tile * W;
     const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
@@ -64,7 +83,6 @@ __device__ __forceinline__ void stage_warp_tile(WarpStage<P, W, MULTI> &st, int 
     for (uint32_t i = wl; i < cnt * (P / 2); i += 32) {
         cp_async_8(&st.ids[b][2 * i], src_i + 2 * i);
         cp_async_8(&st.pred[b][2 * i], src_p + 2 * i);
-        if (MULTI) cp_async_8(&st.pred_q[b][2 * i], a.pred_q + (size_t)base * P + 2 * i);
     }
     for (uint32_t i = wl; i < cnt; i += 32) cp_async_4(&st.meta[b][i], a.meta + base + i);
 }
@@ -76,12 +94,12 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
     constexpr int SPL = (P + L - 1) / L;
     constexpr int HALF = P / 2;
     constexpr int kWarps = kBlock / 32;
-    __shared__ __align__(16) WarpStage<P, W, MULTI> stage_all[kWarps];
+    __shared__ __align__(16) WarpStage<P, W> stage_all[kWarps];
 
     const int wl = threadIdx.x & 31;
     const int lane = wl % L;
     const int grp = wl / L;
-    WarpStage<P, W, MULTI> &stage = stage_all[threadIdx.x >> 5];
+    WarpStage<P, W> &stage = stage_all[threadIdx.x >> 5];
     const uint32_t gmask = L == 32 ? 0xFFFFFFFFu : (((1u << L) - 1u) << (grp * L));
     const double tau2 = a.prm.tau * a.prm.tau;
     const double beta2 = a.prm.beta * a.prm.beta;
@@ -95,13 +113,13 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
     const uint32_t first_tile = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
 
     int pf = 0;
-    if (first_tile < n_tiles) stage_warp_tile<P, W, MULTI>(stage, pf, a, first_tile, wl);
+    if (first_tile < n_tiles) stage_warp_tile<P, W>(stage, pf, a, first_tile, wl);
     for (uint32_t tile = first_tile; tile < n_tiles; tile += stride) {
         cp_async_wait_all();
         __syncwarp();
         const int cur = pf;
         pf ^= 1;
-        if (tile + stride < n_tiles) stage_warp_tile<P, W, MULTI>(stage, pf, a, tile + stride, wl);
+        if (tile + stride < n_tiles) stage_warp_tile<P, W>(stage, pf, a, tile + stride, wl);
         const uint32_t base = tile * W;
         const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
         const uint32_t m = base + grp;
@@ -118,11 +136,13 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
         const int first = rank1 < rank0 ? 1 : 0;
         const bool is_draw = rank0 == rank1;
 
-        // word offsets of this match's two pairs in a player row
+        // this match's queue pair in a player row: compact queue index qj, word offset q_word
         const uint32_t row_words = MULTI ? a.row_words : 8u;
-        const uint32_t s_word = MULTI ? a.shared_word : 0u;
-        const uint32_t q_word = MULTI ? ((a.col_nibbles >> ((mode & 7u) * 4u)) & 7u) * 4u : 4u;
-        uint32_t pid[SPL], want[SPL], want_q[SPL];
+        const uint32_t qj = MULTI ? (a.queue_nibbles >> ((mode & 7u) * 4u)) & 7u : 0u;
+        const uint32_t q_word = MULTI ? 8u + 4u * qj : 4u;
+        const uint32_t ord_shift = 10u * (qj % 3u);
+        uint32_t pid[SPL], want[SPL];
+        uint32_t ord_lo[SPL], ord_hi[SPL];          // MULTI: the player's queue ordinals as read
         bool used[SPL], have[SPL];
         double s_mu[SPL], s_sg[SPL], q_mu[SPL], q_sg[SPL];   // the row as read (NaN = NULL)
 #pragma unroll
@@ -131,7 +151,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
             pid[k] = (live && s < P) ? stage.ids[cur][grp * P + s] : TS_EMPTY_SLOT;
             used[k] = pid[k] != TS_EMPTY_SLOT;
             want[k] = used[k] ? stage.pred[cur][grp * P + s] : TS_NONE;
-            want_q[k] = (MULTI && used[k]) ? stage.pred_q[cur][grp * P + s] : want[k];
+            ord_lo[k] = ord_hi[k] = 0u;
             have[k] = !used[k];
             s_mu[k] = 0.0; s_sg[k] = 1.0; q_mu[k] = 0.0; q_sg[k] = 1.0;
         }
@@ -149,9 +169,20 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
                     if (have[k]) continue;
                     unsigned long long ws[4], wq[4];
                     const unsigned long long *row = a.vt + (size_t)pid[k] * row_words;
-                    ld_row(row + s_word, ws);
+                    ld_row(row, ws);
                     ld_row(row + q_word, wq);
-                    if (row_has_version(ws, want[k]) && row_has_version(wq, want_q[k])) {
+                    bool ok;
+                    if (MULTI) {
+                        unsigned long long wo[2];
+                        ld_ord(row + 4, wo);
+                        const uint32_t ords = (uint32_t)wo[qj >= 3u ? 1 : 0];
+                        ok = row_has_version(ws, want[k]) && (uint32_t)(wo[0] >> 32) == want[k] &&
+                             (uint32_t)(wo[1] >> 32) == want[k] && row_has_version(wq, (ords >> ord_shift) & kOrdMask);
+                        ord_lo[k] = (uint32_t)wo[0]; ord_hi[k] = (uint32_t)wo[1];
+                    } else {
+                        ok = row_has_version(ws, want[k]) && row_has_version(wq, want[k]);
+                    }
+                    if (ok) {
                         have[k] = true;
                         s_mu[k] = row_mu(ws); s_sg[k] = row_sigma(ws);
                         q_mu[k] = row_mu(wq); q_sg[k] = row_sigma(wq);
@@ -224,8 +255,18 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
                             sq2 = sqrt(qi * (1.0 - (gq * rc_q) * w_q));
                         }
                         unsigned long long *row = a.vt + (size_t)pid[k] * row_words;
-                        st_row(row + s_word, ms2, ss2, a.seq_base + m);          // first: successors are waiting
-                        st_row(row + q_word, mq2, sq2, a.seq_base + m);
+                        st_row(row, ms2, ss2, a.seq_base + m);          // first: successors are waiting
+                        if (MULTI) {
+                            // the queue pair moves on to its next ordinal; the ordinals travel with the shared pair
+                            const bool upper = qj >= 3u;
+                            uint32_t word = upper ? ord_hi[k] : ord_lo[k];
+                            const uint32_t next = (((word >> ord_shift) & kOrdMask) + 1u) & kOrdMask;
+                            word = (word & ~(kOrdMask << ord_shift)) | (next << ord_shift);
+                            st_ord(row + 4, upper ? ord_lo[k] : word, upper ? word : ord_hi[k], a.seq_base + m);
+                            st_row(row + q_word, mq2, sq2, next);
+                        } else {
+                            st_row(row + 4, mq2, sq2, a.seq_base + m);
+                        }
                         if (status == TS_ST_OK) {
                             if (a.out.out_shared) __stcg(reinterpret_cast<double2 *>(a.out.out_shared) + o, make_double2(ms2, ss2));
                             if (a.out.out_delta)   // rater.py:150-153
@@ -275,21 +316,39 @@ k_vt_store_pair(const unsigned long long *vt, double *table, int row_pairs, int 
     row[qcol] = make_double2(row_mu(wq), row_sigma(wq));
 }
 
-// MULTI: every pair of the row, each with its own version (one thread per pair)
-__global__ void __launch_bounds__(256) k_vt_load_all(const double *table, unsigned long long *vt, int64_t n_pairs)
+// MULTI: table row [row_pairs][2] <-> shared pair, ordinals, the rated queue pairs
+// (col_of_queue: 4 bits per compact queue index, its table column)
+__global__ void __launch_bounds__(256)
+k_vt_load_queues(const double *table, int row_pairs, int shared_col, uint32_t col_of_queue, int n_queues,
+                 uint32_t row_words, unsigned long long *vt, int64_t n)
 {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_pairs) return;
-    const double2 r = reinterpret_cast<const double2 *>(table)[i];
-    st_row(vt + i * 4, r.x, r.y, TS_NONE);
+    if (i >= n) return;
+    const double2 *row = reinterpret_cast<const double2 *>(table) + i * row_pairs;
+    unsigned long long *out = vt + i * row_words;
+    const double2 sh = row[shared_col];
+    st_row(out, sh.x, sh.y, TS_NONE);
+    st_ord(out + 4, 0u, 0u, TS_NONE);
+    for (int j = 0; j < n_queues; ++j) {
+        const double2 q = row[(col_of_queue >> (4 * j)) & 15u];
+        st_row(out + 8 + 4 * j, q.x, q.y, 0u);
+    }
 }
-__global__ void __launch_bounds__(256) k_vt_store_all(const unsigned long long *vt, double *table, int64_t n_pairs)
+__global__ void __launch_bounds__(256)
+k_vt_store_queues(const unsigned long long *vt, double *table, int row_pairs, int shared_col, uint32_t col_of_queue,
+                  int n_queues, uint32_t row_words, int64_t n)
 {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_pairs) return;
+    if (i >= n) return;
+    double2 *row = reinterpret_cast<double2 *>(table) + i * row_pairs;
+    const unsigned long long *in = vt + i * row_words;
     unsigned long long w[4];
-    ld_row(vt + i * 4, w);
-    reinterpret_cast<double2 *>(table)[i] = make_double2(row_mu(w), row_sigma(w));
+    ld_row(in, w);
+    row[shared_col] = make_double2(row_mu(w), row_sigma(w));
+    for (int j = 0; j < n_queues; ++j) {
+        ld_row(in + 8 + 4 * j, w);
+        row[(col_of_queue >> (4 * j)) & 15u] = make_double2(row_mu(w), row_sigma(w));
+    }
 }
 
 template <int P, int L, bool MULTI>
@@ -308,19 +367,15 @@ int launch_pair(ts_ctx *ctx, const PairArgs &args, cudaStream_t stream)
 template <int P, bool MULTI>
 int dispatch_pair(ts_ctx *ctx, const PairArgs &a, int lanes, cudaStream_t s)
 {
-    // one lane per match stages a 32-match tile: with the second link array that is past the
-    // 48 KB of static shared memory for 5v5, and one lane is never the fast choice
-    if constexpr (!MULTI) {
-        if (lanes == 1) return launch_pair<P, 1, false>(ctx, a, s);
-    }
     switch (lanes) {
+    case 1: return launch_pair<P, 1, MULTI>(ctx, a, s);
     case 2: return launch_pair<P, 2, MULTI>(ctx, a, s);
     case 4: return launch_pair<P, 4, MULTI>(ctx, a, s);
     case 8: return launch_pair<P, 8, MULTI>(ctx, a, s);
     case 16: return launch_pair<P, 16, MULTI>(ctx, a, s);
     case 32: return launch_pair<P, 32, MULTI>(ctx, a, s);
     }
-    ts_set_error(MULTI ? "lanes_per_match must be 0,2,4,8,16 or 32 (got %d)" : "lanes_per_match must be 0,1,2,4,8,16 or 32 (got %d)", lanes);
+    ts_set_error("lanes_per_match must be 0,1,2,4,8,16 or 32 (got %d)", lanes);
     return TS_E_ARG;
 }
 
@@ -334,10 +389,8 @@ void fill_args(PairArgs &a, ts_ctx *ctx, const ts_table *table, const uint32_t *
     a.ids = ids;
     a.meta = meta;
     a.pred = pred;
-    a.pred_q = nullptr;
     a.row_words = 8;
-    a.shared_word = 0;
-    a.col_nibbles = 0;
+    a.queue_nibbles = 0;
     a.n_matches = (uint32_t)n_matches;
     a.seq_base = (uint32_t)seq_base;
     a.sleep_ns = stream_sleep_ns();
@@ -345,6 +398,34 @@ void fill_args(PairArgs &a, ts_ctx *ctx, const ts_table *table, const uint32_t *
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;
+}
+
+// compact index over the distinct rated queue columns of a table (ascending column order)
+struct QueueMap {
+    int n_queues;
+    uint32_t col_of_queue;    // 4 bits per compact index
+    uint32_t queue_nibbles;   // 4 bits per game mode
+};
+
+int map_queues(const ts_table *table, QueueMap &qm)
+{
+    qm.n_queues = 0;
+    qm.col_of_queue = qm.queue_nibbles = 0;
+    int index_of_col[16];
+    for (int c = 0; c < 16; ++c) index_of_col[c] = -1;
+    for (int c = 0; c < 16; ++c) {
+        bool rated = false;
+        for (int i = 0; i < 6; ++i) rated |= table->mode_col[i] == c;
+        if (!rated) continue;
+        index_of_col[c] = qm.n_queues;
+        qm.col_of_queue |= (uint32_t)c << (4 * qm.n_queues);
+        ++qm.n_queues;
+    }
+    for (int i = 0; i < 6; ++i) {
+        const int c = table->mode_col[i];
+        if (c >= 0 && c < 16) qm.queue_nibbles |= (uint32_t)index_of_col[c] << (4 * i);
+    }
+    return qm.n_queues;
 }
 
 }  // namespace
@@ -372,66 +453,36 @@ int ts_rate_stream_pair_impl(ts_ctx *ctx, const ts_table *table, int qcol, const
     return 0;
 }
 
-extern "C" int64_t ts_rate_stream_queues_workspace_bytes(int64_t n_players, int32_t row_pairs)
+// versioned rows of a shared + several-queues table: shared pair, ordinals, one pair per rated queue column
+int64_t ts_rate_stream_queues_row_bytes(const ts_table *table)
 {
-    if (n_players < 0 || row_pairs < 2 || row_pairs > 8) {
-        ts_set_error("ts_rate_stream_queues: the table needs a shared column and 2..8 pairs per row");
-        return TS_E_ARG;
-    }
-    return n_players * row_pairs * 32;
+    QueueMap qm;
+    return 8 * (8 + 4 * (int64_t)map_queues(table, qm));
 }
 
-extern "C" int ts_rate_stream_queues(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
-                                     const uint32_t *pred, const uint32_t *pred_queue, int64_t n_matches, int32_t slots,
-                                     int64_t seq_base, int32_t flags, const ts_outputs *outputs, int32_t lanes_per_match,
-                                     void *workspace, int64_t workspace_bytes, void *stream)
+// called by ts_rate_stream for tables with a shared column and several rated queue columns (stream.cu)
+int ts_rate_stream_queues_impl(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
+                               const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
+                               const ts_outputs *outputs, int32_t lanes_per_match, void *workspace, cudaStream_t s)
 {
-    if (seq_base < 0 || n_matches < 0 || seq_base + n_matches >= 0xFFFFFFFFll) {
-        ts_set_error("ts_rate_stream_queues: stream-wide match numbers must stay below 2^32 - 1");
-        return TS_E_ARG;
-    }
-    if (!ctx || !table || !table->data || (n_matches > 0 && (!ids || !meta || !pred || !pred_queue || !workspace))) {
-        ts_set_error("ts_rate_stream_queues: null argument");
-        return TS_E_ARG;
-    }
-    if (table->row_pairs < 2 || table->row_pairs > 8 || table->shared_col < 0 || table->shared_col >= table->row_pairs) {
-        ts_set_error("ts_rate_stream_queues: the table needs a shared column and 2..8 pairs per row");
-        return TS_E_UNSUPPORTED;
-    }
-    uint32_t nibbles = 0;
-    for (int i = 0; i < 6; ++i) {
-        const int c = table->mode_col[i];
-        if (c < 0) continue;
-        if (c >= table->row_pairs || c == table->shared_col) { ts_set_error("ts_rate_stream_queues: bad mode_col[%d]", i); return TS_E_ARG; }
-        nibbles |= (uint32_t)c << (4 * i);
-    }
-    if (slots != 6 && slots != 10) {
-        ts_set_error("ts_rate_stream_queues: slots must be 6 or 10 (got %d)", slots);
-        return TS_E_UNSUPPORTED;
-    }
-    const int64_t need = ts_rate_stream_queues_workspace_bytes(table->n_players, table->row_pairs);
-    if (workspace_bytes < need) {
-        ts_set_error("ts_rate_stream_queues: workspace too small (%lld < %lld bytes)", (long long)workspace_bytes, (long long)need);
-        return TS_E_WORKSPACE;
-    }
-    TS_CUDA(cudaSetDevice(ctx->device));
-    cudaStream_t s = (cudaStream_t)stream;
+    QueueMap qm;
+    map_queues(table, qm);
     PairArgs a;
     fill_args(a, ctx, table, ids, meta, pred, n_matches, seq_base, outputs, workspace);
-    a.pred_q = pred_queue;
-    a.row_words = 4u * (uint32_t)table->row_pairs;
-    a.shared_word = 4u * (uint32_t)table->shared_col;
-    a.col_nibbles = nibbles;
-    const int64_t pairs = table->n_players * table->row_pairs;
-    if ((flags & TS_STREAM_LOAD) && pairs > 0)
-        k_vt_load_all<<<(unsigned)((pairs + 255) / 256), 256, 0, s>>>(table->data, a.vt, pairs);
+    a.row_words = 8u + 4u * (uint32_t)qm.n_queues;
+    a.queue_nibbles = qm.queue_nibbles;
+    const int64_t u = table->n_players;
+    if ((flags & TS_STREAM_LOAD) && u > 0)
+        k_vt_load_queues<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, table->row_pairs, table->shared_col,
+                                                                    qm.col_of_queue, qm.n_queues, a.row_words, a.vt, u);
     TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
     int lanes = lanes_per_match ? lanes_per_match : (slots == 6 ? 2 : 8);
     int rc = 0;
     if (n_matches > 0) rc = slots == 6 ? dispatch_pair<6, true>(ctx, a, lanes, s) : dispatch_pair<10, true>(ctx, a, lanes, s);
     if (rc) return rc;
-    if ((flags & TS_STREAM_STORE) && pairs > 0)
-        k_vt_store_all<<<(unsigned)((pairs + 255) / 256), 256, 0, s>>>(a.vt, table->data, pairs);
+    if ((flags & TS_STREAM_STORE) && u > 0)
+        k_vt_store_queues<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(a.vt, table->data, table->row_pairs, table->shared_col,
+                                                                     qm.col_of_queue, qm.n_queues, a.row_words, u);
     TS_CUDA(cudaGetLastError());
     return 0;
 }

@@ -108,7 +108,7 @@ class PlayerTable(object):
 
     @property
     def multi_queue(self):
-        """Shared pair + more than one rated queue column: two dependency chains per slot."""
+        """Shared pair + more than one rated queue column (a batch that mixes game modes)."""
         return self.shared_col >= 0 and len(set(c for c in self.mode_cols if c >= 0)) > 1
 
     def mode_col_array(self):
@@ -235,27 +235,6 @@ class Rater(object):
                                            ws.numel(), _stream_ptr()))
         return pred
 
-    def link_pred_queues(self, ids, meta, n_players, mode_cols, seq_base=0, last=None, last_queue=None,
-                         out=None, out_queue=None):
-        """Links for a batch that rates several queue columns (mixed game modes against
-        the faithful table): returns (pred, pred_queue) -- the previous rated match of
-        each slot's player, and the previous one in the same queue column.  Windows:
-        last int32 [n_players] and last_queue int32 [n_players, 8], both TS_NONE at first."""
-        assert ids.is_cuda and ids.is_contiguous() and meta.is_contiguous()
-        assert (last is None) == (last_queue is None)
-        n, p = ids.shape
-        pred = out if out is not None else torch.empty_like(ids)
-        pred_q = out_queue if out_queue is not None else torch.empty_like(ids)
-        assert pred.shape == ids.shape and pred.is_contiguous() and pred_q.shape == ids.shape and pred_q.is_contiguous()
-        nbytes = L.check(self._lib.ts_link_workspace_bytes(n, p))
-        ws = self._workspace(nbytes)
-        cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
-        with torch.cuda.device(ids.device):
-            L.check(self._lib.ts_link_pred_queues(self._ctx, _ptr(ids), _ptr(meta), n, p, int(n_players),
-                                                  (C.c_int8 * 16)(*cols), int(seq_base), _ptr(last), _ptr(last_queue),
-                                                  _ptr(pred), _ptr(pred_q), _ptr(ws), ws.numel(), _stream_ptr()))
-        return pred, pred_q
-
     def link_pred_windows(self, ids, meta, n_players, mode_cols, window=None):
         """pred for a long stream, linked window by window with carried chain tails:
         same result as one link_pred call, but the scatter of every window stays
@@ -274,10 +253,9 @@ class Rater(object):
         return pred
 
     def rate_stream(self, table, ids, meta, pred, outputs=None, lanes_per_match=0, seq_base=0,
-                    flags=L.STREAM_LOAD | L.STREAM_STORE, pred_queue=None):
-        """Dataflow rating in stream order: single-pair ladders, shared + one queue
-        column, or -- with pred_queue from link_pred_queues -- any number of queue
-        columns (mixed game modes)."""
+                    flags=L.STREAM_LOAD | L.STREAM_STORE):
+        """Dataflow rating in stream order: single-pair ladders, or the shared pair
+        plus any number of rated queue columns (mixed game modes)."""
         out = L.TsOutputs()
         if outputs:
             for k in ("quality", "out_shared", "out_delta", "out_queue", "status"):
@@ -285,20 +263,10 @@ class Rater(object):
                 setattr(out, k, t.data_ptr() if t is not None else None)
         desc = table.desc()
         n, p = ids.shape
-        if pred_queue is not None:
-            nbytes = L.check(self._lib.ts_rate_stream_queues_workspace_bytes(table.n_players, table.data.shape[1]))
-        else:
-            nbytes = L.check(self._lib.ts_rate_stream_workspace_bytes(table.n_players))
+        nbytes = L.check(self._lib.ts_rate_stream_table_workspace_bytes(C.byref(desc)))
         if self._vt is None or self._vt.numel() < nbytes:
             assert flags & L.STREAM_LOAD, "the versioned rows of an earlier window are gone"
             self._vt = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=self.device)
-        if pred_queue is not None:
-            with torch.cuda.device(table.data.device):
-                L.check(self._lib.ts_rate_stream_queues(self._ctx, C.byref(desc), _ptr(ids), _ptr(meta), _ptr(pred),
-                                                        _ptr(pred_queue), n, p, int(seq_base), int(flags), C.byref(out),
-                                                        int(lanes_per_match), _ptr(self._vt), self._vt.numel(),
-                                                        _stream_ptr()))
-            return
         with torch.cuda.device(table.data.device):
             L.check(self._lib.ts_rate_stream(self._ctx, C.byref(desc), _ptr(ids), _ptr(meta), _ptr(pred), n, p,
                                              int(seq_base), int(flags), C.byref(out), int(lanes_per_match),
@@ -312,19 +280,11 @@ class Rater(object):
         and gives nothing: the rating kernel holds the whole register file.)"""
         n, p = ids.shape
         last = torch.full((table.n_players,), -1, dtype=torch.int32, device=ids.device)   # TS_NONE
-        last_q = torch.full((table.n_players, 8), -1, dtype=torch.int32, device=ids.device) if table.multi_queue else None
         for lo in range(0, max(n, 1), window):
             hi = min(n, lo + window)
             flags = (L.STREAM_LOAD if lo == 0 else 0) | (L.STREAM_STORE if hi >= n else 0)
-            pred, pred_q = self._link(table, ids[lo:hi], meta[lo:hi], lo, last, last_q)
-            self.rate_stream(table, ids[lo:hi], meta[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags,
-                             pred_queue=pred_q)
-
-    def _link(self, table, ids, meta, seq_base=0, last=None, last_queue=None):
-        """(pred, pred_queue or None) for the table's layout."""
-        if table.multi_queue:
-            return self.link_pred_queues(ids, meta, table.n_players, table.mode_cols, seq_base, last, last_queue)
-        return self.link_pred(ids, meta, table.n_players, table.mode_cols, seq_base=seq_base, last=last), None
+            pred = self.link_pred(ids[lo:hi], meta[lo:hi], table.n_players, table.mode_cols, seq_base=lo, last=last)
+            self.rate_stream(table, ids[lo:hi], meta[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags)
 
     def error_count(self):
         if L.check(self._lib.ts_stream_stalled(self._ctx, _stream_ptr())):
@@ -371,14 +331,14 @@ class Rater(object):
                                        and p in (6, 10) and n > 0 and n * p >= 2 * tab_t.shape[0])
         mode_cols = list(mode_cols)
         if path == "auto" and shared_col >= 0 and p in (6, 10) and n * p >= 2 * tab_t.shape[0]:
-            # shared + queue layout: a batch that rates one queue column only needs one link per
-            # slot (64-byte rows); otherwise the rows mirror the table and slots have two links
+            # shared + queue layout: a batch that rates one queue column only gets the compact
+            # 64-byte rows under one version; a batch that mixes game modes the ordinal-tagged rows
             bits = torch.unique((meta_t >> L.META_MODE_SHIFT) & 15).tolist() if n <= 4_000_000 else None
             if bits is not None:
                 rated = [m for m in bits if m < len(mode_cols) and m < N_MODES and mode_cols[m] >= 0]
                 if len(rated) == 1:
                     mode_cols = [c if i == rated[0] else -1 for i, c in enumerate(mode_cols)]
-            stream = tab_t.shape[1] <= 8 and tab_t.shape[0] < (1 << 29) and max(mode_cols) < 8
+            stream = tab_t.shape[1] <= 16 and any(c >= 0 for c in mode_cols)
         if windows is None:
             # ~1M matches per window, at most 8: enough to hide all but the last window's
             # link + rate behind the PCIe copy of the stream
@@ -399,7 +359,6 @@ class Rater(object):
             seed_d = seed_t.to(dev, non_blocking=True) if seed_t is not None else None
             ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
             last = torch.full((ptab.n_players,), -1, dtype=torch.int32, device=dev)
-            last_q = torch.full((ptab.n_players, 8), -1, dtype=torch.int32, device=dev) if ptab.multi_queue else None
             bounds = [(w * n) // windows for w in range(windows + 1)]
             side.wait_stream(cur)
             ready = []
@@ -415,9 +374,8 @@ class Rater(object):
                 lo, hi = bounds[w], bounds[w + 1]
                 cur.wait_event(ready[w])
                 flags = (L.STREAM_LOAD if w == 0 else 0) | (L.STREAM_STORE if w == windows - 1 else 0)
-                pred, pred_q = self._link(ptab, ids_d[lo:hi], meta_d[lo:hi], lo, last, last_q)
-                self.rate_stream(ptab, ids_d[lo:hi], meta_d[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags,
-                                 pred_queue=pred_q)
+                pred = self.link_pred(ids_d[lo:hi], meta_d[lo:hi], ptab.n_players, ptab.mode_cols, seq_base=lo, last=last)
+                self.rate_stream(ptab, ids_d[lo:hi], meta_d[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags)
             outs = None
             n_rounds = None
         else:
@@ -429,8 +387,8 @@ class Rater(object):
             outs = self.alloc_outputs(n, p) if want_outputs else None
             if stream:
                 # single-pair ladders take the streaming (dataflow) path unless told otherwise
-                pred, pred_q = self._link(ptab, ids_d, meta_d)
-                self.rate_stream(ptab, ids_d, meta_d, pred, outs, lanes_per_match, pred_queue=pred_q)
+                pred = self.link_pred(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
+                self.rate_stream(ptab, ids_d, meta_d, pred, outs, lanes_per_match)
                 n_rounds = None
             else:
                 sch = self.schedule(ids_d, meta_d, ptab.n_players, ptab.mode_cols)

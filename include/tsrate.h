@@ -157,11 +157,12 @@ int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_sorted,
 
 /* Streaming (dataflow) form of the same path: no rounds, no barriers.  Tables:
  * a single-pair ladder (row_pairs == 1, shared_col == -1), or the reference's
- * shared pair plus ONE queue column (shared_col >= 0 and every rated mode's
- * mode_col naming the same column; then quality, shared / delta / queue outputs
- * and the NULL fallbacks of rater.py:115-130 are all produced).  A batch that
- * rates several queue columns takes ts_link_pred_queues + ts_rate_stream_queues
- * below (or ts_schedule + ts_rate).
+ * shared pair plus queue columns (shared_col >= 0; quality, shared / delta /
+ * queue outputs and the NULL fallbacks of rater.py:115-130 are all produced).
+ * With ONE rated queue column a player's row is 64 bytes under one version;
+ * with several (a batch that mixes game modes, worker.py:176-192) every queue
+ * pair is versioned by its own ordinal and the ordinals travel with the shared
+ * pair (csrc/stream_pair.cu) -- the links are the same single pred array.
  * ts_link_pred does the first half of the scheduler only -- radix sort by
  * player id and chain linking -- and writes pred[N][P]: for every slot the
  * stream-wide number of that player's previous rated match (TS_NONE if none,
@@ -169,7 +170,9 @@ int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_sorted,
  * the matches in stream order (worker.py:192), each match waiting until its
  * players' rows carry the version pred names.  Results are identical to
  * ts_schedule + ts_rate.  ids / meta are in ORIGINAL order; outputs too.
- * workspace: ts_rate_stream_workspace_bytes(U).
+ * workspace: ts_rate_stream_table_workspace_bytes(table) -- 32 bytes per player
+ * for a single-pair ladder, 64 for shared + one queue, 64 + 32 per rated queue
+ * column otherwise; ts_rate_stream_workspace_bytes(U) = 64 U covers the first two.
  *
  * Windows (worker.py:18-20 micro-batches; ladders beyond 2^32 slot entries):
  * a stream is processed window after window by passing seq_base = number of
@@ -187,6 +190,7 @@ int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t
                  int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last, uint32_t *pred,
                  void *workspace, int64_t workspace_bytes, void *stream);
 int64_t ts_rate_stream_workspace_bytes(int64_t n_players);
+int64_t ts_rate_stream_table_workspace_bytes(const ts_table *table);
 /* 1 if the last ts_rate_stream / ts_rate_stream_sharded on this context gave up
  * because some match's links were never satisfied (pred does not belong to the
  * stream it was given with): the table is then unusable.  A watchdog inside the
@@ -196,29 +200,6 @@ int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, cons
                    const uint32_t *pred, int64_t n_matches, int32_t slots, int64_t seq_base, int32_t flags,
                    const ts_outputs *outputs, int32_t lanes_per_match, void *workspace, int64_t workspace_bytes,
                    void *stream);
-
-/* The same for a batch that mixes game modes against a table with several queue
- * columns (rater.py:70-82: six queues next to the shared pair; worker.py:176-192
- * rates them in one chronological stream).  A player's shared pair is rewritten
- * by every match of the player, a queue pair only by matches of that queue, so a
- * slot has two links: pred[N][P] as above, and pred_queue[N][P] = the player's
- * previous rated match in the SAME queue column (TS_NONE: the queue pair is still
- * what the table held, NULL included -- rater.py:124-130).  Rows in the workspace
- * mirror the table: row_pairs x 32 bytes per player, every pair with its own
- * version (ts_rate_stream_queues_workspace_bytes).  Windows as above, with a
- * second tail array last_queue = uint32[n_players][8] (all TS_NONE before the
- * first window); last and last_queue are given together or both NULL.
- * Limits: n_players < 2^29, queue columns < 8, slots 6 or 10, one GPU.
- * Results are identical to ts_schedule + ts_rate. */
-int ts_link_pred_queues(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
-                        int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last,
-                        uint32_t *last_queue, uint32_t *pred, uint32_t *pred_queue, void *workspace,
-                        int64_t workspace_bytes, void *stream);
-int64_t ts_rate_stream_queues_workspace_bytes(int64_t n_players, int32_t row_pairs);
-int ts_rate_stream_queues(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta,
-                          const uint32_t *pred, const uint32_t *pred_queue, int64_t n_matches, int32_t slots,
-                          int64_t seq_base, int32_t flags, const ts_outputs *outputs, int32_t lanes_per_match,
-                          void *workspace, int64_t workspace_bytes, void *stream);
 
 /* One ladder whose player table is hash-sharded over the G GPUs of a node
  * (BASELINE.json configs[4]): player p is owned by GPU p % G

@@ -127,14 +127,15 @@ def test_stream_errors_do_not_stall_successors(eng, c_oracle):
     r.close()
 
 
-def test_stream_rejects_several_queue_columns(eng):
-    """The 8-pair table with all six modes enabled has one queue chain per mode: not streamable."""
+def test_stream_rejects_table_without_rated_queue(eng):
+    """A shared column needs at least one rated queue column next to it."""
     from analyzer_b200._lib import TsError
     r = eng.Rater(eng.Env(), 0)
-    ptab = eng.PlayerTable.faithful(8, torch.device("cuda", 0))
+    tab = torch.zeros((8, 2, 2), dtype=torch.float64, device="cuda")
+    ptab = eng.PlayerTable(tab, 0, [-1, -1])
     ids = torch.zeros((1, 6), dtype=torch.int32, device="cuda")
     meta = torch.zeros((1,), dtype=torch.int32, device="cuda")
-    with pytest.raises(TsError, match="ONE queue column"):
+    with pytest.raises(TsError, match="at least one rated queue column"):
         r.rate_stream(ptab, ids, meta, ids.clone())
     r.close()
 

@@ -1,8 +1,8 @@
 """Streaming path for batches that mix game modes against the faithful table
-(shared pair + six queue columns, rater.py:70-82): ts_link_pred_queues +
-ts_rate_stream_queues through the C ABI.  Links are integer work (bit-exact
-against the sequential definition); ratings and every rate_match output are
-compared with the sequential float128 oracle and with ts_schedule + ts_rate."""
+(shared pair + six queue columns, rater.py:70-82): ts_link_pred + ts_rate_stream
+through the C ABI, queue pairs versioned by ordinals.  Ratings and every
+rate_match output are compared with the sequential float128 oracle and with
+ts_schedule + ts_rate."""
 import numpy as np
 import pytest
 import torch
@@ -11,7 +11,6 @@ from tests import helpers as H
 
 pytestmark = pytest.mark.gpu
 TOL = 1e-9
-NONE = 0xFFFFFFFF
 
 
 def _u32(t):
@@ -22,35 +21,6 @@ def _dev(a):
     if a.dtype == np.uint32:
         a = a.view(np.int32)
     return torch.from_numpy(np.ascontiguousarray(a)).cuda()
-
-
-def _links_oracle(ids, meta, mode_cols, last=None, last_q=None, seq_base=0):
-    """Sequential definition: previous rated match of each slot's player, overall
-    and within the queue column of the match (worker.py:192 order)."""
-    n, p = ids.shape
-    last = {} if last is None else last
-    last_q = {} if last_q is None else last_q
-    pred = np.full((n, p), NONE, dtype=np.uint32)
-    pred_q = np.full((n, p), NONE, dtype=np.uint32)
-    live = np.zeros((n, p), dtype=bool)
-    for m in range(n):
-        bits = int(meta[m])
-        mode = (bits >> 4) & 15
-        if mode >= 6 or mode_cols[mode] < 0 or bits & 12:
-            continue
-        col = mode_cols[mode]
-        row = [int(x) for x in ids[m]]
-        for s, pl in enumerate(row):
-            if pl == H.EMPTY:
-                continue
-            live[m, s] = True
-            pred[m, s] = last.get(pl, NONE)
-            pred_q[m, s] = last_q.get((pl, col), NONE)
-        for pl in row:
-            if pl != H.EMPTY:
-                last[pl] = seq_base + m
-                last_q[(pl, col)] = seq_base + m
-    return pred, pred_q, live
 
 
 def _mixed_modes(rng, meta, modes, p_other=0.05):
@@ -70,46 +40,6 @@ def eng():
     return engine
 
 
-def test_link_pred_queues_bit_exact(eng):
-    """Two game modes share a column, one mode is unrated, players listed twice,
-    ragged teams, AFK and unsupported matches."""
-    r = eng.Rater(eng.Env(), 0)
-    rng = np.random.default_rng(17)
-    u = 700
-    ids, meta = H.small_ladder(rng, 30000, u, slots=10, modes=(0, 1, 2, 3, 4, 5), p_afk=0.1, p_unsupported=0.05,
-                               ragged=True)
-    ids[7, 4] = ids[7, 0]                      # a player listed twice in one match
-    ids[8, 1] = ids[7, 0]
-    cols = [1, 2, 3, -1, 2, 6]                 # modes 1 and 4 rate the same column; mode 3 is not rated
-    pred, pred_q = r.link_pred_queues(_dev(ids), _dev(meta), u, cols)
-    want, want_q, live = _links_oracle(ids, meta, cols + [-1] * 10)
-    assert np.array_equal(_u32(pred)[live], want[live])
-    assert np.array_equal(_u32(pred_q)[live], want_q[live])
-    # the single-link entry point gives the same first array
-    assert np.array_equal(_u32(r.link_pred(_dev(ids), _dev(meta), u, cols))[live], want[live])
-    r.close()
-
-
-def test_link_pred_queues_windows_bit_exact(eng):
-    """Carried tails per player and per (player, column) across windows."""
-    r = eng.Rater(eng.Env(), 0)
-    rng = np.random.default_rng(23)
-    u, n, win = 300, 9000, 1250
-    ids, meta = H.small_ladder(rng, n, u, slots=6, modes=(1, 2, 4), p_afk=0.05)
-    cols = [-1, 1, 2, -1, 5]
-    want, want_q, live = _links_oracle(ids, meta, cols + [-1] * 11)
-    last = torch.full((u,), -1, dtype=torch.int32, device="cuda")
-    last_q = torch.full((u, 8), -1, dtype=torch.int32, device="cuda")
-    got, got_q = np.empty_like(want), np.empty_like(want_q)
-    for lo in range(0, n, win):
-        hi = min(n, lo + win)
-        a, b = r.link_pred_queues(_dev(ids[lo:hi]), _dev(meta[lo:hi]), u, cols, seq_base=lo, last=last, last_queue=last_q)
-        got[lo:hi], got_q[lo:hi] = _u32(a), _u32(b)
-    assert np.array_equal(got[live], want[live])
-    assert np.array_equal(got_q[live], want_q[live])
-    r.close()
-
-
 def _faithful_inputs(rng, n_players, cols_used):
     table = np.full((n_players, 8, 2), np.nan)
     has_shared = rng.random(n_players) < 0.6
@@ -124,7 +54,7 @@ def _faithful_inputs(rng, n_players, cols_used):
 
 
 @pytest.mark.parametrize("slots,lanes,modes", [(6, 0, (1, 2)), (6, 4, (0, 1, 2, 3)), (10, 0, (4, 5)), (10, 2, (0, 1, 2, 3, 4, 5)),
-                                               (6, 32, (1, 2, 3)), (10, 16, (1, 5))])
+                                               (6, 32, (1, 2, 3)), (10, 16, (1, 5)), (6, 1, (0, 5))])
 def test_stream_queues_vs_oracle_and_rounds(eng, c_oracle, slots, lanes, modes):
     """Mixed game modes in one chronological stream, deep chains (~240 slot entries per
     player), NULL shared / queue pairs, seeds, draws, AFK: table and all outputs."""
@@ -146,8 +76,8 @@ def test_stream_queues_vs_oracle_and_rounds(eng, c_oracle, slots, lanes, modes):
     pa, pb = eng.PlayerTable(tab_a, 0, mode_cols, seed_d), eng.PlayerTable(tab_b, 0, mode_cols, seed_d)
     assert pa.multi_queue
     outs_a, outs_b = r.alloc_outputs(n, slots), r.alloc_outputs(n, slots)
-    pred, pred_q = r.link_pred_queues(ids_d, meta_d, n_players, pa.mode_cols)
-    r.rate_stream(pa, ids_d, meta_d, pred, outs_a, lanes, pred_queue=pred_q)
+    pred = r.link_pred(ids_d, meta_d, n_players, pa.mode_cols)
+    r.rate_stream(pa, ids_d, meta_d, pred, outs_a, lanes)
     r.rate(pb, r.schedule(ids_d, meta_d, n_players, pb.mode_cols), outs_b, lanes)
     assert r.error_count() == 0
     for got in (tab_a.cpu().numpy(), tab_b.cpu().numpy()):
@@ -167,8 +97,8 @@ def test_stream_queues_vs_oracle_and_rounds(eng, c_oracle, slots, lanes, modes):
 
 @pytest.mark.parametrize("window", [1, 777, 50_000])
 def test_queue_windows_equal_one_shot(eng, window):
-    """Micro-batch windows (worker.py:18-20) over a mixed-mode stream: chain tails per
-    player and per queue column carried, rows kept in the workspace."""
+    """Micro-batch windows (worker.py:18-20) over a mixed-mode stream: chain tails
+    carried, rows and queue ordinals kept in the workspace."""
     dev = torch.device("cuda", 0)
     n, u = (3_000 if window == 1 else 120_000), 2_000
     rng = np.random.default_rng(window)
@@ -181,8 +111,7 @@ def test_queue_windows_equal_one_shot(eng, window):
     cols = [1, 2, 3, 4, 5, 6]
     pa, pb = eng.PlayerTable(tab_a, 0, cols, seed_d), eng.PlayerTable(tab_b, 0, cols, seed_d)
     r.rate_stream_windows(pa, ids, meta, window)
-    pred, pred_q = r.link_pred_queues(ids, meta, u, cols)
-    r.rate_stream(pb, ids, meta, pred, pred_queue=pred_q)
+    r.rate_stream(pb, ids, meta, r.link_pred(ids, meta, u, cols))
     assert r.error_count() == 0
     assert torch.equal(torch.nan_to_num(tab_a, nan=-1.0), torch.nan_to_num(tab_b, nan=-1.0))
     r.close()
@@ -215,22 +144,57 @@ def test_rate_batch_mixed_modes_streams(eng):
     r.close()
 
 
-def test_queue_stream_argument_checks(eng):
-    from analyzer_b200._lib import TsError
+def test_two_modes_on_one_column_and_unrated_modes(eng, c_oracle):
+    """Game modes 1 and 4 rate the same queue column, mode 3 is not rated; a player is
+    listed twice in one match; ragged teams."""
+    rng = np.random.default_rng(31)
+    u, n = 400, 20_000
+    ids, meta = H.small_ladder(rng, n, u, slots=10, modes=(0, 1, 2, 3, 4, 5), p_afk=0.05, p_unsupported=0.05, ragged=True)
+    ids[7, 4] = ids[7, 0]                      # listed twice, same team: both slots write the same pair
+    cols = [1, 2, 3, -1, 2, 6]
+    table, seeds = _faithful_inputs(rng, u, [1, 2, 3, 6])
+    want = table.copy()
+    out = c_oracle.rate_sequential(c_oracle.make_params(), ids, meta, want, 0, cols, seed=seeds, quad=True, want_outputs=True)
+    r = eng.Rater(eng.Env(), 0)
+    tab, seed_d = _dev(table), _dev(seeds)
+    pt = eng.PlayerTable(tab, 0, cols, seed_d)
+    outs = r.alloc_outputs(n, 10)
+    r.reset_errors()
+    r.rate_stream(pt, _dev(ids), _dev(meta), r.link_pred(_dev(ids), _dev(meta), u, pt.mode_cols), outs)
+    assert r.error_count() == out["errors"]
+    got = tab.cpu().numpy()
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and np.nanmax(np.abs(got - want)) < TOL
+    assert np.array_equal(outs["status"].cpu().numpy(), out["status"])
+    r.reset_errors()
+    r.close()
+
+
+def test_more_than_1024_matches_of_one_queue_per_player(eng, c_oracle):
+    """Queue ordinals are 10-bit tags: a player with thousands of matches in one queue wraps them."""
+    rng = np.random.default_rng(37)
+    u, n = 40, 30_000                         # ~4500 slot entries per player
+    ids, meta = H.small_ladder(rng, n, u, slots=6, modes=(1, 2))
+    cols = [1, 2, 3, 4, 5, 6]
+    table, seeds = _faithful_inputs(rng, u, [2, 3])
+    want = table.copy()
+    out = c_oracle.rate_sequential(c_oracle.make_params(), ids, meta, want, 0, cols, seed=seeds, quad=True)
+    assert out["errors"] == 0
+    r = eng.Rater(eng.Env(), 0)
+    tab, seed_d = _dev(table), _dev(seeds)
+    pt = eng.PlayerTable(tab, 0, cols, seed_d)
+    r.rate_stream(pt, _dev(ids), _dev(meta), r.link_pred(_dev(ids), _dev(meta), u, pt.mode_cols))
+    assert r.error_count() == 0
+    got = tab.cpu().numpy()
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and np.nanmax(np.abs(got - want)) < TOL
+    r.close()
+
+
+def test_queue_stream_empty_batch(eng):
     r = eng.Rater(eng.Env(), 0)
     dev = torch.device("cuda", 0)
-    ids = torch.zeros((1, 6), dtype=torch.int32, device=dev)
-    meta = torch.zeros((1,), dtype=torch.int32, device=dev)
-    with pytest.raises(TsError, match="below 8"):
-        r.link_pred_queues(ids, meta, 8, [1, 9])
-    lad = eng.PlayerTable.ladder(torch.zeros((8, 2), dtype=torch.float64, device=dev), mode=1)
-    with pytest.raises(TsError, match="shared column"):
-        r.rate_stream(lad, ids, meta, ids.clone(), pred_queue=ids.clone())
-    # empty batch: nothing to do, table untouched
     ptab = eng.PlayerTable.faithful(8, dev)
     e_ids = torch.zeros((0, 6), dtype=torch.int32, device=dev)
     e_meta = torch.zeros((0,), dtype=torch.int32, device=dev)
-    pred, pred_q = r.link_pred_queues(e_ids, e_meta, 8, ptab.mode_cols)
-    r.rate_stream(ptab, e_ids, e_meta, pred, pred_queue=pred_q)
+    r.rate_stream(ptab, e_ids, e_meta, r.link_pred(e_ids, e_meta, 8, ptab.mode_cols))
     assert r.error_count() == 0 and bool(torch.isnan(ptab.data).all())
     r.close()
