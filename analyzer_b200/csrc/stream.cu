@@ -69,6 +69,11 @@ __device__ __forceinline__ unsigned long long *row_of(const StreamArgs &a, uint3
 
 using tsvw::trunc_vw;
 
+// bit g * L of a lane mask: the first lane of every group of L lanes
+template <int L>
+constexpr uint32_t kGroupBase = L == 1 ? 0xFFFFFFFFu : L == 2 ? 0x55555555u : L == 4 ? 0x11111111u
+                              : L == 8 ? 0x01010101u : L == 16 ? 0x00010001u : 0x00000001u;
+
 // per-warp staging buffers: a warp owns W = 32 / L consecutive matches at a time
 template <int P, int W>
 struct WarpStage {
@@ -110,7 +115,6 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
     const int lane = wl % L;                    // lane in match group
     const int grp = wl / L;                     // match of the warp tile
     WarpStage<P, W> &stage = stage_all[threadIdx.x >> 5];
-    const uint32_t gmask = L == 32 ? 0xFFFFFFFFu : (((1u << L) - 1u) << (grp * L));
     const double tau2 = a.prm.tau * a.prm.tau;
     const double beta2 = a.prm.beta * a.prm.beta;
     const double tb2 = tau2 + beta2;
@@ -160,23 +164,26 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
             q_mu[k] = 0.0; q_sg[k] = 1.0;
         }
         bool done = !live;
-        // warp-uniform wait loop: a group that finds all its rows at the expected
-        // version rates its match inside the iteration.  Watchdog: links that can never
-        // be satisfied (a pred array that does not belong to this stream) must not hang
-        // the GPU -- after max_spins (2^24) fruitless polls (tens of seconds; a legitimate wait is
-        // milliseconds) a warp raises the stall flag, and every warp that sees it gives up.
+        // Wait loop, the same for all lanes of the warp.  Each iteration polls the rows still
+        // missing; then ONE ballot tells every lane which match groups are complete, and if
+        // there is any, the whole warp runs the rating arithmetic together -- the issue slots
+        // are spent whether 2 or 32 lanes are active, and a converged warp needs no
+        // reconvergence barriers, no partial-mask votes and no mask checks on the shuffles;
+        // only the stores are predicated on the lane's group being complete.  Lanes of
+        // groups that are not complete compute on placeholders and throw the result away.
+        // Watchdog: links that can never be satisfied (a pred array that does not belong to
+        // this stream) must not hang the GPU -- after max_spins (2^24) fruitless polls (tens of
+        // seconds; a legitimate wait is milliseconds) a warp raises the stall flag, and every
+        // warp that sees it gives up.
         uint32_t spins = 0;
         while (!__all_sync(0xFFFFFFFFu, done)) {
-            if ((++spins & 0x3FFu) == 0u) {
-                if (spins >= a.max_spins && wl == 0) atomicExch(&a.ctrl[CTRL_STALLED], 1ull);
-                if (ld_relaxed_u64(&a.ctrl[CTRL_STALLED]) != 0ull) return;
-            }
+            bool ready = false;
             if (!done) {
-                bool ready = true;
                 unsigned long long w[SPL][4];
 #pragma unroll
                 for (int k = 0; k < SPL; ++k)
                     if (!have[k]) ld_row<SHARDED>(row_of<SHARDED>(a, pid[k]), w[k]);
+                ready = true;
 #pragma unroll
                 for (int k = 0; k < SPL; ++k) {
                     if (!have[k] && row_has_version(w[k], want[k])) {
@@ -186,74 +193,100 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
                     }
                     ready &= have[k];
                 }
-                if (__all_sync(gmask, ready)) {
-                    double sgn[SPL], r_mu[SPL], r_sg[SPL];
-                    double d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
-                    uint32_t cnts = 0;
+            }
+            const uint32_t rb = __ballot_sync(0xFFFFFFFFu, ready);
+            uint32_t complete = rb;             // bit g * L: all L lanes of group g are ready
 #pragma unroll
-                    for (int k = 0; k < SPL; ++k) {
-                        const int s = lane + k * L;
-                        sgn[k] = ((s >= HALF ? 1 : 0) == first) ? 1.0 : -1.0;
-                        r_mu[k] = q_mu[k]; r_sg[k] = q_sg[k];      // the row as read (kept for a failed match)
-                        if (!used[k]) continue;
-                        bool bad = false;
-                        if (isnan(q_mu[k])) {            // first touch: seed (rater.py:118-119)
-                            double2 sd = make_double2(q_mu[k], q_sg[k]);
-                            if (a.seed) sd = __ldg(reinterpret_cast<const double2 *>(a.seed) + pid[k]);
-                            bad |= isnan(sd.x);
-                            if (!bad) { q_mu[k] = sd.x; q_sg[k] = sd.y; }
-                        }
-                        bad |= q_sg[k] == 0.0;
-                        d_q = fma(sgn[k], q_mu[k], d_q);
-                        c2_q += fma(q_sg[k], q_sg[k], tb2);
-                        ss_q = fma(q_sg[k], q_sg[k], ss_q);
-                        cnts += (sgn[k] > 0.0 ? 1u : 256u) + (bad ? 65536u : 0u);
-                    }
-                    if (L > 1) {
-                        d_q = group_sum<L>(d_q, gmask);
-                        c2_q = group_sum<L>(c2_q, gmask);
-                        ss_q = group_sum<L>(ss_q, gmask);
-                        cnts = group_sum_u32<L>(cnts, gmask);
-                    }
-                    const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
-                    int status = TS_ST_OK;
-                    if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
-                    const double margin = n == P ? margin_full : a.prm.draw_margin[n];   // ragged teams are rare: no indexed load on the hot path
-                    double v_q = 0.0, w_q = 0.0;
-                    const double rc_q = rsqrt(c2_q);
-                    if (status == TS_ST_OK &&
-                        !trunc_vw(d_q * rc_q, margin * rc_q, is_draw, a.prm.draw_is_zero != 0, v_q, w_q))
-                        status = TS_ST_FP_ERROR;
-#pragma unroll
-                    for (int k = 0; k < SPL; ++k) {
-                        if (!used[k]) continue;
-                        const int s = lane + k * L;
-                        // a failed match writes nothing in the reference; here it republishes the
-                        // row it read under its own version so that successors can go on
-                        double mu2 = r_mu[k], sg2 = r_sg[k];
-                        if (status == TS_ST_OK) {
-                            const double si = fma(q_sg[k], q_sg[k], tau2);
-                            const double g = si * rc_q;
-                            mu2 = fma(sgn[k] * g, v_q, q_mu[k]);
-                            sg2 = sqrt(si * (1.0 - (g * rc_q) * w_q));
-                        }
-                        st_row<SHARDED>(row_of<SHARDED>(a, pid[k]), mu2, sg2, a.seq_base + m);   // first: successors are waiting
-                        if (status == TS_ST_OK && a.out.out_queue)
-                            __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + (size_t)m * P + s, make_double2(mu2, sg2));
-                    }
-                    if (lane == 0) {
-                        if (a.out.status) a.out.status[m] = (uint8_t)status;
-                        if (status != TS_ST_OK) atomicAdd(&a.ctrl[CTRL_ERRORS], 1ull);
-                        else if (a.out.quality) {
-                            const double nb2 = (double)n * beta2;
-                            const double den = nb2 + ss_q;
-                            a.out.quality[m] = exp(-0.5 * d_q * d_q / den) * sqrt(nb2 / den);
-                        }
-                    }
-                    done = true;
-                } else {
-                    __nanosleep(a.sleep_ns);
+            for (int o = 1; o < L; o <<= 1) complete &= complete >> o;
+            complete &= kGroupBase<L>;
+            if (complete == 0u) {
+                if ((++spins & 0x3FFu) == 0u) {
+                    if (spins >= a.max_spins && wl == 0) atomicExch(&a.ctrl[CTRL_STALLED], 1ull);
+                    if (ld_relaxed_u64(&a.ctrl[CTRL_STALLED]) != 0ull) return;
                 }
+                __nanosleep(a.sleep_ns);
+                continue;
+            }
+            const bool go = ((complete >> (grp * L)) & 1u) != 0u;
+            // lanes that only tag along take the branch of the first complete group
+            // (the shuffle is executed by every lane: it must not sit inside the conditional)
+            const int lead_draw = __shfl_sync(0xFFFFFFFFu, (int)is_draw, __ffs(complete) - 1);
+            const bool draw_eff = go ? is_draw : lead_draw != 0;
+
+            double sgn[SPL], r_mu[SPL], r_sg[SPL];
+            double d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
+            uint32_t cnts = 0;
+            bool any_null = false;
+#pragma unroll
+            for (int k = 0; k < SPL; ++k) {
+                r_mu[k] = q_mu[k]; r_sg[k] = q_sg[k];      // the row as read (kept for a failed match)
+                any_null |= used[k] && isnan(q_mu[k]);
+            }
+            if (__any_sync(0xFFFFFFFFu, any_null)) {       // first touch: seed (rater.py:118-119)
+#pragma unroll
+                for (int k = 0; k < SPL; ++k) {
+                    if (!(used[k] && isnan(q_mu[k]))) continue;
+                    double2 sd = make_double2(q_mu[k], q_sg[k]);
+                    if (a.seed) sd = __ldg(reinterpret_cast<const double2 *>(a.seed) + pid[k]);
+                    if (isnan(sd.x)) cnts |= 65536u;       // neither rating nor seed
+                    else { q_mu[k] = sd.x; q_sg[k] = sd.y; }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < SPL; ++k) {
+                const int s = lane + k * L;
+                sgn[k] = ((s >= HALF ? 1 : 0) == first) ? 1.0 : -1.0;
+                const bool u = used[k];
+                d_q = fma(sgn[k], u ? q_mu[k] : 0.0, d_q);
+                c2_q += u ? fma(q_sg[k], q_sg[k], tb2) : 0.0;
+                ss_q = u ? fma(q_sg[k], q_sg[k], ss_q) : ss_q;
+                cnts += (u ? (sgn[k] > 0.0 ? 1u : 256u) : 0u) + ((u && q_sg[k] == 0.0) ? 65536u : 0u);
+            }
+            if (L > 1) {
+#pragma unroll
+                for (int o = L / 2; o > 0; o >>= 1) {
+                    d_q += __shfl_xor_sync(0xFFFFFFFFu, d_q, o);
+                    c2_q += __shfl_xor_sync(0xFFFFFFFFu, c2_q, o);
+                    ss_q += __shfl_xor_sync(0xFFFFFFFFu, ss_q, o);
+                    cnts += __shfl_xor_sync(0xFFFFFFFFu, cnts, o);
+                }
+            }
+            const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
+            int status = TS_ST_OK;
+            if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
+            const double margin = n == P ? margin_full : a.prm.draw_margin[n];   // ragged teams are rare: no indexed load on the hot path
+            double v_q = 0.0, w_q = 0.0;
+            const double rc_q = rsqrt(c2_q);
+            if (status == TS_ST_OK &&
+                !trunc_vw(d_q * rc_q, margin * rc_q, draw_eff, a.prm.draw_is_zero != 0, v_q, w_q))
+                status = TS_ST_FP_ERROR;
+            const bool ok = status == TS_ST_OK;
+#pragma unroll
+            for (int k = 0; k < SPL; ++k) {
+                const int s = lane + k * L;
+                // a failed match writes nothing in the reference; here it republishes the
+                // row it read under its own version so that successors can go on
+                const double si = fma(q_sg[k], q_sg[k], tau2);
+                const double g = si * rc_q;
+                const double mu2 = ok ? fma(sgn[k] * g, v_q, q_mu[k]) : r_mu[k];
+                const double sg2 = ok ? sqrt(si * (1.0 - (g * rc_q) * w_q)) : r_sg[k];
+                if (go && used[k]) {
+                    st_row<SHARDED>(row_of<SHARDED>(a, pid[k]), mu2, sg2, a.seq_base + m);   // first: successors are waiting
+                    if (ok && a.out.out_queue)
+                        __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + (size_t)m * P + s, make_double2(mu2, sg2));
+                }
+            }
+            if (go) {
+                if (lane == 0) {
+                    if (a.out.status) a.out.status[m] = (uint8_t)status;
+                    if (!ok) atomicAdd(&a.ctrl[CTRL_ERRORS], 1ull);
+                    else if (a.out.quality) {
+                        const double nb2 = (double)n * beta2;
+                        const double den = nb2 + ss_q;
+                        a.out.quality[m] = exp(-0.5 * d_q * d_q / den) * sqrt(nb2 / den);
+                    }
+                }
+                done = true;
             }
         }
     }
