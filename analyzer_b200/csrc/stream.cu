@@ -213,13 +213,13 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
             const int lead_draw = __shfl_sync(0xFFFFFFFFu, (int)is_draw, __ffs(complete) - 1);
             const bool draw_eff = go ? is_draw : lead_draw != 0;
 
-            double sgn[SPL], r_mu[SPL], r_sg[SPL];
+            double sgn[SPL], e_mu[SPL], e_sg[SPL];     // effective pairs; q_mu / q_sg stay the rows as read
             double d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
             uint32_t cnts = 0;
             bool any_null = false;
 #pragma unroll
             for (int k = 0; k < SPL; ++k) {
-                r_mu[k] = q_mu[k]; r_sg[k] = q_sg[k];      // the row as read (kept for a failed match)
+                e_mu[k] = q_mu[k]; e_sg[k] = q_sg[k];
                 any_null |= used[k] && isnan(q_mu[k]);
             }
             if (__any_sync(0xFFFFFFFFu, any_null)) {       // first touch: seed (rater.py:118-119)
@@ -229,7 +229,7 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
                     double2 sd = make_double2(q_mu[k], q_sg[k]);
                     if (a.seed) sd = __ldg(reinterpret_cast<const double2 *>(a.seed) + pid[k]);
                     if (isnan(sd.x)) cnts |= 65536u;       // neither rating nor seed
-                    else { q_mu[k] = sd.x; q_sg[k] = sd.y; }
+                    else { e_mu[k] = sd.x; e_sg[k] = sd.y; }
                 }
             }
 #pragma unroll
@@ -237,10 +237,10 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
                 const int s = lane + k * L;
                 sgn[k] = ((s >= HALF ? 1 : 0) == first) ? 1.0 : -1.0;
                 const bool u = used[k];
-                d_q = fma(sgn[k], u ? q_mu[k] : 0.0, d_q);
-                c2_q += u ? fma(q_sg[k], q_sg[k], tb2) : 0.0;
-                ss_q = u ? fma(q_sg[k], q_sg[k], ss_q) : ss_q;
-                cnts += (u ? (sgn[k] > 0.0 ? 1u : 256u) : 0u) + ((u && q_sg[k] == 0.0) ? 65536u : 0u);
+                d_q = fma(sgn[k], u ? e_mu[k] : 0.0, d_q);
+                c2_q += u ? fma(e_sg[k], e_sg[k], tb2) : 0.0;
+                ss_q = u ? fma(e_sg[k], e_sg[k], ss_q) : ss_q;
+                cnts += (u ? (sgn[k] > 0.0 ? 1u : 256u) : 0u) + ((u && e_sg[k] == 0.0) ? 65536u : 0u);
             }
             if (L > 1) {
 #pragma unroll
@@ -266,10 +266,10 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
                 const int s = lane + k * L;
                 // a failed match writes nothing in the reference; here it republishes the
                 // row it read under its own version so that successors can go on
-                const double si = fma(q_sg[k], q_sg[k], tau2);
+                const double si = fma(e_sg[k], e_sg[k], tau2);
                 const double g = si * rc_q;
-                const double mu2 = ok ? fma(sgn[k] * g, v_q, q_mu[k]) : r_mu[k];
-                const double sg2 = ok ? sqrt(si * (1.0 - (g * rc_q) * w_q)) : r_sg[k];
+                const double mu2 = ok ? fma(sgn[k] * g, v_q, e_mu[k]) : q_mu[k];
+                const double sg2 = ok ? sqrt(si * (1.0 - (g * rc_q) * w_q)) : q_sg[k];
                 if (go && used[k]) {
                     st_row<SHARDED>(row_of<SHARDED>(a, pid[k]), mu2, sg2, a.seq_base + m);   // first: successors are waiting
                     if (ok && a.out.out_queue)

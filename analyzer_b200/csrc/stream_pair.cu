@@ -57,6 +57,11 @@ struct PairArgs {
 
 constexpr uint32_t kOrdMask = 1023u;
 
+// bit g * L of a lane mask: the first lane of every group of L lanes
+template <int L>
+constexpr uint32_t kGroupBase = L == 1 ? 0xFFFFFFFFu : L == 2 ? 0x55555555u : L == 4 ? 0x11111111u
+                              : L == 8 ? 0x01010101u : L == 16 ? 0x00010001u : 0x00000001u;
+
 __device__ __forceinline__ void ld_ord(const unsigned long long *p, unsigned long long (&w)[2])
 {
     asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(p) : "memory");
@@ -100,7 +105,6 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
     const int lane = wl % L;
     const int grp = wl / L;
     WarpStage<P, W> &stage = stage_all[threadIdx.x >> 5];
-    const uint32_t gmask = L == 32 ? 0xFFFFFFFFu : (((1u << L) - 1u) << (grp * L));
     const double tau2 = a.prm.tau * a.prm.tau;
     const double beta2 = a.prm.beta * a.prm.beta;
     const double tb2 = tau2 + beta2;
@@ -156,14 +160,14 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
             s_mu[k] = 0.0; s_sg[k] = 1.0; q_mu[k] = 0.0; q_sg[k] = 1.0;
         }
         bool done = !live;
+        // wait loop as in stream.cu: one ballot per poll, and the arithmetic of every pass is
+        // run by the whole converged warp (lanes of incomplete groups compute on what they
+        // have and throw the result away); only the stores are predicated
         uint32_t spins = 0;
         while (!__all_sync(0xFFFFFFFFu, done)) {
-            if ((++spins & 0x3FFu) == 0u) {      // watchdog, see stream.cu
-                if (spins >= a.max_spins && wl == 0) atomicExch(&a.ctrl[CTRL_STALLED], 1ull);
-                if (ld_relaxed_u64(&a.ctrl[CTRL_STALLED]) != 0ull) return;
-            }
+            bool ready = false;
             if (!done) {
-                bool ready = true;
+                ready = true;
 #pragma unroll
                 for (int k = 0; k < SPL; ++k) {
                     if (have[k]) continue;
@@ -189,104 +193,131 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
                     }
                     ready &= have[k];
                 }
-                if (__all_sync(gmask, ready)) {
-                    double sgn[SPL], es_mu[SPL], es_sg[SPL], eq_mu[SPL], eq_sg[SPL];   // effective pairs
-                    bool had[SPL];
-                    double d_s = 0.0, c2_s = 0.0, d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
-                    uint32_t cnts = 0;
+            }
+            const uint32_t rb = __ballot_sync(0xFFFFFFFFu, ready);
+            uint32_t complete = rb;             // bit g * L: all L lanes of group g are ready
 #pragma unroll
-                    for (int k = 0; k < SPL; ++k) {
-                        const int s = lane + k * L;
-                        sgn[k] = ((s >= HALF ? 1 : 0) == first) ? 1.0 : -1.0;
-                        es_mu[k] = s_mu[k]; es_sg[k] = s_sg[k]; eq_mu[k] = q_mu[k]; eq_sg[k] = q_sg[k];
-                        had[k] = false;
-                        if (!used[k]) continue;
-                        bool bad = false;
-                        had[k] = !isnan(s_mu[k]);
-                        if (!had[k]) {                      // rater.py:118-119: first touch -> seed
-                            double2 sd = make_double2(s_mu[k], s_sg[k]);
-                            if (a.seed) sd = __ldg(reinterpret_cast<const double2 *>(a.seed) + pid[k]);
-                            bad |= isnan(sd.x);
-                            es_mu[k] = sd.x; es_sg[k] = sd.y;
-                        }
-                        if (isnan(q_mu[k])) { eq_mu[k] = es_mu[k]; eq_sg[k] = es_sg[k]; }   // rater.py:127-130
-                        bad |= (eq_sg[k] == 0.0) || (es_sg[k] == 0.0);
-                        d_s = fma(sgn[k], es_mu[k], d_s);
-                        c2_s += fma(es_sg[k], es_sg[k], tb2);
-                        d_q = fma(sgn[k], eq_mu[k], d_q);
-                        c2_q += fma(eq_sg[k], eq_sg[k], tb2);
-                        ss_q = fma(eq_sg[k], eq_sg[k], ss_q);
-                        cnts += (sgn[k] > 0.0 ? 1u : 256u) + (bad ? 65536u : 0u);
-                    }
-                    if (L > 1) {
-                        d_s = group_sum<L>(d_s, gmask);
-                        c2_s = group_sum<L>(c2_s, gmask);
-                        d_q = group_sum<L>(d_q, gmask);
-                        c2_q = group_sum<L>(c2_q, gmask);
-                        ss_q = group_sum<L>(ss_q, gmask);
-                        cnts = group_sum_u32<L>(cnts, gmask);
-                    }
-                    const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
-                    int status = TS_ST_OK;
-                    if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
-                    const double margin = n == P ? margin_full : a.prm.draw_margin[n];   // ragged teams are rare: no indexed load on the hot path
-                    double v_s = 0.0, w_s = 0.0, v_q = 0.0, w_q = 0.0;
-                    const double rc_s = rsqrt(c2_s), rc_q = rsqrt(c2_q);
-                    if (status == TS_ST_OK &&
-                        (!trunc_vw(d_s * rc_s, margin * rc_s, is_draw, a.prm.draw_is_zero != 0, v_s, w_s) ||
-                         !trunc_vw(d_q * rc_q, margin * rc_q, is_draw, a.prm.draw_is_zero != 0, v_q, w_q)))
-                        status = TS_ST_FP_ERROR;
-#pragma unroll
-                    for (int k = 0; k < SPL; ++k) {
-                        if (!used[k]) continue;
-                        const int s = lane + k * L;
-                        const size_t o = (size_t)m * P + s;
-                        // a failed match writes nothing in the reference; here it republishes the
-                        // row it read under its own version so that successors can go on
-                        double ms2 = s_mu[k], ss2 = s_sg[k], mq2 = q_mu[k], sq2 = q_sg[k];
-                        if (status == TS_ST_OK) {
-                            const double si = fma(es_sg[k], es_sg[k], tau2);
-                            const double gs = si * rc_s;
-                            ms2 = fma(sgn[k] * gs, v_s, es_mu[k]);
-                            ss2 = sqrt(si * (1.0 - (gs * rc_s) * w_s));
-                            const double qi = fma(eq_sg[k], eq_sg[k], tau2);
-                            const double gq = qi * rc_q;
-                            mq2 = fma(sgn[k] * gq, v_q, eq_mu[k]);
-                            sq2 = sqrt(qi * (1.0 - (gq * rc_q) * w_q));
-                        }
-                        unsigned long long *row = a.vt + (size_t)pid[k] * row_words;
-                        st_row(row, ms2, ss2, a.seq_base + m);          // first: successors are waiting
-                        if (MULTI) {
-                            // the queue pair moves on to its next ordinal; the ordinals travel with the shared pair
-                            const bool upper = qj >= 3u;
-                            uint32_t word = upper ? ord_hi[k] : ord_lo[k];
-                            const uint32_t next = (((word >> ord_shift) & kOrdMask) + 1u) & kOrdMask;
-                            word = (word & ~(kOrdMask << ord_shift)) | (next << ord_shift);
-                            st_ord(row + 4, upper ? ord_lo[k] : word, upper ? word : ord_hi[k], a.seq_base + m);
-                            st_row(row + q_word, mq2, sq2, next);
-                        } else {
-                            st_row(row + 4, mq2, sq2, a.seq_base + m);
-                        }
-                        if (status == TS_ST_OK) {
-                            if (a.out.out_shared) __stcg(reinterpret_cast<double2 *>(a.out.out_shared) + o, make_double2(ms2, ss2));
-                            if (a.out.out_delta)   // rater.py:150-153
-                                a.out.out_delta[o] = had[k] ? (ms2 - ss2) - (s_mu[k] - s_sg[k]) : 0.0;
-                            if (a.out.out_queue) __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + o, make_double2(mq2, sq2));
-                        }
-                    }
-                    if (lane == 0) {
-                        if (a.out.status) a.out.status[m] = (uint8_t)status;
-                        if (status != TS_ST_OK) atomicAdd(&a.ctrl[CTRL_ERRORS], 1ull);
-                        else if (a.out.quality) {      // rater.py:141: queue pairs before the update, no tau
-                            const double nb2 = (double)n * beta2;
-                            const double den = nb2 + ss_q;
-                            a.out.quality[m] = exp(-0.5 * d_q * d_q / den) * sqrt(nb2 / den);
-                        }
-                    }
-                    done = true;
-                } else {
-                    __nanosleep(a.sleep_ns);
+            for (int o = 1; o < L; o <<= 1) complete &= complete >> o;
+            complete &= kGroupBase<L>;
+            if (complete == 0u) {
+                if ((++spins & 0x3FFu) == 0u) {      // watchdog, see stream.cu
+                    if (spins >= a.max_spins && wl == 0) atomicExch(&a.ctrl[CTRL_STALLED], 1ull);
+                    if (ld_relaxed_u64(&a.ctrl[CTRL_STALLED]) != 0ull) return;
                 }
+                __nanosleep(a.sleep_ns);
+                continue;
+            }
+            const bool go = ((complete >> (grp * L)) & 1u) != 0u;
+            // lanes that only tag along take the branch of the first complete group
+            // (the shuffle is executed by every lane: it must not sit inside the conditional)
+            const int lead_draw = __shfl_sync(0xFFFFFFFFu, (int)is_draw, __ffs(complete) - 1);
+            const bool draw_eff = go ? is_draw : lead_draw != 0;
+
+            double sgn[SPL], es_mu[SPL], es_sg[SPL], eq_mu[SPL], eq_sg[SPL];   // effective pairs
+            bool had[SPL];
+            double d_s = 0.0, c2_s = 0.0, d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
+            uint32_t cnts = 0;
+            bool any_null = false;
+#pragma unroll
+            for (int k = 0; k < SPL; ++k) {
+                es_mu[k] = s_mu[k]; es_sg[k] = s_sg[k]; eq_mu[k] = q_mu[k]; eq_sg[k] = q_sg[k];
+                had[k] = !isnan(s_mu[k]);
+                any_null |= used[k] && (!had[k] || isnan(q_mu[k]));
+            }
+            if (__any_sync(0xFFFFFFFFu, any_null)) {
+#pragma unroll
+                for (int k = 0; k < SPL; ++k) {
+                    if (!used[k]) continue;
+                    if (!had[k]) {                      // rater.py:118-119: first touch -> seed
+                        double2 sd = make_double2(s_mu[k], s_sg[k]);
+                        if (a.seed) sd = __ldg(reinterpret_cast<const double2 *>(a.seed) + pid[k]);
+                        if (isnan(sd.x)) cnts |= 65536u;    // neither rating nor seed
+                        es_mu[k] = sd.x; es_sg[k] = sd.y;
+                    }
+                    if (isnan(q_mu[k])) { eq_mu[k] = es_mu[k]; eq_sg[k] = es_sg[k]; }   // rater.py:127-130
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < SPL; ++k) {
+                const int s = lane + k * L;
+                sgn[k] = ((s >= HALF ? 1 : 0) == first) ? 1.0 : -1.0;
+                const bool u = used[k];
+                const bool bad = u && ((eq_sg[k] == 0.0) || (es_sg[k] == 0.0));
+                d_s = fma(sgn[k], u ? es_mu[k] : 0.0, d_s);
+                c2_s += u ? fma(es_sg[k], es_sg[k], tb2) : 0.0;
+                d_q = fma(sgn[k], u ? eq_mu[k] : 0.0, d_q);
+                c2_q += u ? fma(eq_sg[k], eq_sg[k], tb2) : 0.0;
+                ss_q = u ? fma(eq_sg[k], eq_sg[k], ss_q) : ss_q;
+                cnts += (u ? (sgn[k] > 0.0 ? 1u : 256u) : 0u) + (bad ? 65536u : 0u);
+            }
+            if (L > 1) {
+#pragma unroll
+                for (int o = L / 2; o > 0; o >>= 1) {
+                    d_s += __shfl_xor_sync(0xFFFFFFFFu, d_s, o);
+                    c2_s += __shfl_xor_sync(0xFFFFFFFFu, c2_s, o);
+                    d_q += __shfl_xor_sync(0xFFFFFFFFu, d_q, o);
+                    c2_q += __shfl_xor_sync(0xFFFFFFFFu, c2_q, o);
+                    ss_q += __shfl_xor_sync(0xFFFFFFFFu, ss_q, o);
+                    cnts += __shfl_xor_sync(0xFFFFFFFFu, cnts, o);
+                }
+            }
+            const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
+            int status = TS_ST_OK;
+            if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
+            const double margin = n == P ? margin_full : a.prm.draw_margin[n];   // ragged teams are rare: no indexed load on the hot path
+            double v_s = 0.0, w_s = 0.0, v_q = 0.0, w_q = 0.0;
+            const double rc_s = rsqrt(c2_s), rc_q = rsqrt(c2_q);
+            if (status == TS_ST_OK &&
+                (!trunc_vw(d_s * rc_s, margin * rc_s, draw_eff, a.prm.draw_is_zero != 0, v_s, w_s) ||
+                 !trunc_vw(d_q * rc_q, margin * rc_q, draw_eff, a.prm.draw_is_zero != 0, v_q, w_q)))
+                status = TS_ST_FP_ERROR;
+            const bool ok = status == TS_ST_OK;
+#pragma unroll
+            for (int k = 0; k < SPL; ++k) {
+                const int s = lane + k * L;
+                const size_t o = (size_t)m * P + s;
+                // a failed match writes nothing in the reference; here it republishes the
+                // row it read under its own version so that successors can go on
+                const double si = fma(es_sg[k], es_sg[k], tau2);
+                const double gs = si * rc_s;
+                const double ms2 = ok ? fma(sgn[k] * gs, v_s, es_mu[k]) : s_mu[k];
+                const double ss2 = ok ? sqrt(si * (1.0 - (gs * rc_s) * w_s)) : s_sg[k];
+                const double qi = fma(eq_sg[k], eq_sg[k], tau2);
+                const double gq = qi * rc_q;
+                const double mq2 = ok ? fma(sgn[k] * gq, v_q, eq_mu[k]) : q_mu[k];
+                const double sq2 = ok ? sqrt(qi * (1.0 - (gq * rc_q) * w_q)) : q_sg[k];
+                if (!(go && used[k])) continue;
+                unsigned long long *row = a.vt + (size_t)pid[k] * row_words;
+                st_row(row, ms2, ss2, a.seq_base + m);          // first: successors are waiting
+                if (MULTI) {
+                    // the queue pair moves on to its next ordinal; the ordinals travel with the shared pair
+                    const bool upper = qj >= 3u;
+                    uint32_t word = upper ? ord_hi[k] : ord_lo[k];
+                    const uint32_t next = (((word >> ord_shift) & kOrdMask) + 1u) & kOrdMask;
+                    word = (word & ~(kOrdMask << ord_shift)) | (next << ord_shift);
+                    st_ord(row + 4, upper ? ord_lo[k] : word, upper ? word : ord_hi[k], a.seq_base + m);
+                    st_row(row + q_word, mq2, sq2, next);
+                } else {
+                    st_row(row + 4, mq2, sq2, a.seq_base + m);
+                }
+                if (ok) {
+                    if (a.out.out_shared) __stcg(reinterpret_cast<double2 *>(a.out.out_shared) + o, make_double2(ms2, ss2));
+                    if (a.out.out_delta)   // rater.py:150-153
+                        a.out.out_delta[o] = had[k] ? (ms2 - ss2) - (s_mu[k] - s_sg[k]) : 0.0;
+                    if (a.out.out_queue) __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + o, make_double2(mq2, sq2));
+                }
+            }
+            if (go) {
+                if (lane == 0) {
+                    if (a.out.status) a.out.status[m] = (uint8_t)status;
+                    if (!ok) atomicAdd(&a.ctrl[CTRL_ERRORS], 1ull);
+                    else if (a.out.quality) {      // rater.py:141: queue pairs before the update, no tau
+                        const double nb2 = (double)n * beta2;
+                        const double den = nb2 + ss_q;
+                        a.out.quality[m] = exp(-0.5 * d_q * d_q / den) * sqrt(nb2 / den);
+                    }
+                }
+                done = true;
             }
         }
     }
