@@ -20,6 +20,7 @@
 // player (rater.py:83-85,102-106): they create no edges and land in bucket 0.
 // All integer work; the result is bit-exact against the sequential schedule
 // oracle by construction (Kahn levels == longest-path levels).
+#include <stdint.h>
 #include <stdlib.h>
 
 #include <algorithm>
@@ -261,6 +262,39 @@ k_radix_hist_all(KeySrc src, uint32_t n, int passes, uint32_t *ghist)
         const uint32_t k = load_key(src, idx);
         if (src.drop && k == src.sentinel) continue;
         for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(k >> (8 * p)) & 255u], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < passes * 256; i += kSortBlock) {
+        const uint32_t c = (&h[0][0])[i];
+        if (c) atomicAdd(&ghist[i], c);
+    }
+}
+
+// The same totals for pass 0's source, the match records themselves: one thread per match reads
+// the meta word once and the ids two at a time -- no division by the slot count, no gather.
+__global__ void __launch_bounds__(kSortBlock)
+k_radix_hist_matches(KeySrc src, uint32_t n_matches, int passes, uint32_t *ghist)
+{
+    __shared__ uint32_t h[kMaxPasses][256];
+    for (int i = threadIdx.x; i < kMaxPasses * 256; i += kSortBlock) (&h[0][0])[i] = 0;
+    __syncthreads();
+    const uint32_t pairs = src.slots / 2;
+    for (uint32_t m = blockIdx.x * kSortBlock + threadIdx.x; m < n_matches; m += gridDim.x * kSortBlock) {
+        const uint32_t meta = __ldg(src.meta + m);
+        const bool gated = ((src.rated_mask >> ((meta >> TS_META_MODE_SHIFT) & 15u)) & 1u) == 0u ||
+                           (meta & (TS_META_AFK | TS_META_INVALID)) != 0u;
+        const uint2 *row = reinterpret_cast<const uint2 *>(src.keys + (size_t)m * src.slots);
+        for (uint32_t j = 0; j < pairs; ++j) {
+            const uint2 two = __ldg(row + j);
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                uint32_t k = e ? two.y : two.x;
+                if (k == TS_EMPTY_SLOT || gated || (k & src.owner_mask) != src.owner_rank) k = src.sentinel;
+                else k >>= src.owner_shift;
+                if (src.drop && k == src.sentinel) continue;
+                for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(k >> (8 * p)) & 255u], 1u);
+            }
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < passes * 256; i += kSortBlock) {
@@ -690,6 +724,17 @@ int frontier_blocks_per_sm_cap()
     return cap;
 }
 
+uint32_t pred_range_entries()
+{
+    static uint32_t mi = 0;
+    if (mi == 0) {
+        const char *e = getenv("TSRATE_PRED_RANGE_MI");   // Mi entries (4 bytes each) of pred per pass
+        int v = e ? atoi(e) : 16;
+        mi = (uint32_t)(v < 1 ? 1 : (v > 512 ? 512 : v));
+    }
+    return mi << 20;
+}
+
 int bits_for(uint64_t max_value)
 {
     int b = 1;
@@ -748,7 +793,10 @@ int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStrea
     uint32_t *ghist = w.totals, *ticket = w.totals + kMaxPasses * 256, *n_dev = ticket + 1;
     if (n_dev_out) *n_dev_out = n_dev;
     if (cudaMemsetAsync(w.totals, 0, kTotalsWords * 4, stream) != cudaSuccess) return ts_cuda_fail(cudaGetLastError(), "memset");
-    k_radix_hist_all<<<sm_count * 8, kSortBlock, 0, stream>>>(src0, n, passes, ghist);
+    if (src0.from_ids && (src0.slots & 1u) == 0u && ((uintptr_t)src0.keys & 7u) == 0u)
+        k_radix_hist_matches<<<sm_count * 8, kSortBlock, 0, stream>>>(src0, n / src0.slots, passes, ghist);
+    else
+        k_radix_hist_all<<<sm_count * 8, kSortBlock, 0, stream>>>(src0, n, passes, ghist);
     k_radix_scan_all<<<1, 256, 0, stream>>>(ghist, passes, n_dev);
     int cur = -1;
     for (int p = 0; p < passes; ++p) {
@@ -994,7 +1042,7 @@ int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64
     // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2.
     // Every pass re-reads the sorted pairs, so this only pays for a handful of passes; a window
     // too large for that (more than 128 Mi slot entries) takes one pass and the read-modify-writes.
-    uint32_t range = 16u << 20;
+    uint32_t range = pred_range_entries();
     if (((uint64_t)np + range - 1) / range > 8) range = 0xFFFFFFFFu;
     for (uint64_t lo = 0; lo < np; lo += range) {
         uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);

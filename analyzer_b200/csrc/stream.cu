@@ -69,6 +69,11 @@ __device__ __forceinline__ unsigned long long *row_of(const StreamArgs &a, uint3
 
 using tsvw::trunc_vw;
 
+// 1: the loads of all missing slots of a poll are issued before any is checked
+#ifndef TS_STREAM_HOIST
+#define TS_STREAM_HOIST 0
+#endif
+
 // bit g * L of a lane mask: the first lane of every group of L lanes
 template <int L>
 constexpr uint32_t kGroupBase = L == 1 ? 0xFFFFFFFFu : L == 2 ? 0x55555555u : L == 4 ? 0x11111111u
@@ -179,11 +184,12 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
         while (!__all_sync(0xFFFFFFFFu, done)) {
             bool ready = false;
             if (!done) {
+                ready = true;
+#if TS_STREAM_HOIST
                 unsigned long long w[SPL][4];
 #pragma unroll
                 for (int k = 0; k < SPL; ++k)
                     if (!have[k]) ld_row<SHARDED>(row_of<SHARDED>(a, pid[k]), w[k]);
-                ready = true;
 #pragma unroll
                 for (int k = 0; k < SPL; ++k) {
                     if (!have[k] && row_has_version(w[k], want[k])) {
@@ -193,6 +199,20 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
                     }
                     ready &= have[k];
                 }
+#else
+#pragma unroll
+                for (int k = 0; k < SPL; ++k) {
+                    if (have[k]) continue;
+                    unsigned long long w[4];
+                    ld_row<SHARDED>(row_of<SHARDED>(a, pid[k]), w);
+                    if (row_has_version(w, want[k])) {
+                        have[k] = true;
+                        q_mu[k] = row_mu(w);
+                        q_sg[k] = row_sigma(w);
+                    }
+                    ready &= have[k];
+                }
+#endif
             }
             const uint32_t rb = __ballot_sync(0xFFFFFFFFu, ready);
             uint32_t complete = rb;             // bit g * L: all L lanes of group g are ready

@@ -36,6 +36,12 @@ using namespace tsstream;
 using tsvw::trunc_vw;
 
 constexpr int kBlock = 256;
+// 1: issue the loads of all missing slots before checking any (measured slower: config 2, K = 2,
+// rate 5.16 vs 3.75 ms -- more loads in flight per poll cost more than the round trips they save;
+// polling only the first missing slot per iteration is slower too, 3.93 ms)
+#ifndef TS_PAIR_HOIST
+#define TS_PAIR_HOIST 0
+#endif
 
 struct PairArgs {
     ts_params prm;
@@ -168,6 +174,36 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
             bool ready = false;
             if (!done) {
                 ready = true;
+#if TS_PAIR_HOIST
+                unsigned long long ws[SPL][4], wq[SPL][4], wo[SPL][2];
+#pragma unroll
+                for (int k = 0; k < SPL; ++k) {
+                    if (have[k]) continue;
+                    const unsigned long long *row = a.vt + (size_t)pid[k] * row_words;
+                    ld_row(row, ws[k]);
+                    ld_row(row + q_word, wq[k]);
+                    if (MULTI) ld_ord(row + 4, wo[k]);
+                }
+#pragma unroll
+                for (int k = 0; k < SPL; ++k) {
+                    if (have[k]) continue;
+                    bool ok;
+                    if (MULTI) {
+                        const uint32_t ords = (uint32_t)wo[k][qj >= 3u ? 1 : 0];
+                        ok = row_has_version(ws[k], want[k]) && (uint32_t)(wo[k][0] >> 32) == want[k] &&
+                             (uint32_t)(wo[k][1] >> 32) == want[k] && row_has_version(wq[k], (ords >> ord_shift) & kOrdMask);
+                        ord_lo[k] = (uint32_t)wo[k][0]; ord_hi[k] = (uint32_t)wo[k][1];
+                    } else {
+                        ok = row_has_version(ws[k], want[k]) && row_has_version(wq[k], want[k]);
+                    }
+                    if (ok) {
+                        have[k] = true;
+                        s_mu[k] = row_mu(ws[k]); s_sg[k] = row_sigma(ws[k]);
+                        q_mu[k] = row_mu(wq[k]); q_sg[k] = row_sigma(wq[k]);
+                    }
+                    ready &= have[k];
+                }
+#else
 #pragma unroll
                 for (int k = 0; k < SPL; ++k) {
                     if (have[k]) continue;
@@ -193,6 +229,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
                     }
                     ready &= have[k];
                 }
+#endif
             }
             const uint32_t rb = __ballot_sync(0xFFFFFFFFu, ready);
             uint32_t complete = rb;             // bit g * L: all L lanes of group g are ready
