@@ -521,7 +521,9 @@ def run_b200(a):
         "config": {"workload": workload_name(a), "seed": hex(SEED), "rounds": n_rounds, "path": a.path,
                    "per_gpu": "one independent ladder per GPU, no data-path collective" if world > 1 else "single GPU",
                    "l2": "256 MiB flush between steps; ids+meta (%d MB) exceed the 126 MB L2; the %d MB player "
-                         "table is L2-resident by nature" % ((n * p * 4 + n * 4) >> 20, (u * 16) >> 20),
+                         "table %s" % ((n * p * 4 + n * 4) >> 20, (u * 16) >> 20,
+                                       "is L2-resident by nature" if u * 32 < (100 << 20) else
+                                       "(versioned rows: twice that) does not fit L2 either"),
                    "lanes_per_match": a.lanes or (2 if p == 6 else 8)},
         "phases": {"schedule_ms": ms_sched, "rate_ms": ms_rate,
                    "rate_only_matches_per_s": n * world / (ms_rate * 1e-3),
