@@ -178,6 +178,35 @@ def faithful_rate(rater, engine, ids_d, meta_d, table0, u, lanes):
     assert rater.error_count() == 0
     out["algorithmic_bytes_per_match"] = rate_bytes_per_match(p, 2)
     out["note"] = "shared + queue pair per player (K = 2), best of 3, no per-participant outputs; both paths agree"
+    if p == 6:
+        # what worker.py:176-192 hands over: ONE chronological stream whose game mode varies from
+        # match to match (here 40% ranked, 30% casual, 20% blitz, 10% br), against the 8-pair table
+        del tab, tab0, pt
+        g = torch.Generator(device=dev)
+        g.manual_seed(7)
+        x = torch.rand(n, device=dev, generator=g)
+        modes = torch.where(x < 0.4, 1, torch.where(x < 0.7, 0, torch.where(x < 0.9, 2, 3))).to(torch.int32)
+        meta_mix = (meta_d & ~0xF0) | (modes << 4)
+        tab0 = torch.full((u, 8, 2), float("nan"), dtype=torch.float64, device=dev)
+        tab0[:, 0] = table0.reshape(u, 2)
+        tab = tab0.clone()
+        pt = engine.PlayerTable(tab, 0, [1, 2, 3, 4, 5, 6])
+        best = None
+        for it in range(3):
+            tab.copy_(tab0)
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            e0.record()
+            pred = rater.link_pred_windows(ids_d, meta_mix, u, pt.mode_cols)
+            e1.record()
+            rater.rate_stream(pt, ids_d, meta_mix, pred, None, lanes)
+            e2.record()
+            torch.cuda.synchronize()
+            t = (e0.elapsed_time(e1), e1.elapsed_time(e2))
+            if best is None or sum(t) < sum(best):
+                best = t
+        assert rater.error_count() == 0
+        out["mixed_modes"] = {"schedule_ms": best[0], "rate_ms": best[1], "matches_per_s": n / (sum(best) * 1e-3),
+                              "note": "stream path, game mode varying from match to match (4 queues), 8-pair table"}
     return out
 
 
