@@ -683,6 +683,81 @@ k_last_update(const uint32_t *keys, const uint32_t *vals, uint32_t n_in, const u
     last[k] = seq_base + (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + i), slots_magic);
 }
 
+// ---- rounds by dataflow -----------------------------------------------------
+// round[m] = 1 + max over the match's players of the round of that player's previous rated
+// match (0 for gated matches) is a recurrence along the links, so it is evaluated the way the
+// streaming rating kernel evaluates ratings: matches in stream order, one lane per match, a
+// lane polls round[] of its predecessors until none is 0 ("not known yet") and publishes its
+// own.  A round word validates itself.  No frontier queue, no atomics per edge, no grid-wide
+// step per round: a dependency hop costs about one L2 round trip and a half (config 2, 888
+// rounds: 4.3 ms of level-synchronous sweep before).
+// The whole grid must be resident (cooperative launch); a warp takes its tiles of 32 matches
+// in increasing order, so the oldest unresolved match never waits on work that has not started.
+template <int P>     // P = slots (compile time for 6 and 10), 0 = run-time slot count
+__global__ void __launch_bounds__(256)
+k_levels(const uint32_t *pred, const uint32_t *meta, uint32_t rated_mask, uint32_t n, uint32_t slots_rt,
+         uint32_t *round, ts_sched_info *info)
+{
+    const uint32_t slots = P ? (uint32_t)P : slots_rt;
+    const int lane = threadIdx.x & 31;
+    const uint32_t n_warps = gridDim.x * (blockDim.x >> 5);
+    const uint32_t warp = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;   // neighbouring tiles on different SMs
+    const uint32_t n_tiles = (n + 31u) / 32u;
+    uint32_t deepest = 0, gated_seen = 0;
+    for (uint32_t tile = warp; tile < n_tiles; tile += n_warps) {
+        const uint32_t m = tile * 32u + lane;
+        bool live = false;
+        if (m < n) {
+            const uint32_t mt = __ldg(meta + m);
+            live = ((rated_mask >> ((mt >> TS_META_MODE_SHIFT) & 15u)) & 1u) != 0u &&
+                   (mt & (TS_META_AFK | TS_META_INVALID)) == 0u;
+        }
+        gated_seen += __popc(__ballot_sync(0xFFFFFFFFu, m < n && !live));
+        // the predecessors still unknown, as a bit per slot
+        uint32_t todo = 0, best = 0;
+        const uint32_t *links = pred + (size_t)m * slots;
+        if (live) {
+#pragma unroll
+            for (uint32_t sl = 0; sl < (P ? (uint32_t)P : 16u); ++sl)
+                if (sl < slots && __ldg(links + sl) != TS_NONE) todo |= 1u << sl;
+        }
+        bool done = !live;
+        while (!__all_sync(0xFFFFFFFFu, done)) {
+            if (!done) {
+                uint32_t lv[P ? P : 16];
+#pragma unroll
+                for (uint32_t sl = 0; sl < (P ? (uint32_t)P : 16u); ++sl)
+                    lv[sl] = ((todo >> sl) & 1u) ? ld_relaxed_u32(round + __ldg(links + sl)) : 0u;
+#pragma unroll
+                for (uint32_t sl = 0; sl < (P ? (uint32_t)P : 16u); ++sl)
+                    if (lv[sl] != 0u) { best = max(best, lv[sl]); todo &= ~(1u << sl); }
+                if (todo == 0u) {
+                    st_relaxed_u32(round + m, best + 1u);
+                    deepest = max(deepest, best + 1u);
+                    done = true;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) deepest = max(deepest, __shfl_xor_sync(0xFFFFFFFFu, deepest, o));
+    if (lane == 0) {
+        if (deepest) atomicMax(&info->n_rounds, deepest);
+        if (gated_seen) atomicAdd(&info->n_gated, gated_seen);
+    }
+}
+
+// round_offsets from the rounds in sorted order: bucket r starts where the first key >= r stands
+__global__ void __launch_bounds__(256)
+k_round_bounds(const uint32_t *sorted_round, uint32_t n, uint32_t n_rounds, uint32_t *round_offsets)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i > n) return;
+    const uint32_t lo = i == 0 ? 0u : __ldg(sorted_round + i - 1) + 1u;           // first bucket starting at i
+    const uint32_t hi = i == n ? n_rounds + 1u : __ldg(sorted_round + i);         // last one
+    for (uint32_t r = lo; r <= hi; ++r) round_offsets[r] = i;
+}
+
 struct Workspace {
     uint32_t *keys[2];
     uint32_t *vals[2];
@@ -822,6 +897,41 @@ int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStrea
     return cur;
 }
 
+uint32_t pred_range_entries();
+
+// pred[v] for every slot of the sorted pairs in w.keys/vals[buf] (pred pre-filled by the caller).
+// Destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2.
+// Every pass re-reads the sorted pairs, so this only pays for a handful of passes; a window
+// too large for that (more than 128 Mi slot entries) takes one pass and the read-modify-writes.
+void launch_pred(const Workspace &w, int buf, uint32_t np, const uint32_t *n_dev, const KeySrc &src, uint32_t seq_base,
+                 const uint32_t *last, uint32_t *pred, cudaStream_t s)
+{
+    uint32_t range = pred_range_entries();
+    if (((uint64_t)np + range - 1) / range > 8) range = 0xFFFFFFFFu;
+    for (uint64_t lo = 0; lo < np; lo += range) {
+        uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);
+        k_pred<<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic, src.sentinel,
+                                                  (uint32_t)lo, hi, seq_base, last, pred);
+    }
+}
+
+int levels_blocks_per_sm_cap()
+{
+    static int cap = -1;
+    if (cap < 0) {
+        const char *e = getenv("TSRATE_LEVELS_BLOCKS_PER_SM");
+        cap = e ? atoi(e) : 2;
+        if (cap < 1) cap = 1;
+    }
+    return cap;
+}
+
+int schedule_frontier_enabled()
+{
+    const char *e = getenv("TSRATE_SCHEDULE_FRONTIER");   // read every call: tests switch it
+    return e ? atoi(e) : 0;
+}
+
 }  // namespace
 
 extern "C" int64_t ts_schedule_workspace_bytes(int64_t n_matches, int32_t slots)
@@ -898,21 +1008,40 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
     if (buf < 0) return buf;
 
-    // 2. link chains
+    // 2. + 3. rounds
     TS_CUDA(cudaMemsetAsync(round, 0, (size_t)n * 4, s));
     // barrier words and queue tail/snapshot; the error counter (word 2) is left alone
     if (int rc = ts_reset_barrier(ctx->d_ctrl, s)) return rc;
     TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_TAIL, 0, (CTRL_WORDS - CTRL_TAIL) * sizeof(unsigned long long), s));
-    k_link<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, (uint32_t)slots, (uint32_t)n_players,
-                                            w.succ);
-    k_init_frontier<<<(n + 255) / 256, 256, 0, s>>>(meta, modes, w.succ, (uint32_t)slots, n, w.pending, w.queue,
-                                                    ctx->d_ctrl);
-    // close level 1: the sweep reads its first `end` from the snapshot word
-    TS_CUDA(cudaMemcpyAsync(ctx->d_ctrl + CTRL_TAIL + 1, ctx->d_ctrl + CTRL_TAIL, sizeof(unsigned long long),
-                            cudaMemcpyDeviceToDevice, s));
-
-    // 3. frontier relaxation (persistent, cooperative)
-    {
+    const bool by_levels = !schedule_frontier_enabled();
+    if (by_levels) {
+        // links to the previous match of every slot's player, then the rounds by dataflow along them
+        uint32_t *pred = w.succ;
+        TS_CUDA(cudaMemsetAsync(pred, 0xFF, (size_t)np * 4, s));
+        launch_pred(w, buf, np, nullptr, src, 0u, nullptr, pred, s);
+        TS_CUDA(cudaMemsetAsync(info, 0, sizeof(ts_sched_info), s));
+        void *fn = slots == 6 ? (void *)k_levels<6> : slots == 10 ? (void *)k_levels<10> : (void *)k_levels<0>;
+        int per_sm = 0;
+        TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 256, 0));
+        if (per_sm < 1) { ts_set_error("levels kernel does not fit"); return TS_E_CUDA; }
+        // every resident lane polls: more than a few levels of matches in flight only floods L2
+        per_sm = std::min(per_sm, levels_blocks_per_sm_cap());
+        dim3 grid(ctx->sm_count * per_sm), block(256);
+        uint32_t slots_u = (uint32_t)slots;
+        const uint32_t *pred_c = pred;
+        void *kargs[] = {&pred_c, &meta, &src.rated_mask, (void *)&n, &slots_u, &round, &info};
+        // cooperative launch only for its guarantee that the whole grid is resident
+        TS_CUDA(cudaLaunchCooperativeKernel(fn, grid, block, kargs, 0, s));
+    } else {
+        // level-synchronous frontier sweep (TSRATE_SCHEDULE_FRONTIER=1): successor links, one
+        // persistent cooperative kernel, one grid-wide step per round
+        k_link<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, (uint32_t)slots, (uint32_t)n_players,
+                                                w.succ);
+        k_init_frontier<<<(n + 255) / 256, 256, 0, s>>>(meta, modes, w.succ, (uint32_t)slots, n, w.pending, w.queue,
+                                                        ctx->d_ctrl);
+        // close level 1: the sweep reads its first `end` from the snapshot word
+        TS_CUDA(cudaMemcpyAsync(ctx->d_ctrl + CTRL_TAIL + 1, ctx->d_ctrl + CTRL_TAIL, sizeof(unsigned long long),
+                                cudaMemcpyDeviceToDevice, s));
         int per_sm = 0;
         TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_frontier, 256, 0));
         if (per_sm < 1) { ts_set_error("frontier kernel does not fit"); return TS_E_CUDA; }
@@ -923,14 +1052,19 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
         void *kargs[] = {&w.queue, &w.succ, &w.pending, &round, &slots_u, (void *)&n, &round_offsets,
                          (void *)&cap, &info, &ctrl};
         TS_CUDA(cudaLaunchCooperativeKernel((void *)k_frontier, grid, block, kargs, 0, s));
+        k_offsets<<<1, 1024, 0, s>>>(round_offsets, info, cap);
     }
-    k_offsets<<<1, 1024, 0, s>>>(round_offsets, info, cap);
 
     // 4. bucket by round, ascending match_seq inside a round
     ts_sched_info h;
     TS_CUDA(cudaMemcpyAsync(&h, info, sizeof h, cudaMemcpyDeviceToHost, s));
     TS_CUDA(cudaStreamSynchronize(s));
     // errors were reset together with the control words above: keep the count
+    if (by_levels && (uint64_t)h.n_rounds + 2 > (uint64_t)cap) {
+        h.overflow = 1;
+        TS_CUDA(cudaMemcpyAsync(info, &h, sizeof h, cudaMemcpyHostToDevice, s));
+        TS_CUDA(cudaStreamSynchronize(s));
+    }
     if (h.overflow) {
         ts_set_error("ts_schedule: %u rounds need offsets_cap >= %u (got %lld)", h.n_rounds, h.n_rounds + 2,
                      (long long)offsets_cap);
@@ -950,6 +1084,7 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s, ctx->sm_count);
     if (buf < 0) return buf;
     TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    if (by_levels) k_round_bounds<<<n / 256 + 1, 256, 0, s>>>(w.keys[buf], n, h.n_rounds, round_offsets);
     if (ids_sorted && meta_sorted) {
         size_t total = (size_t)n * slots;
         k_permute<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(ids, meta, order, n, (uint32_t)slots, ids_sorted,
@@ -1039,16 +1174,7 @@ int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64
     // slots that take no part (empty, gated match) read TS_NONE: the output is fully defined;
     // sharded: slots of players owned elsewhere read 0x7F7F7F7F until the MIN over ranks
     TS_CUDA(cudaMemsetAsync(pred, sharded ? 0x7F : 0xFF, (size_t)np * 4, s));
-    // destination ranges of at most 64 MiB of pred (16 Mi entries) per pass: half of the 126 MB L2.
-    // Every pass re-reads the sorted pairs, so this only pays for a handful of passes; a window
-    // too large for that (more than 128 Mi slot entries) takes one pass and the read-modify-writes.
-    uint32_t range = pred_range_entries();
-    if (((uint64_t)np + range - 1) / range > 8) range = 0xFFFFFFFFu;
-    for (uint64_t lo = 0; lo < np; lo += range) {
-        uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);
-        k_pred<<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic, src.sentinel,
-                                                  (uint32_t)lo, hi, (uint32_t)seq_base, last, pred);
-    }
+    launch_pred(w, buf, np, n_dev, src, (uint32_t)seq_base, last, pred, s);
     if (last)
         k_last_update<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic,
                                                        src.sentinel, (uint32_t)seq_base, last);

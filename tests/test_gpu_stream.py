@@ -302,4 +302,13 @@ def test_link_windows_and_sort_variants_bit_exact(eng, monkeypatch):
     sch_b = r.schedule(ids, meta, u, cols)
     assert torch.equal(one, three)
     assert torch.equal(sch_a.order, sch_b.order) and torch.equal(sch_a.round, sch_b.round)
+    # rounds by dataflow along the links (default) == level-synchronous frontier sweep
+    monkeypatch.delenv("TSRATE_ONESWEEP")
+    monkeypatch.setenv("TSRATE_SCHEDULE_FRONTIER", "1")
+    sch_c = r.schedule(ids, meta, u, cols)
+    assert sch_a.n_rounds == sch_c.n_rounds
+    assert torch.equal(sch_a.order, sch_c.order) and torch.equal(sch_a.round, sch_c.round)
+    k = sch_a.n_rounds + 2
+    assert torch.equal(sch_a.round_offsets[:k], sch_c.round_offsets[:k])
+    assert torch.equal(sch_a.info[:3], sch_c.info[:3])
     r.close()
