@@ -7,11 +7,10 @@
 //   1. radix-sort the (player_id, slot index) pairs of all rated matches by
 //      player id -- LSD, 8-bit digits, stable, so each player's slots stay in
 //      match_seq order;
-//   2. link each player's consecutive matches (successor per slot, number of
-//      predecessors per match);
-//   3. frontier relaxation: level-synchronous sweep in one persistent
-//      cooperative kernel; the frontier of iteration k is exactly the set of
-//      matches whose ASAP round is k (all predecessors resolved in k-1 sweeps);
+//   2. link each player's consecutive matches (predecessor match per slot);
+//   3. rounds: round[m] = 1 + max over the slots of round[predecessor], evaluated
+//      by dataflow along the links in one persistent kernel (k_levels; the
+//      level-synchronous frontier sweep it replaced is kept behind an env switch);
 //   4. radix-sort (round, match_seq) so every round lists its matches in
 //      ascending match_seq, prefix-sum the level sizes into round_offsets, and
 //      permute the match records into that order for the rating kernel.
@@ -19,7 +18,7 @@
 // Gated matches (unsupported mode, AFK, invalid roster count) never touch a
 // player (rater.py:83-85,102-106): they create no edges and land in bucket 0.
 // All integer work; the result is bit-exact against the sequential schedule
-// oracle by construction (Kahn levels == longest-path levels).
+// oracle by construction (longest-path levels).
 #include <stdint.h>
 #include <stdlib.h>
 

@@ -4,7 +4,7 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
 
 A step is one pass of the hot path over one batch: schedule (radix sort, chain
-link, frontier relaxation, round bucketing) + rate (all rounds) of the
+link, rounds, round bucketing) + rate (all rounds) of the
 workload -- BASELINE.json configs[1]: 10M synthetic 3v3 ranked matches over 1M
 players, single (mu, sigma) ladder -- on inputs already resident in HBM.  With
 N GPUs every rank rates its own independent ladder of that size (BASELINE.json
@@ -51,7 +51,7 @@ def parse():
     ap.add_argument("--lanes", type=int, default=0, help="lanes per match of the rating kernel (0 = default)")
     ap.add_argument("--path", default="stream", choices=["rounds", "stream"],
                     help="headline path. stream: ts_link_pred + ts_rate_stream (sort, link, dataflow rating in stream "
-                         "order); rounds: ts_schedule + ts_rate (sort, link, frontier relaxation, round buckets, one "
+                         "order); rounds: ts_schedule + ts_rate (sort, link, rounds by dataflow, round buckets, one "
                          "grid barrier per round).  Both are timed every run; the other one is reported under 'paths'.")
     ap.add_argument("--sharded", action="store_true",
                     help="ONE ladder of --matches over all ranks: player table hash-sharded in NVLink peer memory "
@@ -542,7 +542,7 @@ def run_b200(a):
     # kernels of this library per step (memsets / copies are not kernels): the sort is
     # 1 histogram + 1 scan + one single-sweep kernel per pass
     launches = {"stream": (2 + passes_p) + pred_passes + 3,                 # sort, pred passes, rows load, rate_stream, rows store
-                "rounds": (2 + passes_p) + 2 + 1 + 1 + (2 + passes_r) + 1 + 1}   # sort, link+init, frontier, offsets, sort, permute, rate
+                "rounds": (2 + passes_p) + pred_passes + 1 + (2 + passes_r) + 1 + 1 + 1}   # sort, pred passes, levels, sort, bounds, permute, rate
     line = {
         "metric": METRIC, "value": n * world / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True,
@@ -560,8 +560,8 @@ def run_b200(a):
         "paths": {a.path: {"schedule_ms": ms_sched, "rate_ms": ms_rate, "matches_per_s": n * world / (ms_step * 1e-3)},
                   other: {"schedule_ms": ms_sched2, "rate_ms": ms_rate2,
                           "matches_per_s": n * world / ((ms_sched2 + ms_rate2) * 1e-3)},
-                  "note": "stream = sort + link + dataflow rating in stream order; rounds = sort + link + frontier "
-                          "relaxation + round buckets + one grid barrier per round; same ratings (checked)"},
+                  "note": "stream = sort + link + dataflow rating in stream order; rounds = sort + link + rounds by "
+                          "dataflow + round buckets + one grid barrier per round; same ratings (checked)"},
         "roofline": {"kernel": kernel, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_match": b_rate,
