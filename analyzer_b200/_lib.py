@@ -28,7 +28,7 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_static", "ts_schedule_static_max_slot_entries",
            "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream",
            "ts_stream_stalled", "ts_rate_stream_table_workspace_bytes",
-           "ts_seed_table", "ts_link_pred_sharded", "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_rate_stream_sharded"]
+           "ts_seed_table", "ts_widen_meta", "ts_link_pred_sharded", "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_rate_stream_sharded"]
 
 
 class TsParams(C.Structure):
@@ -135,6 +135,7 @@ def lib():
         L.ts_stream_stalled.argtypes = [C.c_void_p, C.c_void_p]
         L.ts_seed_table.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double,
                                     C.POINTER(C.c_double), C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ts_widen_meta.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         L.ts_gen_matches.argtypes = [C.POINTER(TsGen), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                      C.c_void_p]
         L.ts_gen_table.argtypes = [C.c_uint64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]

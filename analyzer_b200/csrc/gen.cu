@@ -171,3 +171,30 @@ extern "C" int ts_seed_table(const double *rank_points_ranked, const double *ran
     TS_CUDA(cudaGetLastError());
     return 0;
 }
+
+// Ingest helper: the meta word uses its low 8 bits only, so a host may ship it as bytes
+// (a quarter of the PCIe volume of that column) and widen it here.
+__global__ void __launch_bounds__(256) k_widen_meta(const uint8_t *meta8, int64_t n, uint32_t *meta)
+{
+    // four bytes per thread: one 4-byte load, one 16-byte store
+    const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i + 4 <= n && ((reinterpret_cast<uintptr_t>(meta8 + i) & 3u) == 0u) && ((reinterpret_cast<uintptr_t>(meta + i) & 15u) == 0u)) {
+        const uint32_t w = __ldg(reinterpret_cast<const uint32_t *>(meta8 + i));
+        *reinterpret_cast<uint4 *>(meta + i) = make_uint4(w & 255u, (w >> 8) & 255u, (w >> 16) & 255u, w >> 24);
+        return;
+    }
+    for (int64_t j = i; j < n && j < i + 4; ++j) meta[j] = meta8[j];
+}
+
+extern "C" int ts_widen_meta(const uint8_t *meta8, int64_t n_matches, uint32_t *meta, void *stream)
+{
+    if (n_matches < 0 || (n_matches > 0 && (!meta8 || !meta))) {
+        ts_set_error("ts_widen_meta: bad arguments");
+        return TS_E_ARG;
+    }
+    if (n_matches == 0) return 0;
+    const int64_t threads = (n_matches + 3) / 4;
+    k_widen_meta<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(meta8, n_matches, meta);
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}

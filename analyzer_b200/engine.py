@@ -286,6 +286,14 @@ class Rater(object):
             pred = self.link_pred(ids[lo:hi], meta[lo:hi], table.n_players, table.mode_cols, seq_base=lo, last=last)
             self.rate_stream(table, ids[lo:hi], meta[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags)
 
+    def widen_meta(self, meta8, out=None):
+        """uint8 meta column (device) -> the 32-bit words the kernels read."""
+        n = meta8.numel()
+        out = out if out is not None else torch.empty((n,), dtype=torch.int32, device=meta8.device)
+        with torch.cuda.device(meta8.device):
+            L.check(self._lib.ts_widen_meta(_ptr(meta8), n, _ptr(out), _stream_ptr()))
+        return out
+
     def error_count(self):
         if L.check(self._lib.ts_stream_stalled(self._ctx, _stream_ptr())):
             raise L.TsError("ts_rate_stream gave up: the links (pred) do not belong to the stream they were given with")
@@ -308,7 +316,8 @@ class Rater(object):
     def rate_batch(self, ids, meta, table, seed=None, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6),
                    want_outputs=True, lanes_per_match=0, table_out=None, path="auto", windows=None):
         """The reference-facing batch call with HOST buffers: numpy ids
-        [N, P] uint32, meta [N] uint32, table [U, C, 2] float64 (NaN = NULL),
+        [N, P] uint32, meta [N] uint32 or uint8 (only the low 8 bits are used; bytes
+        quarter the column's PCIe volume), table [U, C, 2] float64 (NaN = NULL),
         optional seed [U, 2].  Copies in, schedules, rates, copies back.
         Returns dict(table=..., n_rounds=..., quality=..., out_*=..., status=...).
         Raises FloatingPointError / ValueError like the reference would for the
@@ -319,10 +328,13 @@ class Rater(object):
             if a is None or isinstance(a, torch.Tensor):
                 return a                      # torch CPU tensors (e.g. pinned) pass through
             a = np.ascontiguousarray(a)
+            if as_i32 and a.dtype.itemsize == 1:
+                return torch.from_numpy(a.view(np.uint8))      # meta shipped as bytes, widened on the device
             return torch.from_numpy(a.view(np.int32) if as_i32 else a)
 
         ids_t, meta_t, tab_t, seed_t = host(ids, True), host(meta, True), host(table), host(seed)
         n, p = ids_t.shape
+        meta_bytes = meta_t.element_size() == 1
         # Single-pair ladders take the streaming (dataflow) path when chains are deep
         # (several matches per player: latency-bound, barriers hurt); sparse ladders over a
         # table much larger than the batch are bandwidth-bound and cheaper round by round
@@ -355,6 +367,7 @@ class Rater(object):
             self._copy_stream = side
             ids_d = torch.empty((n, p), dtype=torch.int32, device=dev)
             meta_d = torch.empty((n,), dtype=torch.int32, device=dev)
+            meta_in = torch.empty((n,), dtype=torch.uint8, device=dev) if meta_bytes else meta_d
             tab_d = tab_t.to(dev, non_blocking=True)
             seed_d = seed_t.to(dev, non_blocking=True) if seed_t is not None else None
             ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
@@ -366,13 +379,15 @@ class Rater(object):
                 for w in range(windows):
                     lo, hi = bounds[w], bounds[w + 1]
                     ids_d[lo:hi].copy_(ids_t[lo:hi], non_blocking=True)
-                    meta_d[lo:hi].copy_(meta_t[lo:hi], non_blocking=True)
+                    meta_in[lo:hi].copy_(meta_t[lo:hi], non_blocking=True)
                     ev = torch.cuda.Event()
                     ev.record(side)
                     ready.append(ev)
             for w in range(windows):
                 lo, hi = bounds[w], bounds[w + 1]
                 cur.wait_event(ready[w])
+                if meta_bytes:
+                    self.widen_meta(meta_in[lo:hi], meta_d[lo:hi])
                 flags = (L.STREAM_LOAD if w == 0 else 0) | (L.STREAM_STORE if w == windows - 1 else 0)
                 pred = self.link_pred(ids_d[lo:hi], meta_d[lo:hi], ptab.n_players, ptab.mode_cols, seq_base=lo, last=last)
                 self.rate_stream(ptab, ids_d[lo:hi], meta_d[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags)
@@ -381,6 +396,8 @@ class Rater(object):
         else:
             ids_d = ids_t.to(dev, non_blocking=True)
             meta_d = meta_t.to(dev, non_blocking=True)
+            if meta_bytes:
+                meta_d = self.widen_meta(meta_d)
             tab_d = tab_t.to(dev, non_blocking=True)
             seed_d = seed_t.to(dev, non_blocking=True) if seed_t is not None else None
             ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)

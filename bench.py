@@ -494,7 +494,7 @@ def run_b200(a):
     e2e = None
     if not a.skip_e2e:
         ids_h = ids_d.cpu().pin_memory()
-        meta_h = meta_d.cpu().pin_memory()
+        meta_h = meta_d.cpu().to(torch.uint8).pin_memory()    # the meta word uses 8 bits: shipped as bytes
         tab_h = table0.cpu().pin_memory()
         out_h = torch.empty_like(tab_h).pin_memory()
         k_e2e = max(1, min(a.steps, 5))
@@ -513,7 +513,7 @@ def run_b200(a):
             dt = float(t.cpu()[0])
         # the e2e result must be the same table the device-resident path produced
         assert torch.equal(out_h, final[a.path].cpu()), "e2e table differs from the HBM-resident run"
-        h2d = ids_h.numel() * 4 + meta_h.numel() * 4 + tab_h.numel() * 8
+        h2d = ids_h.numel() * 4 + meta_h.numel() * meta_h.element_size() + tab_h.numel() * 8
         e2e = {"value": n * world / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": out_h.numel() * 8 + 8 + 16, "ms_per_step": dt * 1e3, "steps": k_e2e}
 

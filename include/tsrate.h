@@ -249,6 +249,11 @@ int ts_seed_table(const double *rank_points_ranked, const double *rank_points_bl
                   int64_t n_players, double unknown_player_sigma, const double vst_points[31], double *seed,
                   uint8_t *bad, void *stream);
 
+/* Ingest helper: the meta word uses its low 8 bits only, so a host may ship the
+ * column as bytes (a quarter of its PCIe volume) and widen it on the device.
+ * No counterpart in the reference (it has no columnar format). */
+int ts_widen_meta(const uint8_t *meta8, int64_t n_matches, uint32_t *meta, void *stream);
+
 /* Synthetic ladders of BASELINE.json's configs (SURVEY.md 8d "Generator"):
  * counter-based, so any window [first, first+count) can be produced on its
  * own.  No counterpart in the reference (it has no benchmark input). */

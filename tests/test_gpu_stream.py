@@ -256,6 +256,14 @@ def test_rate_batch_pipelined_windows(eng):
     a = r.rate_batch(ids_h, meta_h, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=5)
     b = r.rate_batch(ids_h, meta_h, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=1)
     assert np.array_equal(a["table"], b["table"]) and a["errors"] == b["errors"] == 0
+    # the meta column shipped as bytes and widened on the device: same result, both ingest forms
+    meta8 = meta_h.to(torch.uint8).pin_memory()
+    for windows in (5, 1):
+        c = r.rate_batch(ids_h, meta8, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=windows)
+        assert np.array_equal(a["table"], c["table"]) and c["errors"] == 0
+    d = r.rate_batch(ids_h.numpy().view(np.uint32), meta_h.numpy().astype(np.uint8), tab_h.numpy(), shared_col=-1,
+                     mode_cols=[-1, 0], path="rounds")
+    assert np.abs(a["table"] - d["table"]).max() < TOL
     r.close()
 
 
