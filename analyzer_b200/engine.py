@@ -352,9 +352,11 @@ class Rater(object):
                     mode_cols = [c if i == rated[0] else -1 for i, c in enumerate(mode_cols)]
             stream = tab_t.shape[1] <= 16 and any(c >= 0 for c in mode_cols)
         if windows is None:
-            # ~1M matches per window, at most 8: enough to hide all but the last window's
-            # link + rate behind the PCIe copy of the stream
-            windows = max(1, min(8, n // 1_000_000)) if (stream and not want_outputs) else 1
+            # The GPU needs about as long for a window as PCIe needs to deliver it, and every
+            # window costs ~0.27 ms of fixed GPU time (launches, look-back chains, ramp-up of the
+            # rating kernel): T(W) ~ first copy + W * fixed + total work has its minimum near
+            # 2.5M matches per window (scripts/e2e_windows.py, scripts/e2e_timeline.py)
+            windows = max(1, min(8, n // 2_500_000)) if (stream and not want_outputs) else 1
         self.reset_errors()
         if stream and windows > 1:
             # Pipelined ingest: the match stream is copied window by window on a side
