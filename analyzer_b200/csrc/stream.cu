@@ -17,14 +17,14 @@
 // four version fields equal the version it waits for.  Same idea as the
 // low-latency flag protocols of collective libraries.
 //
-// Progress: blocks take tiles of consecutive matches round-robin in increasing
+// Progress: warps take tiles of consecutive matches round-robin in increasing
 // order and the grid is co-resident (cooperative launch), so the oldest
 // unfinished match never waits on unstarted work.  Inside a warp the wait loop
-// is warp-uniform and ready groups finish whole matches inside an iteration, so
-// a match may depend on another match of the same warp.
+// is warp-uniform and complete groups finish whole matches inside an iteration,
+// so a match may depend on another match of the same warp.
 //
-// Single-pair ladders only (table.row_pairs == 1, shared_col == -1): the
-// faithful shared + queue layout keeps using ts_rate.
+// This file: single-pair ladders (table.row_pairs == 1, shared_col == -1) and the
+// ts_rate_stream entry point; the shared + queue layouts are in stream_pair.cu.
 #include "stream_common.cuh"
 
 namespace {
@@ -54,7 +54,7 @@ struct StreamArgs {
     const uint32_t *pred;
     uint32_t n_matches;
     uint32_t seq_base;            // stream-wide number of the first match of this window
-    uint32_t sleep_ns;            // back-off between polls of a waiting group
+    uint32_t sleep_ns;            // back-off between polls when no group of the warp is complete
     uint32_t max_spins;           // watchdog: fruitless polls before a warp declares the stream stalled
     ts_outputs out;
     unsigned long long *ctrl;
@@ -73,11 +73,6 @@ using tsvw::trunc_vw;
 #ifndef TS_STREAM_HOIST
 #define TS_STREAM_HOIST 0
 #endif
-
-// bit g * L of a lane mask: the first lane of every group of L lanes
-template <int L>
-constexpr uint32_t kGroupBase = L == 1 ? 0xFFFFFFFFu : L == 2 ? 0x55555555u : L == 4 ? 0x11111111u
-                              : L == 8 ? 0x01010101u : L == 16 ? 0x00010001u : 0x00000001u;
 
 // per-warp staging buffers: a warp owns W = 32 / L consecutive matches at a time
 template <int P, int W>
@@ -214,11 +209,7 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
                 }
 #endif
             }
-            const uint32_t rb = __ballot_sync(0xFFFFFFFFu, ready);
-            uint32_t complete = rb;             // bit g * L: all L lanes of group g are ready
-#pragma unroll
-            for (int o = 1; o < L; o <<= 1) complete &= complete >> o;
-            complete &= kGroupBase<L>;
+            const uint32_t complete = complete_groups<L>(ready);
             if (complete == 0u) {
                 if ((++spins & 0x3FFu) == 0u) {
                     if (spins >= a.max_spins && wl == 0) atomicExch(&a.ctrl[CTRL_STALLED], 1ull);
@@ -262,15 +253,10 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
                 ss_q = u ? fma(e_sg[k], e_sg[k], ss_q) : ss_q;
                 cnts += (u ? (sgn[k] > 0.0 ? 1u : 256u) : 0u) + ((u && e_sg[k] == 0.0) ? 65536u : 0u);
             }
-            if (L > 1) {
-#pragma unroll
-                for (int o = L / 2; o > 0; o >>= 1) {
-                    d_q += __shfl_xor_sync(0xFFFFFFFFu, d_q, o);
-                    c2_q += __shfl_xor_sync(0xFFFFFFFFu, c2_q, o);
-                    ss_q += __shfl_xor_sync(0xFFFFFFFFu, ss_q, o);
-                    cnts += __shfl_xor_sync(0xFFFFFFFFu, cnts, o);
-                }
-            }
+            d_q = group_sum<L>(d_q);
+            c2_q = group_sum<L>(c2_q);
+            ss_q = group_sum<L>(ss_q);
+            cnts = group_sum_u32<L>(cnts);
             const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
             int status = TS_ST_OK;
             if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;

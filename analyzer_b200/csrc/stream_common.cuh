@@ -64,18 +64,35 @@ __device__ __forceinline__ void cp_async_4(void *smem, const void *gmem)
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// bit g * L of a lane mask: the first lane of every group of L lanes
 template <int L>
-__device__ __forceinline__ double group_sum(double x, uint32_t gmask)
+constexpr uint32_t kGroupBase = L == 1 ? 0xFFFFFFFFu : L == 2 ? 0x55555555u : L == 4 ? 0x11111111u
+                              : L == 8 ? 0x01010101u : L == 16 ? 0x00010001u : 0x00000001u;
+
+// From the ballot of the lanes that have everything they wait for: bit g * L set where all L
+// lanes of match group g are ready.  Executed by the whole warp.
+template <int L>
+__device__ __forceinline__ uint32_t complete_groups(bool ready)
+{
+    uint32_t c = __ballot_sync(0xFFFFFFFFu, ready);
+#pragma unroll
+    for (int o = 1; o < L; o <<= 1) c &= c >> o;
+    return c & kGroupBase<L>;
+}
+
+// sum over the L lanes of every group; executed by the whole converged warp
+template <int L>
+__device__ __forceinline__ double group_sum(double x)
 {
 #pragma unroll
-    for (int o = L / 2; o > 0; o >>= 1) x += __shfl_xor_sync(gmask, x, o, L);
+    for (int o = L / 2; o > 0; o >>= 1) x += __shfl_xor_sync(0xFFFFFFFFu, x, o);
     return x;
 }
 template <int L>
-__device__ __forceinline__ uint32_t group_sum_u32(uint32_t x, uint32_t gmask)
+__device__ __forceinline__ uint32_t group_sum_u32(uint32_t x)
 {
 #pragma unroll
-    for (int o = L / 2; o > 0; o >>= 1) x += __shfl_xor_sync(gmask, x, o, L);
+    for (int o = L / 2; o > 0; o >>= 1) x += __shfl_xor_sync(0xFFFFFFFFu, x, o);
     return x;
 }
 

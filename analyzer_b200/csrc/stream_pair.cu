@@ -63,11 +63,6 @@ struct PairArgs {
 
 constexpr uint32_t kOrdMask = 1023u;
 
-// bit g * L of a lane mask: the first lane of every group of L lanes
-template <int L>
-constexpr uint32_t kGroupBase = L == 1 ? 0xFFFFFFFFu : L == 2 ? 0x55555555u : L == 4 ? 0x11111111u
-                              : L == 8 ? 0x01010101u : L == 16 ? 0x00010001u : 0x00000001u;
-
 __device__ __forceinline__ void ld_ord(const unsigned long long *p, unsigned long long (&w)[2])
 {
     asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(p) : "memory");
@@ -231,11 +226,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
                 }
 #endif
             }
-            const uint32_t rb = __ballot_sync(0xFFFFFFFFu, ready);
-            uint32_t complete = rb;             // bit g * L: all L lanes of group g are ready
-#pragma unroll
-            for (int o = 1; o < L; o <<= 1) complete &= complete >> o;
-            complete &= kGroupBase<L>;
+            const uint32_t complete = complete_groups<L>(ready);
             if (complete == 0u) {
                 if ((++spins & 0x3FFu) == 0u) {      // watchdog, see stream.cu
                     if (spins >= a.max_spins && wl == 0) atomicExch(&a.ctrl[CTRL_STALLED], 1ull);
@@ -287,17 +278,12 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
                 ss_q = u ? fma(eq_sg[k], eq_sg[k], ss_q) : ss_q;
                 cnts += (u ? (sgn[k] > 0.0 ? 1u : 256u) : 0u) + (bad ? 65536u : 0u);
             }
-            if (L > 1) {
-#pragma unroll
-                for (int o = L / 2; o > 0; o >>= 1) {
-                    d_s += __shfl_xor_sync(0xFFFFFFFFu, d_s, o);
-                    c2_s += __shfl_xor_sync(0xFFFFFFFFu, c2_s, o);
-                    d_q += __shfl_xor_sync(0xFFFFFFFFu, d_q, o);
-                    c2_q += __shfl_xor_sync(0xFFFFFFFFu, c2_q, o);
-                    ss_q += __shfl_xor_sync(0xFFFFFFFFu, ss_q, o);
-                    cnts += __shfl_xor_sync(0xFFFFFFFFu, cnts, o);
-                }
-            }
+            d_s = group_sum<L>(d_s);
+            c2_s = group_sum<L>(c2_s);
+            d_q = group_sum<L>(d_q);
+            c2_q = group_sum<L>(c2_q);
+            ss_q = group_sum<L>(ss_q);
+            cnts = group_sum_u32<L>(cnts);
             const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
             int status = TS_ST_OK;
             if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
