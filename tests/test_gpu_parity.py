@@ -150,6 +150,12 @@ def test_schedule_edge_cases(eng, rater, c_oracle):
     from analyzer_b200._lib import TsError
     with pytest.raises(TsError):
         rater.schedule(_dev(ids), _dev(meta), 6, cols, offsets_cap=3)
+    # other team sizes (2v2, 8v8): the run-time-slots form of the rounds kernel
+    rng = np.random.default_rng(3)
+    for slots in (4, 16):
+        ids, meta = H.small_ladder(rng, 3000, 200, slots=slots, modes=(1,), p_afk=0.05, ragged=True)
+        sch = rater.schedule(_dev(ids), _dev(meta), 200, cols)
+        assert _check_schedule(c_oracle, sch, ids, meta, cols, 200) > 10
     # empty batch
     sch = rater.schedule(torch.empty((0, 6), dtype=torch.int32, device="cuda"),
                          torch.empty((0,), dtype=torch.int32, device="cuda"), 6, cols)
