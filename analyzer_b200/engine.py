@@ -335,14 +335,17 @@ class Rater(object):
         ids_t, meta_t, tab_t, seed_t = host(ids, True), host(meta, True), host(table), host(seed)
         n, p = ids_t.shape
         meta_bytes = meta_t.element_size() == 1
-        # Single-pair ladders take the streaming (dataflow) path when chains are deep
-        # (several matches per player: latency-bound, barriers hurt); sparse ladders over a
-        # table much larger than the batch are bandwidth-bound and cheaper round by round
-        # (16-byte rows, no versioned copy of the table).  Measured crossover, DESIGN.md 4.
-        stream = path == "stream" or (path == "auto" and shared_col < 0 and tab_t.shape[1] == 1
-                                       and p in (6, 10) and n > 0 and n * p >= 2 * tab_t.shape[0])
+        # The streaming (dataflow) path wins whenever the versioned rows stay in L2 (small tables,
+        # whatever the batch: 0.47 vs 0.58 ms for 500 matches) or chains are deep (several matches
+        # per player: latency-bound, barriers hurt); a sparse batch over a table far larger than L2
+        # is bandwidth-bound and cheaper round by round (16-byte rows, no versioned copy of the
+        # whole table).  Measured crossovers, DESIGN.md 4.
+        n_players = tab_t.shape[0]
+        row_bytes = 32 if shared_col < 0 else 32 * (2 + len(set(c for c in mode_cols if c >= 0)))
+        worth = n > 0 and p in (6, 10) and (n_players * row_bytes <= (64 << 20) or n * p >= 2 * n_players)
+        stream = path == "stream" or (path == "auto" and shared_col < 0 and tab_t.shape[1] == 1 and worth)
         mode_cols = list(mode_cols)
-        if path == "auto" and shared_col >= 0 and p in (6, 10) and n * p >= 2 * tab_t.shape[0]:
+        if path == "auto" and shared_col >= 0 and worth:
             # shared + queue layout: a batch that rates one queue column only gets the compact
             # 64-byte rows under one version; a batch that mixes game modes the ordinal-tagged rows
             bits = torch.unique((meta_t >> L.META_MODE_SHIFT) & 15).tolist() if n <= 4_000_000 else None
