@@ -303,14 +303,19 @@ class Rater(object):
         L.check(self._lib.ts_reset_errors(self._ctx, _stream_ptr()))
 
     def alloc_outputs(self, n, p, device=None):
+        """Device buffers for every rate_match output (NaN = not written).  The four float64
+        outputs are views of one flat buffer (key "_flat"): one fill, one copy back."""
         dev = device or self.device
-        nan = float("nan")
-        return dict(
-            quality=torch.full((n,), nan, dtype=torch.float64, device=dev),
-            out_shared=torch.full((n, p, 2), nan, dtype=torch.float64, device=dev),
-            out_delta=torch.full((n, p), nan, dtype=torch.float64, device=dev),
-            out_queue=torch.full((n, p, 2), nan, dtype=torch.float64, device=dev),
-            status=torch.zeros((n,), dtype=torch.uint8, device=dev))
+        flat = torch.full((n * (1 + 5 * p) + 8,), float("nan"), dtype=torch.float64, device=dev)
+        o = 0
+        outs = {}
+        for key, shape in (("quality", (n,)), ("out_shared", (n, p, 2)), ("out_delta", (n, p)), ("out_queue", (n, p, 2))):
+            k = int(np.prod(shape))
+            outs[key] = flat[o:o + k].view(shape)
+            o = (o + k + 1) & ~1          # the pair outputs are stored as 16-byte double2
+        outs["status"] = torch.zeros((n,), dtype=torch.uint8, device=dev)
+        outs["_flat"] = flat
+        return outs
 
     # ------------------------------------------------------------------
     def rate_batch(self, ids, meta, table, seed=None, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6),
@@ -348,7 +353,8 @@ class Rater(object):
         if path == "auto" and shared_col >= 0 and worth:
             # shared + queue layout: a batch that rates one queue column only gets the compact
             # 64-byte rows under one version; a batch that mixes game modes the ordinal-tagged rows
-            bits = torch.unique((meta_t >> L.META_MODE_SHIFT) & 15).tolist() if n <= 4_000_000 else None
+            bits = np.flatnonzero(np.bincount((meta_t.numpy() >> L.META_MODE_SHIFT) & 15, minlength=16)).tolist() \
+                if n <= 4_000_000 else None
             if bits is not None:
                 rated = [m for m in bits if m < len(mode_cols) and m < N_MODES and mode_cols[m] >= 0]
                 if len(rated) == 1:
@@ -419,8 +425,13 @@ class Rater(object):
         bad = self.error_count()
         result = dict(n_rounds=n_rounds, errors=bad)
         if outs is not None:
-            for k, t in outs.items():
-                result[k] = t.cpu().numpy()
+            flat_h = outs["_flat"].cpu().numpy()
+            o = 0
+            for k in ("quality", "out_shared", "out_delta", "out_queue"):
+                size = outs[k].numel()
+                result[k] = flat_h[o:o + size].reshape(tuple(outs[k].shape))
+                o = (o + size + 1) & ~1
+            result["status"] = outs["status"].cpu().numpy()
         if bad:
             st = result.get("status")
             if st is not None and np.any(st == L.ST_VALUE_ERROR):
