@@ -24,3 +24,69 @@ for n, u in ((500, 2500), (5000, 20000), (50000, 100000)):
             best = min(best, time.perf_counter() - t0)
         print("%6d matches, %6d players, path=%-6s: %.3f ms per batch (%.3g matches/s), rounds=%s" % (
             n, u, path, best * 1e3, n / best, res["n_rounds"]), flush=True)
+
+# ---- the object API on the same batch size: worker.py's own call pattern (one rate_match per
+# match, worker.py:192) and the batch call (rate_matches), with its three parts ---------------
+import logging
+from analyzer_b200 import rater
+
+
+class Row(object):
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+
+QUEUES = ["trueskill_" + m for m in ("casual", "ranked", "blitz", "br", "5v5_casual", "5v5_ranked")]
+
+
+def graphs(n, u, seed):
+    rng = np.random.default_rng(seed)
+
+    def player(i):
+        p = Row(api_id=str(i), skill_tier=i % 30, rank_points_ranked=None, rank_points_blitz=None,
+                trueskill_mu=None, trueskill_sigma=None)
+        for c in QUEUES:
+            setattr(p, c + "_mu", None)
+            setattr(p, c + "_sigma", None)
+        return p
+
+    players = [player(i) for i in range(u)]
+    out = []
+    for m in range(n):
+        who = rng.choice(u, size=6, replace=False)
+        rosters = []
+        for t in range(2):
+            parts = []
+            for i in who[3 * t:3 * t + 3]:
+                items = Row(any_afk=None)
+                for c in QUEUES:
+                    setattr(items, c + "_mu", None)
+                    setattr(items, c + "_sigma", None)
+                parts.append(Row(player=[players[i]], participant_items=[items], went_afk=0, trueskill_mu=None,
+                                 trueskill_sigma=None, trueskill_delta=None))
+            rosters.append(Row(winner=(t == m % 2), participants=parts))
+        out.append(Row(api_id=str(m), game_mode=("casual", "ranked", "blitz")[m % 3], rosters=rosters,
+                       participants=rosters[0].participants + rosters[1].participants, trueskill_quality=None))
+    return out
+
+
+rater.logger.setLevel(logging.WARNING)
+rater.rate_matches(graphs(500, 2500, 2))            # warm-up
+for rep in range(2):
+    ms = graphs(500, 2500, 10 + rep)
+    t0 = time.perf_counter()
+    b = rater.ingest(ms)
+    t1 = time.perf_counter()
+    res = rater._rater(0).rate_batch(b.ids, b.meta, b.table, seed=b.seed, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6),
+                                     want_outputs=True)
+    t2 = time.perf_counter()
+    rater._write_back(b, res)
+    t3 = time.perf_counter()
+    print("rate_matches(500 match graphs, %d players): %.2f ms = ingest %.2f + rate_batch %.2f + write-back %.2f" % (
+        len(b.players), (t3 - t0) * 1e3, (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3))
+ms = graphs(300, 2500, 3)
+t0 = time.perf_counter()
+for m in ms:
+    rater.rate_match(m)
+dt = time.perf_counter() - t0
+print("rate_match per match (worker.py unchanged), 300 calls: %.3f ms per call (%.3g matches/s)" % (dt / 300 * 1e3, 300 / dt))
