@@ -10,7 +10,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libtsrate.so")
-SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "stream_pair.cu", "static_sched.cu"]
+SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "stream_pair.cu", "shard.cu", "static_sched.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-shared", "-Xcompiler", "-fPIC"]
 
@@ -28,7 +28,11 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_static", "ts_schedule_static_max_slot_entries",
            "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream",
            "ts_stream_stalled", "ts_rate_stream_table_workspace_bytes",
-           "ts_seed_table", "ts_widen_meta", "ts_link_pred_sharded", "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_rate_stream_sharded"]
+           "ts_seed_table", "ts_widen_meta", "ts_error_counts",
+           "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_shard_local_matches",
+           "ts_shard_link_workspace_bytes", "ts_shard_reset", "ts_shard_link", "ts_shard_rate", "ts_shard_status"]
+SHARD_BLOCK, SHARD_MAX = 32, 16
+SHARD_STALLED, SHARD_OVERFLOW, SHARD_DUPLICATE = 1, 2, 4
 
 
 class TsParams(C.Structure):
@@ -50,6 +54,12 @@ class TsSchedInfo(C.Structure):
 class TsOutputs(C.Structure):
     _fields_ = [("quality", C.c_void_p), ("out_shared", C.c_void_p), ("out_delta", C.c_void_p),
                 ("out_queue", C.c_void_p), ("status", C.c_void_p)]
+
+
+class TsShardView(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("n_shards", C.c_int32),
+                ("ids", C.c_void_p * 16), ("meta", C.c_void_p * 16), ("succ", C.c_void_p * 16),
+                ("rows", C.c_void_p * 16), ("table", C.c_void_p * 16)]
 
 
 class TsGen(C.Structure):
@@ -122,16 +132,21 @@ def lib():
                                      C.c_void_p, C.c_int64, C.c_void_p]
         L.ts_rate_stream_table_workspace_bytes.restype = C.c_int64
         L.ts_rate_stream_table_workspace_bytes.argtypes = [C.POINTER(TsTable)]
-        L.ts_link_pred_sharded.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int64,
-                                           C.POINTER(C.c_int8), C.c_int64, C.c_void_p, C.c_void_p, C.c_int32,
-                                           C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]
         L.ts_shard_alloc.argtypes = [C.c_int, C.c_int64, C.POINTER(C.c_void_p), C.c_void_p]
         L.ts_shard_open.argtypes = [C.c_int, C.c_void_p, C.POINTER(C.c_void_p)]
         L.ts_shard_close.argtypes = [C.c_void_p]
         L.ts_shard_free.argtypes = [C.c_void_p]
-        L.ts_rate_stream_sharded.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_int32, C.c_int32,
-                                             C.POINTER(C.c_void_p), C.c_int8, C.c_void_p, C.c_void_p, C.c_void_p,
-                                             C.c_int64, C.c_int32, C.POINTER(TsOutputs), C.c_int32, C.c_void_p]
+        L.ts_shard_local_matches.restype = C.c_int64
+        L.ts_shard_local_matches.argtypes = [C.c_int64, C.c_int32, C.c_int32]
+        L.ts_shard_link_workspace_bytes.restype = C.c_int64
+        L.ts_shard_link_workspace_bytes.argtypes = [C.c_int64]
+        L.ts_shard_reset.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_void_p]
+        L.ts_shard_link.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_int32, C.c_int64, C.c_int8,
+                                    C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]
+        L.ts_shard_rate.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_int32, C.c_int64, C.c_int8,
+                                    C.c_int64, C.POINTER(TsOutputs), C.c_int32, C.c_int32, C.c_void_p]
+        L.ts_shard_status.argtypes = [C.c_void_p, C.c_void_p]
+        L.ts_error_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_void_p]
         L.ts_stream_stalled.argtypes = [C.c_void_p, C.c_void_p]
         L.ts_seed_table.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double,
                                     C.POINTER(C.c_double), C.c_void_p, C.c_void_p, C.c_void_p]

@@ -80,18 +80,31 @@ extern "C" void ts_ctx_destroy(ts_ctx *ctx)
 
 extern "C" int ts_sm_count(const ts_ctx *ctx) { return ctx ? ctx->sm_count : 0; }
 
-extern "C" int64_t ts_error_count(ts_ctx *ctx, void *stream)
+extern "C" int ts_error_counts(ts_ctx *ctx, int64_t *fp_errors, int64_t *value_errors, void *stream)
 {
     if (!ctx) return TS_E_ARG;
-    unsigned long long v = 0;
-    TS_CUDA(cudaMemcpyAsync(&v, ctx->d_ctrl + CTRL_ERRORS, sizeof v, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    unsigned long long fp = 0, val = 0;
+    TS_CUDA(cudaMemcpyAsync(&fp, ctx->d_ctrl + CTRL_ERRORS, sizeof fp, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    TS_CUDA(cudaMemcpyAsync(&val, ctx->d_ctrl + CTRL_VALUE_ERRORS, sizeof val, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     TS_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
-    return (int64_t)v;
+    if (fp_errors) *fp_errors = (int64_t)fp;
+    if (value_errors) *value_errors = (int64_t)val;
+    return 0;
+}
+
+extern "C" int64_t ts_error_count(ts_ctx *ctx, void *stream)
+{
+    int64_t fp = 0, val = 0;
+    if (int rc = ts_error_counts(ctx, &fp, &val, stream)) return rc;
+    return fp + val;
 }
 
 extern "C" int ts_reset_errors(ts_ctx *ctx, void *stream)
 {
     if (!ctx) return TS_E_ARG;
-    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_ERRORS, 0, sizeof(unsigned long long), (cudaStream_t)stream));
+    cudaStream_t s = (cudaStream_t)stream;
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_ERRORS, 0, sizeof(unsigned long long), s));
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_VALUE_ERRORS, 0, 2 * sizeof(unsigned long long), s));   // + CTRL_SHARD
     return 0;
 }

@@ -18,10 +18,12 @@ struct ts_ctx {
     unsigned long long *d_ctrl;  // TS_CTRL_BYTES of control words, layout below
 };
 
-// Control words (device): word 0 barrier counter, 2 error count, 3 queue tail,
-// 4 tail snapshot, 5 stall flag of the streaming kernel, 8..10 rotating per-level
-// words of the frontier sweep.
-enum { CTRL_ARRIVE = 0, CTRL_ERRORS = 2, CTRL_TAIL = 3, CTRL_STALLED = 5, CTRL_LEVEL = 8, CTRL_WORDS = 16 };
+// Control words (device): word 0 barrier counter, 2 matches that ended in TS_ST_FP_ERROR,
+// 3 queue tail, 4 tail snapshot, 8..10 rotating per-level words of the frontier sweep;
+// sticky until ts_reset_errors: 5 stall flag of the streaming kernels, 12 matches that
+// ended in TS_ST_VALUE_ERROR, 13 TS_SHARD_* bits of the sharded ladder.
+enum { CTRL_ARRIVE = 0, CTRL_ERRORS = 2, CTRL_TAIL = 3, CTRL_STALLED = 5, CTRL_LEVEL = 8, CTRL_VALUE_ERRORS = 12,
+       CTRL_SHARD = 13, CTRL_WORDS = 16 };
 constexpr size_t TS_CTRL_BYTES = CTRL_WORDS * 8;
 
 void ts_set_error(const char *fmt, ...);

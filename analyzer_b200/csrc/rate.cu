@@ -33,6 +33,7 @@ struct RateArgs {
     ts_params prm;
     double *table;
     const double *seed;
+    uint32_t n_players;           // ids at or beyond it are refused (TS_ST_VALUE_ERROR), never dereferenced
     int32_t row_pairs;
     int32_t shared_col;
     ModeCols modes;
@@ -173,6 +174,7 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
             bool used[SPL], had[SPL];
             double d_s = 0.0, c2_s = 0.0, d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
             uint32_t cnts = 0;   // n_first | n_second << 8 | bad << 16
+            bool bad_id = false;
 
             // issue every gather of this lane before consuming any of them
             double2 raw_s[SPL], raw_q[SPL];
@@ -181,6 +183,7 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
                 const int s = lane + k * L;
                 pid[k] = (live && s < P) ? stage.ids[cur][grp * P + s] : TS_EMPTY_SLOT;
                 used[k] = pid[k] != TS_EMPTY_SLOT;
+                if (used[k] && pid[k] >= a.n_players) { used[k] = false; bad_id = true; }   // corrupt id: no table access
                 raw_s[k] = make_double2(0.0, 1.0);
                 raw_q[k] = make_double2(0.0, 1.0);
                 if (used[k]) {
@@ -225,6 +228,7 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
                 ss_q = fma(qd.y, qd.y, ss_q);
                 cnts += (sgn[k] > 0.0 ? 1u : 256u) + (bad ? 65536u : 0u);
             }
+            cnts += bad_id ? 65536u : 0u;
             if (L > 1) {
                 if (SHARED) { d_s = group_sum<L>(d_s); c2_s = group_sum<L>(c2_s); }
                 d_q = group_sum<L>(d_q);
@@ -250,7 +254,7 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
             const uint32_t m = (live && want_order) ? stage.order[cur][grp] : 0u;
             if (live && lane == 0) {
                 if (a.out.status) a.out.status[m] = (uint8_t)status;
-                if (status != TS_ST_OK) atomicAdd(&a.ctrl[CTRL_ERRORS], 1ull);
+                if (status != TS_ST_OK) atomicAdd(&a.ctrl[status == TS_ST_VALUE_ERROR ? CTRL_VALUE_ERRORS : CTRL_ERRORS], 1ull);
                 else if (a.out.quality) {
                     // rater.py:141 on the queue-specific pre-update ratings (no tau)
                     const double nb2 = (double)n * beta2;
@@ -370,6 +374,7 @@ extern "C" int ts_rate(ts_ctx *ctx, const ts_table *table, const uint32_t *ids_s
     a.prm = ctx->params;
     a.table = table->data;
     a.seed = table->seed;
+    a.n_players = (uint32_t)(table->n_players > 0xFFFFFFFFll ? 0xFFFFFFFFll : table->n_players);
     a.row_pairs = table->row_pairs;
     a.shared_col = table->shared_col;
     for (int i = 0; i < 16; ++i) a.modes.col[i] = i < 6 ? table->mode_col[i] : (int8_t)-1;

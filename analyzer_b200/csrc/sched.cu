@@ -49,11 +49,6 @@ struct KeySrc {
     uint32_t sentinel;
     int from_ids;
     unsigned long long slots_magic;   // floor(2^64 / slots) + 1: idx / slots == umul64hi(idx, magic) for idx < 2^32
-    // sharded linking: this rank links only the players p with (p & owner_mask) == owner_rank and
-    // sorts them by their local index p >> owner_shift; other slots become the sentinel.
-    // drop: sentinel keys leave the sort in pass 0 (the later passes see only *n_dev entries).
-    uint32_t owner_mask, owner_rank, owner_shift;
-    int drop;
     uint32_t rated_mask;   // bit m set: game mode m is rated (a register test instead of indexing modes.col)
 };
 
@@ -64,8 +59,7 @@ __device__ __forceinline__ uint32_t load_key(const KeySrc &src, uint32_t idx)
         uint32_t m = __ldg(src.meta + (uint32_t)__umul64hi((unsigned long long)idx, src.slots_magic));
         const bool gated = ((src.rated_mask >> ((m >> TS_META_MODE_SHIFT) & 15u)) & 1u) == 0u ||
                            (m & (TS_META_AFK | TS_META_INVALID)) != 0u;
-        if (k == TS_EMPTY_SLOT || gated || (k & src.owner_mask) != src.owner_rank) k = src.sentinel;
-        else k >>= src.owner_shift;
+        if (k == TS_EMPTY_SLOT || gated) k = src.sentinel;
     }
     return k;
 }
@@ -252,14 +246,14 @@ constexpr int kMaxPasses = 4;
 constexpr int kTotalsWords = kMaxPasses * 256 + 64;    // digit bases of every pass + the ticket
 
 __global__ void __launch_bounds__(kSortBlock)
-k_radix_hist_all(KeySrc src, uint32_t n, int passes, uint32_t *ghist)
+k_radix_hist_all(KeySrc src, uint32_t n_in, const uint32_t *n_dev, int passes, uint32_t *ghist)
 {
+    const uint32_t n = n_dev ? __ldg(n_dev) : n_in;
     __shared__ uint32_t h[kMaxPasses][256];
     for (int i = threadIdx.x; i < kMaxPasses * 256; i += kSortBlock) (&h[0][0])[i] = 0;
     __syncthreads();
     for (uint32_t idx = blockIdx.x * kSortBlock + threadIdx.x; idx < n; idx += gridDim.x * kSortBlock) {
         const uint32_t k = load_key(src, idx);
-        if (src.drop && k == src.sentinel) continue;
         for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(k >> (8 * p)) & 255u], 1u);
     }
     __syncthreads();
@@ -288,9 +282,7 @@ k_radix_hist_matches(KeySrc src, uint32_t n_matches, int passes, uint32_t *ghist
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 uint32_t k = e ? two.y : two.x;
-                if (k == TS_EMPTY_SLOT || gated || (k & src.owner_mask) != src.owner_rank) k = src.sentinel;
-                else k >>= src.owner_shift;
-                if (src.drop && k == src.sentinel) continue;
+                if (k == TS_EMPTY_SLOT || gated) k = src.sentinel;
                 for (int p = 0; p < passes; ++p) atomicAdd(&h[p][(k >> (8 * p)) & 255u], 1u);
             }
         }
@@ -303,7 +295,7 @@ k_radix_hist_matches(KeySrc src, uint32_t n_matches, int passes, uint32_t *ghist
 }
 
 // exclusive scan of each pass's 256 digit totals (one block, thread = digit)
-__global__ void __launch_bounds__(256) k_radix_scan_all(uint32_t *ghist, int passes, uint32_t *n_dev)
+__global__ void __launch_bounds__(256) k_radix_scan_all(uint32_t *ghist, int passes)
 {
     __shared__ uint32_t s[256];
     for (int p = 0; p < passes; ++p) {
@@ -312,7 +304,6 @@ __global__ void __launch_bounds__(256) k_radix_scan_all(uint32_t *ghist, int pas
         if (threadIdx.x == 0) {
             uint32_t run = 0;
             for (int d = 0; d < 256; ++d) { uint32_t c = s[d]; s[d] = run; run += c; }
-            if (p == 0) *n_dev = run;          // entries that stay in the sort
         }
         __syncthreads();
         ghist[p * 256 + threadIdx.x] = s[threadIdx.x];
@@ -331,7 +322,7 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t *p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-template <bool DROP>      // DROP: sentinel keys leave the sort in this pass (sharded linking, pass 0)
+// n_dev (optional): the number of entries lives on the device (the owned slots of a sharded ladder)
 __global__ void __launch_bounds__(kSortBlock, TS_SORT_MIN_BLOCKS)
 k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n_in, const uint32_t *n_dev, int shift,
                  const uint32_t *digit_base, uint32_t *status, uint32_t *ticket, uint32_t *keys_out,
@@ -350,6 +341,7 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
     __syncthreads();
     const uint32_t tile = s_tile;
     const uint32_t tile_base = tile * kSortTile;
+    if (tile_base >= n) return;            // beyond the device-side count: no earlier tile waits for this one
     const uint32_t wbase = tile_base + warp * (kSortItems * 32);
     uint32_t key[kSortItems], off[kSortItems];
 #pragma unroll
@@ -360,7 +352,7 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
-        bool ok = idx < n && !(DROP && key[k] == src.sentinel);
+        bool ok = idx < n;
         const uint32_t d = (key[k] >> shift) & 255u;
         uint32_t peers = __ballot_sync(0xFFFFFFFFu, ok);
         peers = ok ? peers : ~peers;
@@ -416,19 +408,14 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
-        if (idx < n && !(DROP && key[k] == src.sentinel)) {
+        if (idx < n) {
             uint32_t pos = wcount[warp][(key[k] >> shift) & 255u] + off[k];
             skey[pos] = key[k];
             sval[pos] = ident_vals ? idx : __ldg(vals_in + idx);
         }
     }
     __syncthreads();
-    uint32_t cnt = tile_base < n ? min((uint32_t)kSortTile, n - tile_base) : 0u;
-    if (DROP) {                             // only the elements of this tile that stay in the sort
-        cnt = 0;
-#pragma unroll
-        for (int w = 0; w < kWarps; ++w) cnt += warp_tot[w];
-    }
+    const uint32_t cnt = min((uint32_t)kSortTile, n - tile_base);
     for (uint32_t i = threadIdx.x; i < cnt; i += kSortBlock) {
         uint32_t k = skey[i];
         uint32_t pos = gbase[(k >> shift) & 255u] + i;
@@ -787,6 +774,21 @@ Workspace carve(char *base, int64_t n_matches, int32_t slots)
     return w;
 }
 
+// sort buffers only (ts_link_pred, ts_shard_link): two (key, val) buffers of np entries, the
+// tile status rows and the digit totals
+Workspace carve_link(char *base, uint32_t np)
+{
+    Workspace w;
+    size_t off = 0, n_blocks = ((size_t)np + kSortTile - 1) / kSortTile;
+    auto take = [&](size_t bytes) { char *p = base + off; off += align_up(bytes); return (uint32_t *)p; };
+    for (int i = 0; i < 2; ++i) { w.keys[i] = take((size_t)np * 4); w.vals[i] = take((size_t)np * 4); }
+    w.hist = take((n_blocks * 256 + 256) * 4);
+    w.totals = take(kTotalsWords * 4);
+    w.succ = w.pending = w.queue = nullptr;
+    w.bytes = off;
+    return w;
+}
+
 int frontier_blocks_per_sm_cap()
 {
     static int cap = -1;
@@ -851,44 +853,39 @@ int radix_onesweep_enabled()
 // LSD radix sort of n (key, val) pairs on the low `bits` bits.  Pass 0 reads
 // `src` (with identity values); results ping-pong between the two buffers.
 // Returns the index of the buffer holding the result (or <0).
+// staged: the pairs already stand in w.keys[0] / w.vals[0] and their number in *n_dev
+// (n is then only an upper bound that sizes the grids): the owned slots of a sharded ladder.
 int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream, int sm_count,
-               const uint32_t **n_dev_out = nullptr)
+               const uint32_t *n_dev = nullptr)
 {
     const int passes = (bits + 7) / 8;
-    if (n_dev_out) *n_dev_out = nullptr;
+    const bool staged = n_dev != nullptr;
     if (n >= (1u << 30) || passes > kMaxPasses || !radix_onesweep_enabled()) {
-        if (src0.drop) {
-            ts_set_error("sharded linking needs the single-sweep sort (fewer than 2^30 slot entries per window)");
+        if (staged) {
+            ts_set_error("the sharded ladder needs the single-sweep sort (fewer than 2^30 owned slot entries per window)");
             return TS_E_UNSUPPORTED;
         }
         return radix_sort_3kernel(src0, n, bits, w, stream);
     }
     const uint32_t n_tiles = (n + kSortTile - 1) / kSortTile;
-    uint32_t *ghist = w.totals, *ticket = w.totals + kMaxPasses * 256, *n_dev = ticket + 1;
-    if (n_dev_out) *n_dev_out = n_dev;
-    if (cudaMemsetAsync(w.totals, 0, kTotalsWords * 4, stream) != cudaSuccess) return ts_cuda_fail(cudaGetLastError(), "memset");
-    if (src0.from_ids && (src0.slots & 1u) == 0u && ((uintptr_t)src0.keys & 7u) == 0u)
+    uint32_t *ghist = w.totals, *ticket = w.totals + kMaxPasses * 256;
+    if (cudaMemsetAsync(ghist, 0, kMaxPasses * 256 * 4, stream) != cudaSuccess) return ts_cuda_fail(cudaGetLastError(), "memset");
+    if (!staged && src0.from_ids && (src0.slots & 1u) == 0u && ((uintptr_t)src0.keys & 7u) == 0u)
         k_radix_hist_matches<<<sm_count * 8, kSortBlock, 0, stream>>>(src0, n / src0.slots, passes, ghist);
     else
-        k_radix_hist_all<<<sm_count * 8, kSortBlock, 0, stream>>>(src0, n, passes, ghist);
-    k_radix_scan_all<<<1, 256, 0, stream>>>(ghist, passes, n_dev);
-    int cur = -1;
+        k_radix_hist_all<<<sm_count * 8, kSortBlock, 0, stream>>>(src0, n, n_dev, passes, ghist);
+    k_radix_scan_all<<<1, 256, 0, stream>>>(ghist, passes);
+    int cur = staged ? 0 : -1;
     for (int p = 0; p < passes; ++p) {
         KeySrc src = src0;
         const uint32_t *vals_in = nullptr;
-        if (p > 0) { src.keys = w.keys[cur]; src.from_ids = 0; src.drop = 0; vals_in = w.vals[cur]; }
+        if (cur >= 0) { src.keys = w.keys[cur]; src.from_ids = 0; vals_in = w.vals[cur]; }
         int dst = cur < 0 ? 0 : ((cur + 1) & 1);
         if (cudaMemsetAsync(w.hist, 0, (size_t)n_tiles * 256 * 4, stream) != cudaSuccess ||
             cudaMemsetAsync(ticket, 0, 4, stream) != cudaSuccess)
             return ts_cuda_fail(cudaGetLastError(), "memset");
-        if (p == 0 && src0.drop)
-            k_radix_onesweep<true><<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, 1, n, nullptr, 0, ghist, w.hist, ticket,
-                                                                       w.keys[dst], w.vals[dst]);
-        else
-            k_radix_onesweep<false><<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, p == 0 ? 1 : 0, n,
-                                                                        (p > 0 && src0.drop) ? n_dev : nullptr, p * 8,
-                                                                        ghist + p * 256, w.hist, ticket, w.keys[dst],
-                                                                        w.vals[dst]);
+        k_radix_onesweep<<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, vals_in ? 0 : 1, n, n_dev, p * 8, ghist + p * 256,
+                                                             w.hist, ticket, w.keys[dst], w.vals[dst]);
         cur = dst;
     }
     cudaError_t e = cudaGetLastError();
@@ -1000,8 +997,6 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
-    src.owner_mask = src.owner_rank = src.owner_shift = 0;
-    src.drop = 0;
     src.rated_mask = 0;
     for (int i = 0; i < 6; ++i) if (src.modes.col[i] >= 0) src.rated_mask |= 1u << i;
     int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
@@ -1011,7 +1006,8 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     TS_CUDA(cudaMemsetAsync(round, 0, (size_t)n * 4, s));
     // barrier words and queue tail/snapshot; the error counter (word 2) is left alone
     if (int rc = ts_reset_barrier(ctx->d_ctrl, s)) return rc;
-    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_TAIL, 0, (CTRL_WORDS - CTRL_TAIL) * sizeof(unsigned long long), s));
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_TAIL, 0, 2 * sizeof(unsigned long long), s));
+    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_LEVEL, 0, 3 * sizeof(unsigned long long), s));
     const bool by_levels = !schedule_frontier_enabled();
     if (by_levels) {
         // links to the previous match of every slot's player, then the rounds by dataflow along them
@@ -1077,8 +1073,6 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     rsrc.sentinel = 0;
     rsrc.from_ids = 0;
     rsrc.slots_magic = 0ull;   // unused: keys are read as they are
-    rsrc.owner_mask = rsrc.owner_rank = rsrc.owner_shift = 0;
-    rsrc.drop = 0;
     rsrc.rated_mask = 0;
     buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s, ctx->sm_count);
     if (buf < 0) return buf;
@@ -1103,10 +1097,9 @@ extern "C" int64_t ts_link_workspace_bytes(int64_t n_matches, int32_t slots)
     return (int64_t)(4 * align_up(np * 4) + align_up((n_blocks * 256 + 256) * 4) + align_up(kTotalsWords * 4));
 }
 
-namespace {
-int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
-                   int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last, uint32_t *pred,
-                   void *workspace, int64_t workspace_bytes, void *stream, int32_t rank, int32_t n_shards)
+extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
+                            int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last,
+                            uint32_t *pred, void *workspace, int64_t workspace_bytes, void *stream)
 {
     if (seq_base < 0 || seq_base + n_matches >= 0xFFFFFFFFll) {
         ts_set_error("ts_link_pred: stream-wide match numbers must stay below 2^32 - 1");
@@ -1129,17 +1122,7 @@ int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64
     TS_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
     const uint32_t np = (uint32_t)n_matches * (uint32_t)slots;
-    Workspace w;
-    {
-        char *base = (char *)workspace;
-        size_t off = 0, n_blocks = ((size_t)np + kSortTile - 1) / kSortTile;
-        auto take = [&](size_t bytes) { char *p = base + off; off += align_up(bytes); return (uint32_t *)p; };
-        for (int i = 0; i < 2; ++i) { w.keys[i] = take((size_t)np * 4); w.vals[i] = take((size_t)np * 4); }
-        w.hist = take((n_blocks * 256 + 256) * 4);
-        w.totals = take(kTotalsWords * 4);
-        w.succ = w.pending = w.queue = nullptr;
-        w.bytes = off;
-    }
+    Workspace w = carve_link((char *)workspace, np);
     KeySrc src;
     src.keys = ids;
     src.meta = meta;
@@ -1148,57 +1131,284 @@ int link_pred_impl(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64
     src.sentinel = (uint32_t)n_players;
     src.from_ids = 1;
     src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
-    src.owner_mask = src.owner_rank = src.owner_shift = 0;
-    src.drop = 0;
     src.rated_mask = 0;
     for (int i = 0; i < 6; ++i) if (src.modes.col[i] >= 0) src.rated_mask |= 1u << i;
-    // sharded: link only the players this rank owns, by local index; every other slot leaves
-    // the sort in pass 0 and keeps the fill value, so an element-wise MIN over the ranks'
-    // pred arrays assembles the complete links (owned entries are < 2^31 or TS_NONE = -1)
-    const bool sharded = n_shards > 1;
-    int shard_shift = 0;
-    while ((1 << shard_shift) < n_shards) ++shard_shift;
-    const int64_t local_players = sharded ? (n_players - rank + n_shards - 1) / n_shards : n_players;
-    if (sharded) {
-        src.owner_mask = (uint32_t)n_shards - 1u;
-        src.owner_rank = (uint32_t)rank;
-        src.owner_shift = (uint32_t)shard_shift;
-        src.sentinel = (uint32_t)local_players;
-        src.drop = 1;
-    }
-    const uint32_t *n_dev = nullptr;
-    int buf = radix_sort(src, np, bits_for((uint64_t)local_players), w, s, ctx->sm_count, &n_dev);
+    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
     if (buf < 0) return buf;
-    if (!sharded) n_dev = nullptr;
-    // slots that take no part (empty, gated match) read TS_NONE: the output is fully defined;
-    // sharded: slots of players owned elsewhere read 0x7F7F7F7F until the MIN over ranks
-    TS_CUDA(cudaMemsetAsync(pred, sharded ? 0x7F : 0xFF, (size_t)np * 4, s));
-    launch_pred(w, buf, np, n_dev, src, (uint32_t)seq_base, last, pred, s);
+    // slots that take no part (empty, gated match) read TS_NONE: the output is fully defined
+    TS_CUDA(cudaMemsetAsync(pred, 0xFF, (size_t)np * 4, s));
+    launch_pred(w, buf, np, nullptr, src, (uint32_t)seq_base, last, pred, s);
     if (last)
-        k_last_update<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, n_dev, src.slots_magic,
+        k_last_update<<<(np + 255) / 256, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, nullptr, src.slots_magic,
                                                        src.sentinel, (uint32_t)seq_base, last);
     TS_CUDA(cudaGetLastError());
     return 0;
 }
-}  // namespace
 
-extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
-                            int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last,
-                            uint32_t *pred, void *workspace, int64_t workspace_bytes, void *stream)
+// ---------------------------------------------------------------------------
+// Links of ONE ladder spread over the G GPUs of a node (tsrate.h: ts_shard_view).
+// Every rank links the players it owns (p % G == rank):
+//   1. k_owned_compact reads the whole id stream once -- its own slice and, over NVLink,
+//      its peers' -- and keeps, in stream order, (local player index, slot index of the
+//      window) of every live slot of an owned player (single pass, decoupled look-back);
+//   2. the pairs are radix-sorted by local player index (same single-sweep passes as the
+//      one-GPU sort, their number known only on the device);
+//   3. k_succ walks the sorted runs: a slot's successor match goes straight into the succ
+//      slice of the rank that rates the slot's match (peer store), and the head of every
+//      run sends the player's pair from the owner's table shard to the mailbox of the rank
+//      that rates the player's first match, tagged with that match's number.
+// ---------------------------------------------------------------------------
+namespace {
+
+struct ShardSrc {
+    const uint32_t *ids[TS_SHARD_MAX];
+    const uint32_t *meta[TS_SHARD_MAX];
+    uint32_t g_mask, g_shift;       // G - 1, log2 G
+    uint32_t owner;                 // this rank
+    uint32_t slots;
+    unsigned long long slots_magic;
+    uint32_t rated_mask;
+    uint32_t n_players;
+};
+
+// slot idx = m * slots + s of the window -> local index of its player on this rank, or TS_NONE
+__device__ __forceinline__ uint32_t shard_key(const ShardSrc &src, uint32_t idx)
 {
-    return link_pred_impl(ctx, ids, meta, n_matches, slots, n_players, mode_col, seq_base, last, pred, workspace,
-                          workspace_bytes, stream, 0, 1);
+    const uint32_t m = (uint32_t)__umul64hi((unsigned long long)idx, src.slots_magic);
+    const uint32_t sl = idx - m * src.slots;
+    const uint32_t blk = m >> 5, r = blk & src.g_mask;
+    const uint32_t lm = ((blk >> src.g_shift) << 5) | (m & 31u);
+    const uint32_t k = src.ids[r][(size_t)lm * src.slots + sl];
+    if (k == TS_EMPTY_SLOT || k >= src.n_players || (k & src.g_mask) != src.owner) return TS_NONE;
+    const uint32_t mt = src.meta[r][lm];
+    const bool gated = ((src.rated_mask >> ((mt >> TS_META_MODE_SHIFT) & 15u)) & 1u) == 0u ||
+                       (mt & (TS_META_AFK | TS_META_INVALID)) != 0u;
+    return gated ? TS_NONE : (k >> src.g_shift);
 }
 
-extern "C" int ts_link_pred_sharded(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches,
-                                    int32_t slots, int64_t n_players, const int8_t mode_col[16], int64_t seq_base,
-                                    uint32_t *last, uint32_t *pred, int32_t rank, int32_t n_shards, void *workspace,
-                                    int64_t workspace_bytes, void *stream)
+__global__ void __launch_bounds__(kSortBlock)
+k_owned_compact(ShardSrc src, uint32_t np, uint32_t cap, uint32_t *status, uint32_t *ticket, uint32_t *keys_out,
+                uint32_t *vals_out, uint32_t *n_out, unsigned long long *ctrl)
 {
-    if (n_shards < 1 || n_shards > 16 || (n_shards & (n_shards - 1)) || rank < 0 || rank >= n_shards) {
-        ts_set_error("ts_link_pred_sharded: n_shards must be a power of two <= 16 and 0 <= rank < n_shards");
+    __shared__ uint32_t s_tile, s_excl;
+    __shared__ uint32_t warp_tot[kWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t tile = s_tile;
+    const uint32_t wbase = tile * kSortTile + warp * (kSortItems * 32);
+    uint32_t key[kSortItems], off[kSortItems];
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const uint32_t idx = wbase + k * 32 + lane;
+        key[k] = idx < np ? shard_key(src, idx) : TS_NONE;
+    }
+    uint32_t running = 0;
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, key[k] != TS_NONE);
+        off[k] = running + __popc(bal & ((1u << lane) - 1u));
+        running += __popc(bal);
+    }
+    if (lane == 0) warp_tot[warp] = running;
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) { before += (w < warp) ? warp_tot[w] : 0u; total += warp_tot[w]; }
+    if (warp == 0) {
+        // publish this tile's count, then look back over the tiles before it, 32 at a time
+        if (lane == 0) st_relaxed_u32(status + tile, total | (tile == 0 ? kStPrefix : kStCount));
+        uint32_t excl = 0, j = tile;
+        while (j > 0) {
+            const bool in = (uint32_t)lane < j;
+            const uint32_t v = in ? ld_relaxed_u32(status + (j - 1 - lane)) : kStPrefix;
+            const uint32_t pending = __ballot_sync(0xFFFFFFFFu, (v & (kStPrefix | kStCount)) == 0u);
+            const uint32_t prefixed = __ballot_sync(0xFFFFFFFFu, (v & kStPrefix) != 0u);
+            const int first_pending = pending ? __ffs(pending) - 1 : 32;
+            const int first_prefix = prefixed ? __ffs(prefixed) - 1 : 32;
+            const int take = first_prefix < first_pending ? first_prefix + 1 : first_pending;   // lanes 0 .. take-1 count
+            uint32_t x = lane < take ? (v & kStMask) : 0u;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xFFFFFFFFu, x, o);
+            excl += x;
+            if (first_prefix < first_pending) break;
+            j -= (uint32_t)take;
+            if (take == 0) __nanosleep(40);
+        }
+        if (lane == 0) {
+            if (tile > 0) st_relaxed_u32(status + tile, (excl + total) | kStPrefix);
+            s_excl = excl;
+            if ((tile + 1) * (uint32_t)kSortTile >= np) {          // the last tile knows the grand total
+                const uint32_t all = excl + total;
+                *n_out = all < cap ? all : cap;
+                if (all > cap) atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
+            }
+        }
+    }
+    __syncthreads();
+    const uint32_t base = s_excl + before;
+#pragma unroll
+    for (int k = 0; k < kSortItems; ++k) {
+        if (key[k] == TS_NONE) continue;
+        const uint32_t pos = base + off[k];
+        if (pos < cap) { keys_out[pos] = key[k]; vals_out[pos] = wbase + k * 32 + lane; }
+    }
+}
+
+struct ShardDst {
+    uint32_t *succ[TS_SHARD_MAX];
+    unsigned long long *rows[TS_SHARD_MAX];
+    const double *table_own;
+    uint32_t g_mask, g_shift, owner;
+    uint32_t slots;
+    unsigned long long slots_magic;
+    uint32_t seq_base;
+};
+
+__device__ __forceinline__ void st_row_sys(unsigned long long *row, double mu, double sigma, uint32_t ver)
+{
+    const unsigned long long v = (unsigned long long)ver << 32;
+    const unsigned long long m = (unsigned long long)__double_as_longlong(mu);
+    const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
+    asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"((m & 0xFFFFFFFFull) | v), "l"((m >> 32) | v) : "memory");
+    asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"((s & 0xFFFFFFFFull) | v), "l"((s >> 32) | v) : "memory");
+}
+
+// one thread per sorted entry; destinations m in [m_lo, m_hi) only (the scatter is done in
+// passes over ranges that the destination GPUs' L2 can hold, like k_pred)
+__global__ void __launch_bounds__(256)
+k_succ(const uint32_t *keys, const uint32_t *vals, const uint32_t *n_dev, ShardDst dst, uint32_t m_lo, uint32_t m_hi,
+       unsigned long long *ctrl)
+{
+    const uint32_t n = __ldg(n_dev);
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t k = __ldcs(keys + i), v = __ldcs(vals + i);
+    const uint32_t m = (uint32_t)__umul64hi((unsigned long long)v, dst.slots_magic);
+    if (m < m_lo || m >= m_hi) return;
+    const uint32_t sl = v - m * dst.slots;
+    uint32_t nxt = TS_NONE;
+    if (i + 1 < n && __ldcs(keys + i + 1) == k) {
+        const uint32_t m2 = (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + i + 1), dst.slots_magic);
+        if (m2 == m) atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_DUPLICATE);
+        nxt = dst.seq_base + m2;
+    }
+    const uint32_t blk = m >> 5, r = blk & dst.g_mask;
+    const uint32_t lm = ((blk >> dst.g_shift) << 5) | (m & 31u);
+    dst.succ[r][(size_t)lm * dst.slots + sl] = nxt;
+    if (i == 0 || __ldcs(keys + i - 1) != k) {            // the player's first match of the window
+        const double2 pr = __ldg(reinterpret_cast<const double2 *>(dst.table_own) + k);
+        const uint32_t pid = (k << dst.g_shift) | dst.owner;
+        st_row_sys(dst.rows[r] + (size_t)pid * 4, pr.x, pr.y, dst.seq_base + m);
+    }
+}
+
+int check_view(const ts_shard_view *v, const char *who)
+{
+    if (!v || v->n_shards < 1 || v->n_shards > TS_SHARD_MAX || (v->n_shards & (v->n_shards - 1)) || v->rank < 0 ||
+        v->rank >= v->n_shards) {
+        ts_set_error("%s: n_shards must be a power of two <= %d and 0 <= rank < n_shards", who, TS_SHARD_MAX);
         return TS_E_ARG;
     }
-    return link_pred_impl(ctx, ids, meta, n_matches, slots, n_players, mode_col, seq_base, last, pred, workspace,
-                          workspace_bytes, stream, rank, n_shards);
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int64_t ts_shard_local_matches(int64_t n_matches, int32_t rank, int32_t n_shards)
+{
+    if (n_matches < 0 || n_shards < 1 || rank < 0 || rank >= n_shards) return TS_E_ARG;
+    const int64_t blocks = (n_matches + TS_SHARD_BLOCK - 1) / TS_SHARD_BLOCK;
+    if (blocks <= rank) return 0;
+    const int64_t mine = (blocks - rank + n_shards - 1) / n_shards;
+    const bool last_is_mine = (blocks - 1) % n_shards == rank;
+    return (mine - 1) * TS_SHARD_BLOCK + (last_is_mine ? n_matches - (blocks - 1) * TS_SHARD_BLOCK : TS_SHARD_BLOCK);
+}
+
+extern "C" int64_t ts_shard_link_workspace_bytes(int64_t owned_cap)
+{
+    if (owned_cap < 0 || owned_cap >= 0xFFFF0000ll) return TS_E_ARG;
+    return ts_link_workspace_bytes(owned_cap / 2 + 1, 2);
+}
+
+extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
+                             int8_t mode, int64_t seq_base, void *workspace, int64_t workspace_bytes, void *stream)
+{
+    if (int rc = check_view(view, "ts_shard_link")) return rc;
+    const int G = view->n_shards, rank = view->rank;
+    if (!ctx || n_matches < 0 || slots < 2 || slots > TS_MAX_SLOTS || (slots & 1) || n_players < 1 ||
+        n_players >= 0xFFFFFFFFll || (uint64_t)n_matches * (uint64_t)slots >= 0xFFFF0000ull || mode < 0 || mode > 5) {
+        ts_set_error("ts_shard_link: bad sizes (n_matches * slots must stay below 2^32 - 2^16, mode 0..5)");
+        return TS_E_ARG;
+    }
+    if (seq_base < 0 || seq_base % (TS_SHARD_BLOCK * G) != 0 || seq_base + n_matches >= 0xFFFFFFFFll) {
+        ts_set_error("ts_shard_link: seq_base must be a multiple of 32 * n_shards and match numbers stay below 2^32 - 1");
+        return TS_E_ARG;
+    }
+    if (n_matches == 0) return 0;
+    for (int g = 0; g < G; ++g)
+        if (!view->ids[g] || !view->meta[g] || !view->succ[g] || !view->rows[g] || !view->table[g]) {
+            ts_set_error("ts_shard_link: shard %d not mapped", g);
+            return TS_E_ARG;
+        }
+    // capacity (pairs) of the workspace: two (key, val) buffers, one status word per 4096 pairs
+    // (the sort's passes need 256), the digit totals
+    const uint32_t np = (uint32_t)n_matches * (uint32_t)slots;
+    int64_t cap = np;
+    while (cap > 0 && ts_shard_link_workspace_bytes(cap) > workspace_bytes) cap -= (cap + 15) / 16;
+    const int64_t compact_tiles = ((int64_t)np + kSortTile - 1) / kSortTile;
+    if (cap < 1 || !workspace || ((cap + kSortTile - 1) / kSortTile) * 256 + 256 < compact_tiles) {
+        ts_set_error("ts_shard_link: workspace too small");
+        return TS_E_WORKSPACE;
+    }
+    TS_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    Workspace w = carve_link((char *)workspace, (uint32_t)cap);
+    uint32_t *ticket = w.totals + kMaxPasses * 256, *n_dev = ticket + 8;
+    int shift = 0;
+    while ((1 << shift) < G) ++shift;
+    ShardSrc src;
+    for (int g = 0; g < TS_SHARD_MAX; ++g) { src.ids[g] = g < G ? view->ids[g] : nullptr; src.meta[g] = g < G ? view->meta[g] : nullptr; }
+    src.g_mask = (uint32_t)G - 1u;
+    src.g_shift = (uint32_t)shift;
+    src.owner = (uint32_t)rank;
+    src.slots = (uint32_t)slots;
+    src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
+    src.rated_mask = 1u << mode;
+    src.n_players = (uint32_t)n_players;
+    TS_CUDA(cudaMemsetAsync(w.totals, 0, kTotalsWords * 4, s));
+    TS_CUDA(cudaMemsetAsync(w.hist, 0, (size_t)compact_tiles * 4, s));
+    k_owned_compact<<<(unsigned)compact_tiles, kSortBlock, 0, s>>>(src, np, (uint32_t)cap, w.hist, ticket, w.keys[0], w.vals[0],
+                                                                 n_dev, ctx->d_ctrl);
+    const int64_t local_players = (n_players - rank + G - 1) / G;
+    KeySrc ks;
+    ks.keys = w.keys[0];
+    ks.meta = nullptr;
+    for (int i = 0; i < 16; ++i) ks.modes.col[i] = (int8_t)-1;
+    ks.slots = 1;
+    ks.sentinel = 0xFFFFFFFFu;
+    ks.from_ids = 0;
+    ks.slots_magic = 0ull;
+    ks.rated_mask = 0;
+    int buf = radix_sort(ks, (uint32_t)cap, bits_for((uint64_t)(local_players > 0 ? local_players - 1 : 0)), w, s,
+                         ctx->sm_count, n_dev);
+    if (buf < 0) return buf;
+    ShardDst dst;
+    for (int g = 0; g < TS_SHARD_MAX; ++g) { dst.succ[g] = g < G ? view->succ[g] : nullptr; dst.rows[g] = g < G ? view->rows[g] : nullptr; }
+    dst.table_own = view->table[rank];
+    dst.g_mask = src.g_mask;
+    dst.g_shift = src.g_shift;
+    dst.owner = src.owner;
+    dst.slots = src.slots;
+    dst.slots_magic = src.slots_magic;
+    dst.seq_base = (uint32_t)seq_base;
+    // destination ranges: 16 Mi succ entries per GPU and pass (64 MiB, half an L2)
+    const uint64_t range_m = (uint64_t)pred_range_entries() * (uint64_t)G / (uint64_t)slots;
+    uint64_t step = ((uint64_t)n_matches + range_m - 1) / range_m > 8 ? (uint64_t)n_matches : range_m;
+    for (uint64_t lo = 0; lo < (uint64_t)n_matches; lo += step) {
+        const uint32_t hi = (uint32_t)std::min<uint64_t>(lo + step, (uint64_t)n_matches);
+        k_succ<<<(unsigned)((cap + 255) / 256), 256, 0, s>>>(w.keys[buf], w.vals[buf], n_dev, dst, (uint32_t)lo, hi, ctx->d_ctrl);
+    }
+    TS_CUDA(cudaGetLastError());
+    return 0;
 }

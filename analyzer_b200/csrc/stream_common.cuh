@@ -97,6 +97,117 @@ __device__ __forceinline__ uint32_t group_sum_u32(uint32_t x)
 }
 
 
+// per-warp staging buffers: a warp owns W = 32 / L consecutive matches at a time; `link` holds
+// pred (single GPU: the version to wait for) or succ (sharded ladder: where the new row goes)
+template <int P, int W>
+struct WarpStage {
+    uint32_t ids[2][W * P];
+    uint32_t link[2][W * P];
+    uint32_t meta[2][W];
+};
+
+template <int P, int W>
+__device__ __forceinline__ void stage_warp_tile(WarpStage<P, W> &st, int b, const uint32_t *ids, const uint32_t *link,
+                                                const uint32_t *meta, uint32_t base, uint32_t cnt, int wl)
+{
+    const uint32_t *src_i = ids + (size_t)base * P, *src_p = link + (size_t)base * P;
+    for (uint32_t i = wl; i < cnt * (P / 2); i += 32) {
+        cp_async_8(&st.ids[b][2 * i], src_i + 2 * i);
+        cp_async_8(&st.link[b][2 * i], src_p + 2 * i);
+    }
+    for (uint32_t i = wl; i < cnt; i += 32) cp_async_4(&st.meta[b][i], meta + base + i);
+}
+
+// What a pass needs of the environment (rater.py:30-37), in registers.
+struct PassEnv {
+    double tau2, beta2, tb2, margin_full;
+    const double *margins;       // draw margin by number of players (ragged teams)
+    const double *seed;          // get_trueskill_seed per player, or nullptr
+    bool draw_is_zero;
+};
+
+// One rating pass of the ladder layout (one (mu, sigma) pair per player; rater.py:132-169 with
+// a single rate()), shared by the single-GPU stream kernel and the sharded one so that both give
+// the same bits: every product-sum is written with an explicit rounding (no contraction is left
+// to the compiler, which decides it per template instantiation).  Executed by the whole converged
+// warp; lanes of groups that are not complete compute on placeholders.  L lanes share a match;
+// lane `lane` of the group owns slots lane, lane + L, ...  q_* are the rows as read; mu2 / sg2
+// the rows to publish (unchanged where the reference would raise).  Returns TS_ST_*.
+template <int P, int L, int SPL>
+__device__ __forceinline__ int rate_pass(const PassEnv &env, int lane, int first, bool draw_eff,
+                                         const uint32_t (&pid)[SPL], const bool (&used)[SPL], bool bad_id,
+                                         const double (&q_mu)[SPL], const double (&q_sg)[SPL],
+                                         double (&mu2)[SPL], double (&sg2)[SPL], double &quality_d, double &quality_ss,
+                                         int &n_out)
+{
+    constexpr int HALF = P / 2;
+    double sgn[SPL], e_mu[SPL], e_sg[SPL];     // effective pairs; q_mu / q_sg stay the rows as read
+    double d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
+    uint32_t cnts = bad_id ? 65536u : 0u;
+    bool any_null = false;
+#pragma unroll
+    for (int k = 0; k < SPL; ++k) {
+        e_mu[k] = q_mu[k]; e_sg[k] = q_sg[k];
+        any_null |= used[k] && isnan(q_mu[k]);
+    }
+    if (__any_sync(0xFFFFFFFFu, any_null)) {       // first touch: seed (rater.py:118-119)
+#pragma unroll
+        for (int k = 0; k < SPL; ++k) {
+            if (!(used[k] && isnan(q_mu[k]))) continue;
+            double2 sd = make_double2(q_mu[k], q_sg[k]);
+            if (env.seed) sd = __ldg(reinterpret_cast<const double2 *>(env.seed) + pid[k]);
+            if (isnan(sd.x)) cnts |= 65536u;       // neither rating nor seed
+            else { e_mu[k] = sd.x; e_sg[k] = sd.y; }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < SPL; ++k) {
+        const int s = lane + k * L;
+        sgn[k] = ((s >= HALF ? 1 : 0) == first) ? 1.0 : -1.0;
+        const bool u = used[k];
+        d_q = __fma_rn(sgn[k], u ? e_mu[k] : 0.0, d_q);
+        c2_q = __dadd_rn(c2_q, u ? __fma_rn(e_sg[k], e_sg[k], env.tb2) : 0.0);
+        ss_q = u ? __fma_rn(e_sg[k], e_sg[k], ss_q) : ss_q;
+        cnts += (u ? (sgn[k] > 0.0 ? 1u : 256u) : 0u) + ((u && e_sg[k] == 0.0) ? 65536u : 0u);
+    }
+    d_q = group_sum<L>(d_q);
+    c2_q = group_sum<L>(c2_q);
+    ss_q = group_sum<L>(ss_q);
+    cnts = group_sum_u32<L>(cnts);
+    const int n0 = cnts & 255u, n1 = (cnts >> 8) & 255u, n = n0 + n1;
+    int status = TS_ST_OK;
+    if ((cnts >> 16) != 0u || n0 == 0 || n1 == 0) status = TS_ST_VALUE_ERROR;
+    const double margin = n == P ? env.margin_full : env.margins[n];   // ragged teams are rare: no indexed load on the hot path
+    double v_q = 0.0, w_q = 0.0;
+    const double rc_q = rsqrt(c2_q);
+    if (status == TS_ST_OK &&
+        !tsvw::trunc_vw(__dmul_rn(d_q, rc_q), __dmul_rn(margin, rc_q), draw_eff, env.draw_is_zero, v_q, w_q))
+        status = TS_ST_FP_ERROR;
+    const bool ok = status == TS_ST_OK;
+#pragma unroll
+    for (int k = 0; k < SPL; ++k) {
+        // a failed match writes nothing in the reference; here it republishes the rows it
+        // read so that successors can go on
+        const double si = __fma_rn(e_sg[k], e_sg[k], env.tau2);
+        const double g = __dmul_rn(si, rc_q);
+        mu2[k] = ok ? __fma_rn(__dmul_rn(sgn[k], g), v_q, e_mu[k]) : q_mu[k];
+        sg2[k] = ok ? __dsqrt_rn(__dmul_rn(si, __fma_rn(-__dmul_rn(g, rc_q), w_q, 1.0))) : q_sg[k];
+    }
+    quality_d = d_q;
+    quality_ss = ss_q;
+    n_out = n;
+    return status;
+}
+
+// match.trueskill_quality (rater.py:141) of a rated match, from the pass's team sums
+__device__ __forceinline__ double match_quality(double d_q, double ss_q, int n, double beta2)
+{
+    const double nb2 = __dmul_rn((double)n, beta2);
+    const double den = __dadd_rn(nb2, ss_q);
+    return __dmul_rn(exp(__ddiv_rn(__dmul_rn(__dmul_rn(-0.5, d_q), d_q), den)), __dsqrt_rn(__ddiv_rn(nb2, den)));
+}
+
+
 inline int stream_sleep_ns()
 {
     static int ns = -1;

@@ -54,6 +54,7 @@ struct PairArgs {
     uint32_t row_words;           // words per player row: 8, MULTI: 8 + 4 * (rated queue columns)
     uint32_t queue_nibbles;       // MULTI: 4 bits per game mode, the compact index of its queue column
     uint32_t n_matches;
+    uint32_t n_players;           // ids at or beyond it are refused, never dereferenced
     uint32_t seq_base;
     uint32_t sleep_ns;
     uint32_t max_spins;
@@ -71,26 +72,6 @@ __device__ __forceinline__ void st_ord(unsigned long long *p, uint32_t lo, uint3
 {
     const unsigned long long v = (unsigned long long)ver << 32;
     asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(v | lo), "l"(v | hi) : "memory");
-}
-
-template <int P, int W>
-struct WarpStage {
-    uint32_t ids[2][W * P];
-    uint32_t pred[2][W * P];
-    uint32_t meta[2][W];
-};
-
-template <int P, int W>
-__device__ __forceinline__ void stage_warp_tile(WarpStage<P, W> &st, int b, const PairArgs &a, uint32_t tile, int wl)
-{
-    const uint32_t base = tile * W;
-    const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
-    const uint32_t *src_i = a.ids + (size_t)base * P, *src_p = a.pred + (size_t)base * P;
-    for (uint32_t i = wl; i < cnt * (P / 2); i += 32) {
-        cp_async_8(&st.ids[b][2 * i], src_i + 2 * i);
-        cp_async_8(&st.pred[b][2 * i], src_p + 2 * i);
-    }
-    for (uint32_t i = wl; i < cnt; i += 32) cp_async_4(&st.meta[b][i], a.meta + base + i);
 }
 
 template <int P, int L, bool MULTI>
@@ -118,13 +99,16 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
     const uint32_t first_tile = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
 
     int pf = 0;
-    if (first_tile < n_tiles) stage_warp_tile<P, W>(stage, pf, a, first_tile, wl);
+    if (first_tile < n_tiles)
+        stage_warp_tile<P, W>(stage, pf, a.ids, a.pred, a.meta, first_tile * W, min((uint32_t)W, a.n_matches - first_tile * W), wl);
     for (uint32_t tile = first_tile; tile < n_tiles; tile += stride) {
         cp_async_wait_all();
         __syncwarp();
         const int cur = pf;
         pf ^= 1;
-        if (tile + stride < n_tiles) stage_warp_tile<P, W>(stage, pf, a, tile + stride, wl);
+        if (tile + stride < n_tiles)
+            stage_warp_tile<P, W>(stage, pf, a.ids, a.pred, a.meta, (tile + stride) * W,
+                                  min((uint32_t)W, a.n_matches - (tile + stride) * W), wl);
         const uint32_t base = tile * W;
         const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
         const uint32_t m = base + grp;
@@ -150,12 +134,14 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
         uint32_t ord_lo[SPL], ord_hi[SPL];          // MULTI: the player's queue ordinals as read
         bool used[SPL], have[SPL];
         double s_mu[SPL], s_sg[SPL], q_mu[SPL], q_sg[SPL];   // the row as read (NaN = NULL)
+        bool bad_id = false;
 #pragma unroll
         for (int k = 0; k < SPL; ++k) {
             const int s = lane + k * L;
             pid[k] = (live && s < P) ? stage.ids[cur][grp * P + s] : TS_EMPTY_SLOT;
             used[k] = pid[k] != TS_EMPTY_SLOT;
-            want[k] = used[k] ? stage.pred[cur][grp * P + s] : TS_NONE;
+            if (used[k] && pid[k] >= a.n_players) { used[k] = false; bad_id = true; }   // corrupt id: no table access
+            want[k] = used[k] ? stage.link[cur][grp * P + s] : TS_NONE;
             ord_lo[k] = ord_hi[k] = 0u;
             have[k] = !used[k];
             s_mu[k] = 0.0; s_sg[k] = 1.0; q_mu[k] = 0.0; q_sg[k] = 1.0;
@@ -244,7 +230,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
             double sgn[SPL], es_mu[SPL], es_sg[SPL], eq_mu[SPL], eq_sg[SPL];   // effective pairs
             bool had[SPL];
             double d_s = 0.0, c2_s = 0.0, d_q = 0.0, c2_q = 0.0, ss_q = 0.0;
-            uint32_t cnts = 0;
+            uint32_t cnts = bad_id ? 65536u : 0u;
             bool any_null = false;
 #pragma unroll
             for (int k = 0; k < SPL; ++k) {
@@ -333,7 +319,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
             if (go) {
                 if (lane == 0) {
                     if (a.out.status) a.out.status[m] = (uint8_t)status;
-                    if (!ok) atomicAdd(&a.ctrl[CTRL_ERRORS], 1ull);
+                    if (!ok) atomicAdd(&a.ctrl[status == TS_ST_VALUE_ERROR ? CTRL_VALUE_ERRORS : CTRL_ERRORS], 1ull);
                     else if (a.out.quality) {      // rater.py:141: queue pairs before the update, no tau
                         const double nb2 = (double)n * beta2;
                         const double den = nb2 + ss_q;
@@ -446,6 +432,7 @@ void fill_args(PairArgs &a, ts_ctx *ctx, const ts_table *table, const uint32_t *
     a.row_words = 8;
     a.queue_nibbles = 0;
     a.n_matches = (uint32_t)n_matches;
+    a.n_players = (uint32_t)(table->n_players > 0xFFFFFFFFll ? 0xFFFFFFFFll : table->n_players);
     a.seq_base = (uint32_t)seq_base;
     a.sleep_ns = stream_sleep_ns();
     a.max_spins = stream_max_spins();
@@ -495,7 +482,6 @@ int ts_rate_stream_pair_impl(ts_ctx *ctx, const ts_table *table, int qcol, const
     if (flags & TS_STREAM_LOAD)
         k_vt_load_pair<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, table->row_pairs, table->shared_col, qcol,
                                                                   a.vt, u);
-    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
     int lanes = lanes_per_match ? lanes_per_match : (slots == 6 ? 2 : 8);
     int rc = 0;
     if (n_matches > 0) rc = slots == 6 ? dispatch_pair<6, false>(ctx, a, lanes, s) : dispatch_pair<10, false>(ctx, a, lanes, s);
@@ -529,7 +515,6 @@ int ts_rate_stream_queues_impl(ts_ctx *ctx, const ts_table *table, const uint32_
     if ((flags & TS_STREAM_LOAD) && u > 0)
         k_vt_load_queues<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, table->row_pairs, table->shared_col,
                                                                     qm.col_of_queue, qm.n_queues, a.row_words, a.vt, u);
-    TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
     int lanes = lanes_per_match ? lanes_per_match : (slots == 6 ? 2 : 8);
     int rc = 0;
     if (n_matches > 0) rc = slots == 6 ? dispatch_pair<6, true>(ctx, a, lanes, s) : dispatch_pair<10, true>(ctx, a, lanes, s);

@@ -20,7 +20,7 @@ constexpr double kInvSqrt2 = 0.70710678118654752440;
 constexpr double kSqrt2OverPi = 0.79788456080286535588;   // sqrt(2/pi)
 constexpr double kInvSqrt2Pi = 0.39894228040143267794;
 
-__device__ __forceinline__ double npdf(double x) { return kInvSqrt2Pi * exp(-0.5 * x * x); }
+__device__ __forceinline__ double npdf(double x) { return __dmul_rn(kInvSqrt2Pi, exp(__dmul_rn(__dmul_rn(-0.5, x), x))); }
 __device__ __forceinline__ double ncdf(double x) { return 0.5 * erfc(-x * kInvSqrt2); }
 
 __device__ __forceinline__ double v_win_table(double x)
@@ -50,7 +50,7 @@ __device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, boo
             // no cancellation in either tail
             v = kSqrt2OverPi / erfcx(-x * kInvSqrt2);
         }
-        w = v * (v + x);
+        w = __dmul_rn(v, __dadd_rn(v, x));
         if (w > 0.0 && w < 1.0) return true;
         // far favourite-wins tail: erfcx overflows where the 50-digit reference
         // still sees 0 < w << 1e-300; the update is then the tau-only one.
@@ -67,8 +67,8 @@ __device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, boo
     const double mass = ncdf(a) - ncdf(b);
     if (mass == 0.0) return false;
     const double pa = npdf(a), pb = npdf(b);
-    const double vv = (pb - pa) / mass;
-    w = vv * vv + (a * pa - b * pb) / mass;
+    const double vv = __ddiv_rn(__dadd_rn(pb, -pa), mass);
+    w = __fma_rn(vv, vv, __ddiv_rn(__fma_rn(a, pa, -__dmul_rn(b, pb)), mass));   // explicit rounding: same bits in every kernel
     v = t < 0.0 ? -vv : vv;
     return true;
 }

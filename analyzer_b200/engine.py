@@ -294,10 +294,18 @@ class Rater(object):
             L.check(self._lib.ts_widen_meta(_ptr(meta8), n, _ptr(out), _stream_ptr()))
         return out
 
-    def error_count(self):
+    def error_counts(self):
+        """(matches that ended in TS_ST_FP_ERROR, in TS_ST_VALUE_ERROR) since the last
+        reset_errors -- the two exceptions the trueskill package raises, kept apart on the
+        device so that the batch can raise the right one without the status column."""
         if L.check(self._lib.ts_stream_stalled(self._ctx, _stream_ptr())):
             raise L.TsError("ts_rate_stream gave up: the links (pred) do not belong to the stream they were given with")
-        return L.check(self._lib.ts_error_count(self._ctx, _stream_ptr()))
+        fp, val = C.c_int64(0), C.c_int64(0)
+        L.check(self._lib.ts_error_counts(self._ctx, C.byref(fp), C.byref(val), _stream_ptr()))
+        return int(fp.value), int(val.value)
+
+    def error_count(self):
+        return sum(self.error_counts())
 
     def reset_errors(self):
         L.check(self._lib.ts_reset_errors(self._ctx, _stream_ptr()))
@@ -422,7 +430,8 @@ class Rater(object):
                 sch = self.schedule(ids_d, meta_d, ptab.n_players, ptab.mode_cols)
                 self.rate(ptab, sch, outs, lanes_per_match)
                 n_rounds = sch.n_rounds
-        bad = self.error_count()
+        n_fp, n_val = self.error_counts()
+        bad = n_fp + n_val
         result = dict(n_rounds=n_rounds, errors=bad)
         if outs is not None:
             flat_h = outs["_flat"].cpu().numpy()
@@ -432,12 +441,11 @@ class Rater(object):
                 result[k] = flat_h[o:o + size].reshape(tuple(outs[k].shape))
                 o = (o + size + 1) & ~1
             result["status"] = outs["status"].cpu().numpy()
-        if bad:
-            st = result.get("status")
-            if st is not None and np.any(st == L.ST_VALUE_ERROR):
-                raise ValueError("sigma**2 should be greater than 0 / player without rating or seed "
-                                 "(%d matches)" % int(np.sum(st == L.ST_VALUE_ERROR)))
-            raise FloatingPointError("%d matches outside the truncated-Gaussian domain" % bad)
+        if n_val:      # the reference raises on the first failing match of the batch; either kind fails it
+            raise ValueError("sigma**2 should be greater than 0 / player without rating or seed / player id outside "
+                             "the table (%d matches)" % n_val)
+        if n_fp:
+            raise FloatingPointError("%d matches outside the truncated-Gaussian domain" % n_fp)
         if table_out is not None:             # caller-provided (pinned) host tensor
             table_out.copy_(tab_d, non_blocking=True)
             torch.cuda.current_stream().synchronize()

@@ -1,12 +1,21 @@
-"""One ladder over the GPUs of a node: hash-sharded player table in NVLink peer
-memory (BASELINE.json configs[4]), one process per GPU.
+"""One ladder over the GPUs of a node (BASELINE.json configs[4]),
+one process per GPU, rows pushed to where they are read (include/tsrate.h,
+ts_shard_view).
 
-Player p lives on rank p % world at local row p // world.  Every rank rates
-the warp tiles t with t % world == rank of the same match stream; a match
-waits for the versions of its players' rows wherever they live, so there is
-no inter-GPU barrier and no collective while rating -- torch.distributed is
-used only to exchange the 64-byte IPC handles once and to separate the three
-phases (load / rate / read back).
+Layout: blocks of 32 consecutive matches go round-robin to the ranks, so rank g
+holds ids / meta / succ of its own 1/G of the stream only.  Player p is owned by
+rank p % world (local row p // world): the owner's table shard holds the pair
+before the first and after the last match.  Every rank has a mailbox of versioned
+rows; a rated match stores each new row into the mailbox of the rank that rates
+that player's next match, so a match polls only its own GPU's memory.  The links
+(succ) are computed by the players' owners and stored straight into the slice of
+the rank that needs them.  torch.distributed exchanges the 64-byte IPC handles
+once and separates the phases (reset | link | rate |); there is no collective on
+the data path.
+
+emulate=True: one process plays all `world` ranks on one GPU (every pointer
+local, one launch of the rating kernel for all ranks) -- the same kernels and
+index arithmetic, for single-GPU boxes and tests.
 """
 from __future__ import annotations
 
@@ -18,6 +27,7 @@ import torch.distributed as dist
 from . import _lib as L
 
 ROW_BYTES = 32
+BLOCK = L.SHARD_BLOCK
 
 
 def owner(pid, world):
@@ -48,10 +58,41 @@ def merge_tables(shards):
     return out
 
 
-def tiles_of(rank, world, n_matches, tile):
-    """Match tiles (start, stop) a rank rates: t % world == rank."""
-    n_tiles = (n_matches + tile - 1) // tile
-    return [(t * tile, min(n_matches, (t + 1) * tile)) for t in range(rank, n_tiles, world)]
+def match_rank(m, world):
+    """Rank that rates match m of a window."""
+    return (m // BLOCK) % world
+
+
+def local_index(m, world):
+    """Index of match m in the slice of match_rank(m, world)."""
+    return (m // BLOCK // world) * BLOCK + m % BLOCK
+
+
+def global_index(lm, rank, world):
+    """Inverse of (match_rank, local_index)."""
+    return ((lm // BLOCK) * world + rank) * BLOCK + lm % BLOCK
+
+
+def local_matches(n_matches, rank, world):
+    """Matches of an n_matches window that live on `rank` (= ts_shard_local_matches)."""
+    blocks = (n_matches + BLOCK - 1) // BLOCK
+    if blocks <= rank:
+        return 0
+    mine = (blocks - rank + world - 1) // world
+    last_is_mine = (blocks - 1) % world == rank
+    return (mine - 1) * BLOCK + (n_matches - (blocks - 1) * BLOCK if last_is_mine else BLOCK)
+
+
+def take_slice(full, rank, world):
+    """Rows of a full [N, ...] stream tensor that live on `rank`, in local order."""
+    n = full.shape[0]
+    step = BLOCK * world * 32768                     # bounded index temporaries
+    parts = []
+    for lo in range(0, n, step):
+        hi = min(n, lo + step)
+        m = torch.arange(lo, hi, device=full.device)
+        parts.append(full[lo:hi][((m >> 5) % world) == rank])
+    return torch.cat(parts) if parts else full[:0]
 
 
 def exchange_handles(handle, group=None):
@@ -62,78 +103,180 @@ def exchange_handles(handle, group=None):
     return out
 
 
+def _align(x):
+    return (x + 255) & ~255
+
+
+def arena_layout(n_players, n_matches_cap, slots, rank, world):
+    """Byte offsets of (rows, table, ids, meta, succ) in rank's arena, and its size.
+    Every rank computes every rank's layout: peers' pointers are base + offset."""
+    nl = local_matches(n_matches_cap, rank, world)
+    sizes = (n_players * ROW_BYTES, max(1, shard_rows(n_players, rank, world)) * 16, max(1, nl) * slots * 4,
+             max(1, nl) * 4, max(1, nl) * slots * 4)
+    offs, o = [], 0
+    for sz in sizes:
+        offs.append(o)
+        o += _align(sz)
+    return offs, o
+
+
+class _Raw(object):
+    """Device memory that torch did not allocate, for torch.as_tensor."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
 class ShardedLadder(object):
-    def __init__(self, rater, n_players, rank, world, group=None):
-        if world & (world - 1) or not 1 <= world <= 16:
-            raise ValueError("world size must be a power of two <= 16")
-        self.rater, self.n_players, self.rank, self.world, self.group = rater, n_players, rank, world, group
+    def __init__(self, rater, n_players, n_matches_cap, slots, rank=0, world=1, group=None, emulate=False):
+        if world & (world - 1) or not 1 <= world <= L.SHARD_MAX:
+            raise ValueError("world size must be a power of two <= %d" % L.SHARD_MAX)
+        if n_matches_cap * slots >= 0xFFFF0000:
+            raise ValueError("a window holds fewer than 2^32 - 2^16 slot entries")
+        self.rater, self.n_players, self.cap, self.slots = rater, n_players, n_matches_cap, slots
+        self.rank, self.world, self.group, self.emulate = rank, world, group, emulate
         self.lib = L.lib()
         self.device = rater.device.index or 0
-        self.rows = shard_rows(n_players, rank, world)
-        own = C.c_void_p()
-        handle = (C.c_char * 64)()
-        L.check(self.lib.ts_shard_alloc(self.device, max(self.rows, 1) * ROW_BYTES, C.byref(own), handle))
-        self.own = own
-        self.ptrs = (C.c_void_p * world)()
-        self.ptrs[rank] = own.value
-        self.opened = []
-        handles = exchange_handles(handle.raw, group)
-        for r, h in enumerate(handles):
-            if r == rank:
-                continue
-            p = C.c_void_p()
-            buf = C.create_string_buffer(h, 64)
-            L.check(self.lib.ts_shard_open(self.device, buf, C.byref(p)))
-            self.ptrs[r] = p.value
-            self.opened.append(p)
+        dev = torch.device("cuda", self.device)
+        self.layouts = [arena_layout(n_players, n_matches_cap, slots, g, world) for g in range(world)]
+        self.bases = [0] * world
+        self.opened, self.own = [], None
+        self._keep = []
+        if emulate:
+            for g in range(world):
+                t = torch.empty(self.layouts[g][1], dtype=torch.uint8, device=dev)
+                self._keep.append(t)
+                self.bases[g] = t.data_ptr()
+            self.played = list(range(world))
+        else:
+            own = C.c_void_p()
+            handle = (C.c_char * 64)()
+            L.check(self.lib.ts_shard_alloc(self.device, self.layouts[rank][1], C.byref(own), handle))
+            self.own = own
+            self.bases[rank] = own.value
+            if world > 1:
+                for r, h in enumerate(exchange_handles(handle.raw, group)):
+                    if r == rank:
+                        continue
+                    p = C.c_void_p()
+                    L.check(self.lib.ts_shard_open(self.device, C.create_string_buffer(h, 64), C.byref(p)))
+                    self.bases[r] = p.value
+                    self.opened.append(p)
+            self._keep.append(torch.as_tensor(_Raw(own.value, self.layouts[rank][1]), device=dev))
+            self.played = [rank]
+        # torch views of the arenas this process fills and reads
+        self.ids, self.meta, self.table, self.succ = {}, {}, {}, {}
+        for i, g in enumerate(self.played):
+            arena = self._keep[i]
+            offs, _ = self.layouts[g]
+            nl = local_matches(n_matches_cap, g, world)
+            rows = shard_rows(n_players, g, world)
+            self.table[g] = arena[offs[1]:offs[1] + rows * 16].view(torch.float64).view(rows, 2)
+            self.ids[g] = arena[offs[2]:offs[2] + nl * slots * 4].view(torch.int32).view(nl, slots)
+            self.meta[g] = arena[offs[3]:offs[3] + nl * 4].view(torch.int32)
+            self.succ[g] = arena[offs[4]:offs[4] + nl * slots * 4].view(torch.int32).view(nl, slots)
+        self._ws = None
 
-    def _phase(self, phase, table_shard, ids=None, meta=None, pred=None, mode=1, lanes=0):
-        n, p = (ids.shape if ids is not None else (0, 6))
-        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+    def view(self, rank=None):
+        v = L.TsShardView()
+        v.rank = self.rank if rank is None else rank
+        v.n_shards = self.world
+        for g in range(self.world):
+            offs, _ = self.layouts[g]
+            v.rows[g], v.table[g] = self.bases[g] + offs[0], self.bases[g] + offs[1]
+            v.ids[g], v.meta[g], v.succ[g] = self.bases[g] + offs[2], self.bases[g] + offs[3], self.bases[g] + offs[4]
+        return v
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def barrier(self):
+        torch.cuda.synchronize(self.device)
+        if not self.emulate and self.world > 1:
+            dist.barrier(group=self.group)
+
+    def set_stream(self, ids_full, meta_full):
+        """Take this rank's blocks (all ranks' when emulating) out of a full stream on this GPU."""
+        for g in self.played:
+            nl = local_matches(ids_full.shape[0], g, self.world)
+            self.ids[g][:nl].copy_(take_slice(ids_full, g, self.world))
+            self.meta[g][:nl].copy_(take_slice(meta_full, g, self.world))
+
+    def set_table(self, full):
+        """Own shard(s) of a full [U, 2] table on this GPU."""
+        for g in self.played:
+            self.table[g].copy_(full.reshape(-1, 2)[g::self.world])
+
+    def reset(self):
+        with torch.cuda.device(self.device):
+            for g in self.played:
+                v = self.view(g)
+                L.check(self.lib.ts_shard_reset(self.rater._ctx, C.byref(v), self.n_players, self._stream()))
+
+    def link(self, n_matches, mode=1, seq_base=0, owned_cap=None):
+        """succ slices and first rows of the window, for the players this rank owns."""
+        np_ = n_matches * self.slots
+        if owned_cap is None:       # a rank owns ~1/world of the slots; skewed ladders may need more
+            owned_cap = np_ if self.world == 1 else min(np_, int(np_ / self.world * 1.25) + (1 << 16))
+        nbytes = L.check(self.lib.ts_shard_link_workspace_bytes(owned_cap))
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = None
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", self.device))
+        with torch.cuda.device(self.device):
+            for g in self.played:
+                v = self.view(g)
+                L.check(self.lib.ts_shard_link(self.rater._ctx, C.byref(v), n_matches, self.slots, self.n_players, mode,
+                                               seq_base, C.c_void_p(self._ws.data_ptr()), self._ws.numel(), self._stream()))
+
+    def rate(self, n_matches, mode=1, seq_base=0, outputs=None, lanes=0):
         out = L.TsOutputs()
+        if outputs:
+            for k in ("quality", "out_queue", "status"):
+                t = outputs.get(k)
+                setattr(out, k, t.data_ptr() if t is not None else None)
+        v = self.view()
         with torch.cuda.device(self.device):
-            L.check(self.lib.ts_rate_stream_sharded(
-                self.rater._ctx, phase, ptr(table_shard), self.n_players, self.rank, self.world, self.ptrs, mode,
-                ptr(ids), ptr(meta), ptr(pred), n, p, C.byref(out), lanes,
-                C.c_void_p(torch.cuda.current_stream().cuda_stream)))
+            L.check(self.lib.ts_shard_rate(self.rater._ctx, C.byref(v), n_matches, self.slots, self.n_players, mode,
+                                           seq_base, C.byref(out), lanes, 1 if self.emulate else 0, self._stream()))
 
-    def link(self, ids, meta, mode_cols=(-1, 0), data_group=None):
-        """Distributed linking: every rank links the players it owns, then one
-        element-wise MIN all-reduce assembles pred [N, P] on every rank."""
-        n, p = ids.shape
-        pred = torch.empty_like(ids)
-        nbytes = L.check(self.lib.ts_link_workspace_bytes(n, p))
-        ws = self.rater._workspace(nbytes)
-        cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
-        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+    def status(self):
         with torch.cuda.device(self.device):
-            L.check(self.lib.ts_link_pred_sharded(
-                self.rater._ctx, ptr(ids), ptr(meta), n, p, self.n_players, (C.c_int8 * 16)(*cols), 0, None,
-                ptr(pred), self.rank, self.world, ptr(ws), ws.numel(),
-                C.c_void_p(torch.cuda.current_stream().cuda_stream)))
-        if self.world > 1:
-            dist.all_reduce(pred, op=dist.ReduceOp.MIN, group=data_group if data_group is not None else self.group)
-        return pred
+            return L.check(self.lib.ts_shard_status(self.rater._ctx, self._stream()))
 
-    def _barrier(self):
-        torch.cuda.synchronize(self.device)
-        dist.barrier(group=self.group)
+    def check(self):
+        st = self.status()
+        if not self.emulate and self.world > 1:      # every rank sees every rank's flags: all raise together
+            t = torch.tensor([st], dtype=torch.int32, device=torch.device("cuda", self.device))
+            parts = [torch.zeros_like(t) for _ in range(self.world)]
+            dist.all_gather(parts, t, group=self.group)
+            for x in parts:
+                st |= int(x)
+        if st & L.SHARD_OVERFLOW:
+            raise L.TsError("ts_shard_link: workspace too small for the slots this rank owns (pass a larger owned_cap)")
+        if st & L.SHARD_DUPLICATE:
+            raise L.TsError("sharded ladder: a player is listed twice in one match")
+        if st & L.SHARD_STALLED:
+            raise L.TsError("sharded ladder: a match's rows never arrived (links and stream do not belong together)")
 
-    def rate(self, table_shard, ids, meta, pred, mode=1, lanes=0):
-        """table_shard: float64 [rows, 2] on this rank's GPU, updated in place.
-        ids / meta / pred: the full arrays of the ladder on this GPU."""
-        assert table_shard.is_cuda and table_shard.dtype == torch.float64 and table_shard.shape == (self.rows, 2)
-        self._phase(0, table_shard)
-        self._barrier()                       # every shard is loaded before anyone polls it
-        self._phase(1, table_shard, ids, meta, pred, mode, lanes)
-        self._barrier()                       # every rank is done before rows are read back
-        self._phase(2, table_shard)
-        torch.cuda.synchronize(self.device)
+    def run(self, n_matches, mode=1, seq_base=0, outputs=None, lanes=0, first=True):
+        """One window: (reset |) link | rate |, tables updated in place in the owners' shards."""
+        if first:
+            self.reset()
+        self.barrier()
+        self.link(n_matches, mode, seq_base)
+        self.check()                   # synchronises: duplicates / overflow must not reach the rating kernel
+        self.barrier()
+        self.rate(n_matches, mode, seq_base, outputs, lanes)
+        self.barrier()
+        self.check()
 
     def close(self):
+        self.ids = self.meta = self.table = self.succ = {}
+        self._keep = []
         for p in self.opened:
             self.lib.ts_shard_close(p)
         self.opened = []
         if self.own:
+            torch.cuda.synchronize(self.device)
             self.lib.ts_shard_free(self.own)
-            self.own = C.c_void_p()
+            self.own = None

@@ -201,43 +201,78 @@ int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, cons
                    const ts_outputs *outputs, int32_t lanes_per_match, void *workspace, int64_t workspace_bytes,
                    void *stream);
 
-/* One ladder whose player table is hash-sharded over the G GPUs of a node
- * (BASELINE.json configs[4]): player p is owned by GPU p % G
- * (G a power of two <= 16) at local row p / G, one process per GPU.  Each rank
- * allocates its row shard with ts_shard_alloc (a dedicated cudaMalloc, because
- * the block is exported through CUDA IPC), exchanges the 64-byte handles, maps
- * its peers' shards with ts_shard_open (NVLink peer memory), and calls
- * ts_rate_stream_sharded in three phases separated by a barrier across ranks:
- * 0 load table_shard[rows][2] into the own rows, 1 rate the warp tiles t with
- * t % G == rank (ids / meta / pred are the full arrays of the ladder, stream
- * order), 2 read the own rows back.  Between GPUs there is no barrier and no
- * collective while rating: a match waits for the versions of its players' rows
- * wherever they live.  vt_shards: host array of G device pointers (index rank
- * = own shard).  Shard size: 32 bytes * ceil((n_players - rank) / G).
- * No counterpart in the reference (single process, single thread). */
-/* Linking for the sharded ladder: rank r links only the players it owns (p %
- * n_shards == r), sorted by local index, and leaves 0x7F7F7F7F in every slot of a
- * player owned elsewhere; an element-wise MIN of the ranks' pred arrays (one
- * all-reduce) yields the complete links, identical to ts_link_pred's.  `last`, if
- * given, has one entry per OWNED player (local index).  Sort and scatter work
- * shrink with 1 / n_shards; every rank still reads the whole id stream once. */
-int ts_link_pred_sharded(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
-                         int64_t n_players, const int8_t mode_col[16], int64_t seq_base, uint32_t *last,
-                         uint32_t *pred, int32_t rank, int32_t n_shards, void *workspace, int64_t workspace_bytes,
-                         void *stream);
+/* One ladder over the G GPUs of a node (BASELINE.json configs[4]), one
+ * process per GPU, G a power of two <= 16.  No counterpart in the reference (single
+ * process, single thread: worker.py:176-192 is the one sequential order this reproduces).
+ *
+ * Matches: blocks of TS_SHARD_BLOCK consecutive matches go round-robin to the GPUs --
+ * match m of a window lives on rank (m / 32) % G at local index ((m / 32) / G) * 32 +
+ * m % 32 -- and every rank holds only its own slice of ids / meta.
+ * Table: player p is owned by rank p % G (local row p / G): the owner holds the
+ * player's (mu, sigma) before the first and after the last match of a window.
+ * Rows travel to where they are needed: every rank has a mailbox of n_players
+ * versioned rows (32 bytes each); the rank that rates a player's match stores the new
+ * row, tagged with the number of the player's NEXT match, into the mailbox of the rank
+ * that will rate that match (one one-way NVLink store), and a match polls only its own
+ * GPU's mailbox until every row carries the match's own number.  After a player's last
+ * match the pair goes back to the owner's table shard.  No inter-GPU barrier and no
+ * collective while rating.
+ * Links: ts_shard_link reads the whole id stream once (its peers' slices over NVLink),
+ * keeps the slots of the players it owns, sorts them, and stores succ[m][s] (the
+ * stream-wide number of that player's next rated match, TS_NONE if none) straight into
+ * the slice of the rank that rates m, together with every owned player's first row.
+ * A player listed twice in one match is not supported here (TS_SHARD_DUPLICATE).
+ *
+ * All arrays of a ts_shard_view are device pointers valid on THIS GPU: index rank =
+ * own allocations, the others peer mappings (ts_shard_alloc / ts_shard_open).
+ * Call order per window, with a barrier across the ranks at every "|":
+ *   slices and table shards in place, ts_shard_reset | ts_shard_link | ts_shard_rate |
+ * Windows (seq_base > 0) continue a ladder: seq_base must be a multiple of 32 * G and
+ * stream-wide match numbers stay below 2^32 - 1; ts_shard_reset is for the first only. */
+#define TS_SHARD_BLOCK 32
+#define TS_SHARD_MAX 16
+typedef struct ts_shard_view {
+    int32_t rank, n_shards;
+    const uint32_t *ids[TS_SHARD_MAX];       /* [n_local(g)][slots]                              */
+    const uint32_t *meta[TS_SHARD_MAX];      /* [n_local(g)]                                     */
+    uint32_t *succ[TS_SHARD_MAX];            /* [n_local(g)][slots], written by the players' owners */
+    unsigned long long *rows[TS_SHARD_MAX];  /* mailbox: n_players rows of four 64-bit words      */
+    double *table[TS_SHARD_MAX];             /* [ceil((n_players - g) / G)][2]                    */
+} ts_shard_view;
+/* ts_shard_status bits */
+#define TS_SHARD_STALLED 1    /* a match's rows never arrived (watchdog): tables unusable      */
+#define TS_SHARD_OVERFLOW 2   /* ts_shard_link: workspace too small for the owned slots        */
+#define TS_SHARD_DUPLICATE 4  /* a player is listed twice in one match                          */
+int64_t ts_shard_local_matches(int64_t n_matches, int32_t rank, int32_t n_shards);
+/* workspace for ts_shard_link that holds `owned_cap` (player, slot) pairs; a rank owns
+ * about n_matches * slots / n_shards of them (all of them in the worst case) */
+int64_t ts_shard_link_workspace_bytes(int64_t owned_cap);
 int ts_shard_alloc(int device, int64_t bytes, void **ptr, void *handle64);
 int ts_shard_open(int device, const void *handle64, void **ptr);
 int ts_shard_close(void *ptr);
 int ts_shard_free(void *ptr);
-int ts_rate_stream_sharded(ts_ctx *ctx, int32_t phase, double *table_shard, int64_t n_players, int32_t rank,
-                           int32_t n_shards, void *const *vt_shards, int8_t mode, const uint32_t *ids,
-                           const uint32_t *meta, const uint32_t *pred, int64_t n_matches, int32_t slots,
-                           const ts_outputs *outputs, int32_t lanes_per_match, void *stream);
+int ts_shard_reset(ts_ctx *ctx, const ts_shard_view *view, int64_t n_players, void *stream);
+int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
+                  int8_t mode, int64_t seq_base, void *workspace, int64_t workspace_bytes, void *stream);
+/* outputs: indexed by the LOCAL match index of this rank.  emulate_all = 1: this one
+ * launch plays every rank of the view on one GPU (all pointers local; testing and
+ * single-GPU runs of the sharded code path); outputs are then indexed by the window's
+ * match number. */
+int ts_shard_rate(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
+                  int8_t mode, int64_t seq_base, const ts_outputs *outputs, int32_t lanes_per_match,
+                  int32_t emulate_all, void *stream);
+/* TS_SHARD_* bits raised on this context since the last ts_shard_reset.  Synchronises the stream. */
+int ts_shard_status(ts_ctx *ctx, void *stream);
 
 /* Number of matches that ended in TS_ST_FP_ERROR / TS_ST_VALUE_ERROR since the
  * last ts_reset_errors (the reference raises and fails the whole batch,
  * worker.py:108-120,195-197).  Synchronises the stream. */
 int64_t ts_error_count(ts_ctx *ctx, void *stream);
+/* the two kinds apart, so that a host can raise what the reference would raise without
+ * asking for the per-match status bytes */
+int ts_error_counts(ts_ctx *ctx, int64_t *fp_errors, int64_t *value_errors, void *stream);
+/* also clears the stall flag of the streaming kernels, which is sticky: after a stall
+ * every streaming launch on this context returns at once until this call */
 int ts_reset_errors(ts_ctx *ctx, void *stream);
 
 /* get_trueskill_seed (rater.py:42-62) for a column of players, on the device:

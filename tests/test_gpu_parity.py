@@ -249,3 +249,45 @@ def test_full_size_properties(eng, rater, c_oracle):
     out = c_oracle.rate_sequential(c_oracle.make_params(), ids, meta, want, -1, ptab.mode_cols[:6], quad=True)
     assert out["errors"] == 0
     assert np.abs(tab_d.cpu().numpy() - want).max() < TOL
+
+
+def test_player_id_outside_the_table_is_refused(eng, rater):
+    """A corrupt id (>= n_players) is never used as an index: its match gets TS_ST_VALUE_ERROR on
+    every path, nobody else is touched through it, and the batch raises ValueError with or without
+    the status column."""
+    from analyzer_b200 import _lib
+    rng = np.random.default_rng(5)
+    n, u = 3000, 400
+    ids, meta = H.small_ladder(rng, n, u, slots=6, modes=(1,))
+    bad = ids.copy()
+    bad[1234, 4] = u                      # exactly one past the table
+    bad[2000, 0] = 0xFFFFFFF0
+    tab = np.empty((u, 1, 2))
+    tab[:, 0] = (1500.0, 300.0)
+    finals = []
+    for path in ("rounds", "stream"):
+        tab_d = _dev(tab)
+        ptab = eng.PlayerTable(tab_d, -1, [-1, 0])
+        outs = rater.alloc_outputs(n, 6)
+        rater.reset_errors()
+        if path == "rounds":
+            rater.rate(ptab, rater.schedule(_dev(bad), _dev(meta), u, ptab.mode_cols), outs)
+        else:
+            rater.rate_stream(ptab, _dev(bad), _dev(meta), rater.link_pred(_dev(bad), _dev(meta), u, ptab.mode_cols), outs)
+        assert rater.error_counts() == (0, 2)
+        st = outs["status"].cpu().numpy()
+        assert st[1234] == st[2000] == _lib.ST_VALUE_ERROR and int((st != 0).sum()) == 2
+        finals.append(tab_d.cpu().numpy())
+    assert np.abs(finals[0] - finals[1]).max() < TOL
+    # shared + queue layout, stream path
+    tab2 = np.full((u, 2, 2), np.nan)
+    tab2[:, 0] = (1500.0, 300.0)
+    tab_d = _dev(tab2)
+    ptab = eng.PlayerTable(tab_d, 0, [-1, 1])
+    rater.reset_errors()
+    rater.rate_stream(ptab, _dev(bad), _dev(meta), rater.link_pred(_dev(bad), _dev(meta), u, ptab.mode_cols))
+    assert rater.error_counts() == (0, 2)
+    rater.reset_errors()
+    for want_outputs in (True, False):
+        with pytest.raises(ValueError):
+            rater.rate_batch(bad, meta, tab, shared_col=-1, mode_cols=[-1, 0], want_outputs=want_outputs)

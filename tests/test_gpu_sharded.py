@@ -1,8 +1,9 @@
-"""Sharded ladder on 2 GPUs (skipped on a single-GPU box): one process per GPU,
-table rows in NVLink peer memory, no collective while rating.  The result must
-agree with the single-GPU streaming path within the 1e-9 tolerance: same
-arithmetic, and the row versions enforce every player's stream order across
-GPUs."""
+"""The sharded ladder (ts_shard_link / ts_shard_rate, rows pushed to the rank that reads
+them).  On one GPU every rank of a 1/2/4/8-way ladder is played by one launch
+(emulate=True: same kernels, same index arithmetic, every pointer local); with 2 GPUs
+the real thing runs, one process per GPU over NVLink peer memory.  The tables must equal
+the single-GPU stream path BIT FOR BIT (both use the same explicitly rounded pass) and
+stay within 1e-9 of the sequential float128 oracle."""
 import os
 
 import numpy as np
@@ -12,6 +13,131 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 pytestmark = pytest.mark.gpu
+
+CASES = [(6, False, 0.0), (10, True, 0.02)]
+
+
+def _single(engine, r, ids, meta, full, u, outputs=None):
+    single = full.clone().reshape(u, 1, 2)
+    pt = engine.PlayerTable.ladder(single, mode=1)
+    pred = r.link_pred(ids, meta, u, pt.mode_cols)
+    r.rate_stream(pt, ids, meta, pred, outputs)
+    assert r.error_count() == 0
+    return single.reshape(u, 2), pred
+
+
+@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("slots,zipf,p_draw", CASES)
+def test_emulated_ranks_equal_single_gpu_and_oracle(c_oracle, world, slots, zipf, p_draw):
+    from analyzer_b200 import engine, sharded
+    co = c_oracle
+    dev = torch.device("cuda", 0)
+    n, u, seed = 60_011, 3_001, 0xA11CE005
+    r = engine.Rater(engine.Env(draw_probability=p_draw), 0)
+    gen = engine.make_gen(seed, u, slots=slots, mode=1, p_draw=p_draw, p_afk=0.02, zipf=zipf)
+    ids, meta = engine.gen_matches(gen, 0, n, dev)
+    full = engine.gen_table(seed, 0, u, dev).reshape(u, 2)
+    outs1 = r.alloc_outputs(n, slots)
+    want, pred = _single(engine, r, ids, meta, full, u, outs1)
+    ladder = sharded.ShardedLadder(r, u, n, slots, 0, world, emulate=True)
+    ladder.set_stream(ids, meta)
+    ladder.set_table(full)
+    outs = r.alloc_outputs(n, slots)
+    ladder.run(n, mode=1, outputs=outs)
+    assert r.error_count() == 0
+    got = sharded.merge_tables([ladder.table[g] for g in range(world)])
+    assert torch.equal(got, want), float((got - want).abs().max())
+    for k in ("quality", "out_queue", "status"):
+        a, b = outs[k], outs1[k]
+        assert torch.equal(torch.nan_to_num(a.double(), nan=-7.0), torch.nan_to_num(b.double(), nan=-7.0)), k
+    # the links: succ is the inverse of the single-GPU pred on every slot that takes part
+    pred_h = pred.cpu().numpy().view(np.uint32)
+    succ_full = np.full((n, slots), 0xFFFFFFFF, dtype=np.uint32)
+    for g in range(world):
+        nl = sharded.local_matches(n, g, world)
+        gm = np.array([sharded.global_index(lm, g, world) for lm in range(nl)], dtype=np.int64)
+        succ_full[gm] = ladder.succ[g][:nl].cpu().numpy().view(np.uint32)
+    ids_h = ids.cpu().numpy().view(np.uint32)
+    meta_h = meta.cpu().numpy().view(np.uint32)
+    live = ((meta_h & 12) == 0)
+    last = {}
+    want_succ = np.full((n, slots), 0xFFFFFFFF, dtype=np.uint32)
+    for m in range(n):
+        if not live[m]:
+            continue
+        for s in range(slots):
+            p = int(ids_h[m, s])
+            if p in last:
+                pm, ps = last[p]
+                want_succ[pm, ps] = m
+                assert pred_h[m, s] == pm
+            last[p] = (m, s)
+    used = live[:, None] & np.ones((1, slots), dtype=bool)
+    assert np.array_equal(succ_full[used], want_succ[used])
+    # float128 sequential oracle
+    tab = full.cpu().numpy().reshape(u, 1, 2).copy()
+    co.rate_sequential(co.make_params(draw_probability=p_draw), ids_h, meta_h, tab, -1, [-1, 0], quad=True)
+    assert float(np.abs(got.cpu().numpy() - tab.reshape(u, 2)).max()) < 1e-9
+    ladder.close()
+    r.close()
+
+
+def test_emulated_windows_equal_one_shot():
+    """A ladder rated window after window (the owners' table shards carry the state) equals one shot."""
+    from analyzer_b200 import engine, sharded
+    dev = torch.device("cuda", 0)
+    world, slots = 4, 6
+    n, u, seed = 40_000, 2_003, 0xA11CE006
+    r = engine.Rater(engine.Env(), 0)
+    ids, meta = engine.gen_matches(engine.make_gen(seed, u, slots=slots, mode=1, p_afk=0.01), 0, n, dev)
+    full = engine.gen_table(seed, 0, u, dev).reshape(u, 2)
+    want, _ = _single(engine, r, ids, meta, full, u)
+    win = 32 * world * 100                      # windows start at multiples of 32 * world
+    ladder = sharded.ShardedLadder(r, u, win, slots, 0, world, emulate=True)
+    ladder.set_table(full)
+    for lo in range(0, n, win):
+        hi = min(n, lo + win)
+        ladder.set_stream(ids[lo:hi], meta[lo:hi])
+        ladder.run(hi - lo, mode=1, seq_base=lo, first=(lo == 0))
+    got = sharded.merge_tables([ladder.table[g] for g in range(world)])
+    assert torch.equal(got, want)
+    assert r.error_count() == 0
+    ladder.close()
+
+
+def test_duplicate_player_and_bad_id_are_reported():
+    from analyzer_b200 import _lib, engine, sharded
+    dev = torch.device("cuda", 0)
+    world, slots, n, u = 2, 6, 500, 400
+    r = engine.Rater(engine.Env(), 0)
+    ids, meta = engine.gen_matches(engine.make_gen(5, u, slots=slots, mode=1), 0, n, dev)
+    full = engine.gen_table(5, 0, u, dev).reshape(u, 2)
+    ladder = sharded.ShardedLadder(r, u, n, slots, 0, world, emulate=True)
+    bad = ids.clone()
+    bad[100, 3] = bad[100, 0]                   # the same player twice in one match
+    ladder.set_stream(bad, meta)
+    ladder.set_table(full)
+    with pytest.raises(_lib.TsError, match="twice"):
+        ladder.run(n, mode=1)
+    # an id beyond the table is nobody's: the match is refused (ValueError status), everyone else goes on
+    bad = ids.clone()
+    bad[100, 3] = u + 5
+    ladder.set_stream(bad, meta)
+    ladder.set_table(full)
+    r.reset_errors()
+    outs = r.alloc_outputs(n, slots)
+    ladder.run(n, mode=1, outputs=outs)
+    assert int(outs["status"][100]) == _lib.ST_VALUE_ERROR
+    fp, val = r.error_counts()
+    assert (fp, val) == (0, 1)
+    single = full.clone().reshape(u, 1, 2)
+    pt = engine.PlayerTable.ladder(single, mode=1)
+    r.reset_errors()
+    r.rate_stream(pt, bad, meta, r.link_pred(bad, meta, u, pt.mode_cols))
+    assert r.error_counts() == (0, 1)
+    got = sharded.merge_tables([ladder.table[g] for g in range(world)])
+    assert torch.equal(got, single.reshape(u, 2))
+    ladder.close()
 
 
 def _worker(rank, world, port, results):
@@ -23,36 +149,24 @@ def _worker(rank, world, port, results):
     from analyzer_b200 import engine, sharded
     n, u, seed = 200_000, 3_001, 0xA11CE005
     ok = True
-    for slots, zipf in ((6, False), (10, True)):
-        r = engine.Rater(engine.Env(draw_probability=0.02), rank)
-        gen = engine.make_gen(seed, u, slots=slots, mode=1, p_draw=0.02, p_afk=0.02, zipf=zipf)
+    for slots, zipf, p_draw in CASES:
+        r = engine.Rater(engine.Env(draw_probability=p_draw), rank)
+        gen = engine.make_gen(seed, u, slots=slots, mode=1, p_draw=p_draw, p_afk=0.02, zipf=zipf)
         ids, meta = engine.gen_matches(gen, 0, n, dev)
         full = engine.gen_table(seed, 0, u, dev).reshape(u, 2)
-        ladder = sharded.ShardedLadder(r, u, rank, world)
-        single_pred = r.link_pred(ids, meta, u, [-1, 0])
-        pred = ladder.link(ids, meta, [-1, 0])              # owned players only + MIN all-reduce
-        live = single_pred != pred
-        # identical on every slot that takes part; unused slots read TS_NONE vs the fill value
-        ok = ok and bool(((single_pred == -1) & (pred == 0x7F7F7F7F))[live].all())
-        mine = sharded.split_table(full, rank, world)
-        ladder.rate(mine, ids, meta, pred, mode=1)
+        want, _ = _single(engine, r, ids, meta, full, u)
+        ladder = sharded.ShardedLadder(r, u, n, slots, rank, world)
+        ladder.set_stream(ids, meta)
+        ladder.set_table(full)
+        ladder.run(n, mode=1)
         errs = r.error_count()
-        gathered = [None] * world
-        dist.all_gather_object(gathered, mine.cpu())
-        if rank == 0:
-            single = full.clone().reshape(u, 1, 2)
-            r.rate_stream(engine.PlayerTable.ladder(single, mode=1), ids, meta, pred)
-            merged = sharded.merge_tables(gathered)
-            want = single.reshape(u, 2).cpu()
-            diff = (merged - want).abs()
-            # not bit-for-bit: the sharded and the single-GPU kernel are different template
-            # instantiations and the compiler contracts their FMAs differently (last-bit
-            # differences, ~3e-12 after 400-deep chains); a race would show as a gross error
-            same = float(diff.max()) < 1e-9 and errs == 0 and r.error_count() == 0
-            if not same:
-                print("sharded mismatch: slots", slots, "errs", errs, "rows differing", int((diff > 0).any(dim=1).sum()),
-                      "max", float(diff.max()), "nan", int(torch.isnan(merged).sum()), flush=True)
-            ok = ok and same
+        mine = ladder.table[rank]
+        same = torch.equal(mine, want[rank::world]) and errs == 0        # bit for bit
+        if not same:
+            diff = (mine - want[rank::world]).abs()
+            print("sharded mismatch: rank", rank, "slots", slots, "errs", errs, "rows differing",
+                  int((diff > 0).any(dim=1).sum()), "max", float(diff.max()), flush=True)
+        ok = ok and same
         dist.barrier()
         ladder.close()
         r.close()
@@ -61,7 +175,7 @@ def _worker(rank, world, port, results):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_sharded_ladder_equals_single_gpu():
+def test_sharded_ladder_two_gpus_equals_single_gpu():
     world = 2
     with mp.Manager() as mgr:
         results = mgr.dict()
