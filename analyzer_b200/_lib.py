@@ -28,7 +28,7 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_static", "ts_schedule_static_max_slot_entries",
            "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream",
            "ts_stream_stalled", "ts_rate_stream_table_workspace_bytes",
-           "ts_seed_table", "ts_widen_meta", "ts_error_counts",
+           "ts_seed_table", "ts_widen_meta", "ts_unpack_ids", "ts_error_counts",
            "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_shard_local_matches",
            "ts_shard_link_workspace_bytes", "ts_shard_reset", "ts_shard_link", "ts_shard_rate", "ts_shard_status"]
 SHARD_BLOCK, SHARD_MAX = 32, 16
@@ -59,7 +59,8 @@ class TsOutputs(C.Structure):
 class TsShardView(C.Structure):
     _fields_ = [("rank", C.c_int32), ("n_shards", C.c_int32),
                 ("ids", C.c_void_p * 16), ("meta", C.c_void_p * 16), ("succ", C.c_void_p * 16),
-                ("rows", C.c_void_p * 16), ("table", C.c_void_p * 16)]
+                ("rows", C.c_void_p * 16), ("table", C.c_void_p * 16), ("inbox", C.c_void_p * 16),
+                ("inbox_count", C.c_void_p * 16), ("inbox_cap", C.c_int64)]
 
 
 class TsGen(C.Structure):
@@ -151,6 +152,7 @@ def lib():
         L.ts_seed_table.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double,
                                     C.POINTER(C.c_double), C.c_void_p, C.c_void_p, C.c_void_p]
         L.ts_widen_meta.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.ts_unpack_ids.argtypes = [C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p]
         L.ts_gen_matches.argtypes = [C.POINTER(TsGen), C.c_int64, C.c_int64, C.c_void_p, C.c_void_p,
                                      C.c_void_p]
         L.ts_gen_table.argtypes = [C.c_uint64, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p]

@@ -198,3 +198,47 @@ extern "C" int ts_widen_meta(const uint8_t *meta8, int64_t n_matches, uint32_t *
     TS_CUDA(cudaGetLastError());
     return 0;
 }
+
+// Ingest helper: player ids shipped at the width they need.  A host column of n ids packed as a
+// little-endian bit stream of `bits` bits each (bits = ceil(log2(n_players + 1)); the all-ones
+// value stands for TS_EMPTY_SLOT) is 20/32 of the 32-bit column for a million players -- and the
+// PCIe copy of that column is what bounds the end-to-end call.  Four ids per thread: the 4 * bits
+// bits they occupy start on a nibble boundary at worst, read as unaligned bytes.
+__global__ void __launch_bounds__(256) k_unpack_ids(const uint8_t *packed, int bits, int64_t count, uint32_t *ids)
+{
+    const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i0 >= count) return;
+    const uint32_t mask = bits >= 32 ? 0xFFFFFFFFu : ((1u << bits) - 1u);
+    uint32_t out[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int64_t i = i0 + j;
+        out[j] = TS_EMPTY_SLOT;
+        if (i >= count) continue;
+        const int64_t bit = i * bits;
+        const uint8_t *src = packed + (bit >> 3);
+        unsigned long long w = 0;                       // up to 5 bytes hold 7 + 32 bits
+        const int n_bytes = (int)(((bit & 7) + bits + 7) >> 3);
+        for (int b = 0; b < n_bytes; ++b) w |= (unsigned long long)__ldg(src + b) << (8 * b);
+        const uint32_t v = (uint32_t)(w >> (bit & 7)) & mask;
+        out[j] = v == mask ? TS_EMPTY_SLOT : v;
+    }
+    if (i0 + 4 <= count && ((reinterpret_cast<uintptr_t>(ids + i0) & 15u) == 0u)) {
+        *reinterpret_cast<uint4 *>(ids + i0) = make_uint4(out[0], out[1], out[2], out[3]);
+        return;
+    }
+    for (int j = 0; j < 4 && i0 + j < count; ++j) ids[i0 + j] = out[j];
+}
+
+extern "C" int ts_unpack_ids(const uint8_t *packed, int32_t bits, int64_t count, uint32_t *ids, void *stream)
+{
+    if (bits < 1 || bits > 32 || count < 0 || (count > 0 && (!packed || !ids))) {
+        ts_set_error("ts_unpack_ids: bad arguments (bits must be 1..32)");
+        return TS_E_ARG;
+    }
+    if (count == 0) return 0;
+    const int64_t threads = (count + 3) / 4;
+    k_unpack_ids<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(packed, bits, count, ids);
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -125,6 +125,10 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
     const double tb2 = tau2 + beta2;
     const double margin_full = a.prm.draw_margin[P];
     const uint32_t n_rounds = __ldcg(&a.info->n_rounds);
+    if (__ldcg(&a.info->overflow) != 0u) {      // round_offsets was too small for this schedule: rate nothing, say so
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&a.ctrl[CTRL_VALUE_ERRORS], 1ull);
+        return;
+    }
     const bool want_order = a.out.quality || a.out.out_shared || a.out.out_delta || a.out.out_queue || a.out.status;
     unsigned long long generation = 0;
 

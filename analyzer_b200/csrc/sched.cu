@@ -326,8 +326,12 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t *p, uint32_t v)
 __global__ void __launch_bounds__(kSortBlock, TS_SORT_MIN_BLOCKS)
 k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n_in, const uint32_t *n_dev, int shift,
                  const uint32_t *digit_base, uint32_t *status, uint32_t *ticket, uint32_t *keys_out,
-                 uint32_t *vals_out)
+                 uint32_t *vals_out, const uint32_t *key_bound)
 {
+    // key_bound (optional, device): the largest key.  A pass whose digit is zero for every key
+    // would only copy: it is skipped, and the consumers find the result one buffer earlier
+    // (result_buffer below) -- the pass count is decided on the device, the host never waits.
+    if (key_bound && shift > 0 && (__ldg(key_bound) >> shift) == 0u) return;
     const uint32_t n = n_dev ? __ldg(n_dev) : n_in;
     __shared__ uint32_t wcount[kWarps][256];
     __shared__ uint32_t gbase[256];
@@ -733,15 +737,31 @@ k_levels(const uint32_t *pred, const uint32_t *meta, uint32_t rated_mask, uint32
     }
 }
 
-// round_offsets from the rounds in sorted order: bucket r starts where the first key >= r stands
-__global__ void __launch_bounds__(256)
-k_round_bounds(const uint32_t *sorted_round, uint32_t n, uint32_t n_rounds, uint32_t *round_offsets)
+// which of the two ping-pong buffers holds a sort whose passes beyond the largest key were skipped
+__device__ __forceinline__ int result_buffer(uint32_t key_bound)
 {
+    int passes = 1;
+    while (passes < 4 && (key_bound >> (8 * passes)) != 0u) ++passes;
+    return (passes - 1) & 1;
+}
+
+// round_offsets from the rounds in sorted order: bucket r starts where the first key >= r stands;
+// order = the match indices in that order.  The number of rounds is read on the device.
+__global__ void __launch_bounds__(256)
+k_round_bounds(const uint32_t *keys0, const uint32_t *keys1, const uint32_t *vals0, const uint32_t *vals1, uint32_t n,
+               ts_sched_info *info, uint32_t cap, uint32_t *round_offsets, uint32_t *order)
+{
+    const uint32_t n_rounds = info->n_rounds;
+    const int buf = result_buffer(n_rounds);
+    const uint32_t *sorted_round = buf ? keys1 : keys0;
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0 && (uint64_t)n_rounds + 2 > (uint64_t)cap) info->overflow = 1;
     if (i > n) return;
+    if (i < n) order[i] = __ldg((buf ? vals1 : vals0) + i);
     const uint32_t lo = i == 0 ? 0u : __ldg(sorted_round + i - 1) + 1u;           // first bucket starting at i
     const uint32_t hi = i == n ? n_rounds + 1u : __ldg(sorted_round + i);         // last one
-    for (uint32_t r = lo; r <= hi; ++r) round_offsets[r] = i;
+    for (uint32_t r = lo; r <= hi; ++r)
+        if (r < cap) round_offsets[r] = i;
 }
 
 struct Workspace {
@@ -856,11 +876,12 @@ int radix_onesweep_enabled()
 // staged: the pairs already stand in w.keys[0] / w.vals[0] and their number in *n_dev
 // (n is then only an upper bound that sizes the grids): the owned slots of a sharded ladder.
 int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream, int sm_count,
-               const uint32_t *n_dev = nullptr)
+               const uint32_t *n_dev = nullptr, const uint32_t *key_bound = nullptr)
 {
     const int passes = (bits + 7) / 8;
     const bool staged = n_dev != nullptr;
     if (n >= (1u << 30) || passes > kMaxPasses || !radix_onesweep_enabled()) {
+        if (key_bound) return TS_E_UNSUPPORTED;      // the caller sizes the sort on the host instead
         if (staged) {
             ts_set_error("the sharded ladder needs the single-sweep sort (fewer than 2^30 owned slot entries per window)");
             return TS_E_UNSUPPORTED;
@@ -885,7 +906,7 @@ int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStrea
             cudaMemsetAsync(ticket, 0, 4, stream) != cudaSuccess)
             return ts_cuda_fail(cudaGetLastError(), "memset");
         k_radix_onesweep<<<n_tiles, kSortBlock, 0, stream>>>(src, vals_in, vals_in ? 0 : 1, n, n_dev, p * 8, ghist + p * 256,
-                                                             w.hist, ticket, w.keys[dst], w.vals[dst]);
+                                                             w.hist, ticket, w.keys[dst], w.vals[dst], key_bound);
         cur = dst;
     }
     cudaError_t e = cudaGetLastError();
@@ -970,10 +991,8 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     TS_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
     if (n_matches == 0) {
-        ts_sched_info z = {0, 0, 0, 0};
-        TS_CUDA(cudaMemcpyAsync(info, &z, sizeof z, cudaMemcpyHostToDevice, s));
+        TS_CUDA(cudaMemsetAsync(info, 0, sizeof(ts_sched_info), s));
         TS_CUDA(cudaMemsetAsync(round_offsets, 0, 3 * sizeof(uint32_t), s));
-        TS_CUDA(cudaStreamSynchronize(s));
         if (n_rounds_host) *n_rounds_host = 0;
         return 0;
     }
@@ -1051,20 +1070,6 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     }
 
     // 4. bucket by round, ascending match_seq inside a round
-    ts_sched_info h;
-    TS_CUDA(cudaMemcpyAsync(&h, info, sizeof h, cudaMemcpyDeviceToHost, s));
-    TS_CUDA(cudaStreamSynchronize(s));
-    // errors were reset together with the control words above: keep the count
-    if (by_levels && (uint64_t)h.n_rounds + 2 > (uint64_t)cap) {
-        h.overflow = 1;
-        TS_CUDA(cudaMemcpyAsync(info, &h, sizeof h, cudaMemcpyHostToDevice, s));
-        TS_CUDA(cudaStreamSynchronize(s));
-    }
-    if (h.overflow) {
-        ts_set_error("ts_schedule: %u rounds need offsets_cap >= %u (got %lld)", h.n_rounds, h.n_rounds + 2,
-                     (long long)offsets_cap);
-        return TS_E_WORKSPACE;
-    }
     KeySrc rsrc;
     rsrc.keys = round;
     rsrc.meta = nullptr;
@@ -1074,17 +1079,44 @@ extern "C" int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *met
     rsrc.from_ids = 0;
     rsrc.slots_magic = 0ull;   // unused: keys are read as they are
     rsrc.rated_mask = 0;
-    buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s, ctx->sm_count);
-    if (buf < 0) return buf;
-    TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
-    if (by_levels) k_round_bounds<<<n / 256 + 1, 256, 0, s>>>(w.keys[buf], n, h.n_rounds, round_offsets);
+    bool async = by_levels && !n_rounds_host && n < (1u << 30) && radix_onesweep_enabled();
+    if (async) {
+        // The number of rounds stays on the device: the sort is launched for as many passes as n
+        // matches could need and the passes beyond the largest round skip themselves; bounds,
+        // order and the overflow flag are written by k_round_bounds.  No host wait anywhere.
+        buf = radix_sort(rsrc, n, bits_for((uint64_t)n), w, s, ctx->sm_count, nullptr, &info->n_rounds);
+        if (buf < 0) return buf;
+        k_round_bounds<<<n / 256 + 1, 256, 0, s>>>(w.keys[0], w.keys[1], w.vals[0], w.vals[1], n, info, cap, round_offsets,
+                                                   order);
+    } else {
+        ts_sched_info h;
+        TS_CUDA(cudaMemcpyAsync(&h, info, sizeof h, cudaMemcpyDeviceToHost, s));
+        TS_CUDA(cudaStreamSynchronize(s));
+        if (by_levels && (uint64_t)h.n_rounds + 2 > (uint64_t)cap) {
+            h.overflow = 1;
+            TS_CUDA(cudaMemcpyAsync(info, &h, sizeof h, cudaMemcpyHostToDevice, s));
+            TS_CUDA(cudaStreamSynchronize(s));
+        }
+        if (h.overflow) {
+            ts_set_error("ts_schedule: %u rounds need offsets_cap >= %u (got %lld)", h.n_rounds, h.n_rounds + 2,
+                         (long long)offsets_cap);
+            return TS_E_WORKSPACE;
+        }
+        buf = radix_sort(rsrc, n, bits_for((uint64_t)h.n_rounds), w, s, ctx->sm_count);
+        if (buf < 0) return buf;
+        if (by_levels)
+            k_round_bounds<<<n / 256 + 1, 256, 0, s>>>(w.keys[buf], w.keys[buf], w.vals[buf], w.vals[buf], n, info, cap,
+                                                       round_offsets, order);
+        else
+            TS_CUDA(cudaMemcpyAsync(order, w.vals[buf], (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+        if (n_rounds_host) *n_rounds_host = h.n_rounds;
+    }
     if (ids_sorted && meta_sorted) {
         size_t total = (size_t)n * slots;
         k_permute<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(ids, meta, order, n, (uint32_t)slots, ids_sorted,
                                                                   meta_sorted);
     }
     TS_CUDA(cudaGetLastError());
-    if (n_rounds_host) *n_rounds_host = h.n_rounds;
     return 0;
 }
 
@@ -1153,10 +1185,11 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
 //      window) of every live slot of an owned player (single pass, decoupled look-back);
 //   2. the pairs are radix-sorted by local player index (same single-sweep passes as the
 //      one-GPU sort, their number known only on the device);
-//   3. k_succ walks the sorted runs: a slot's successor match goes straight into the succ
-//      slice of the rank that rates the slot's match (peer store), and the head of every
-//      run sends the player's pair from the owner's table shard to the mailbox of the rank
-//      that rates the player's first match, tagged with that match's number.
+//   3. k_succ_route walks the sorted runs: a slot's successor match becomes a message to the
+//      rank that rates the slot's match, appended to that rank's inbox in large coalesced
+//      pieces (the receiver scatters them into its succ slice, k_succ_apply), and the head of
+//      every run sends the player's pair from the owner's table shard to the mailbox of the
+//      rank that rates the player's first match, tagged with that match's number.
 // ---------------------------------------------------------------------------
 namespace {
 
@@ -1256,9 +1289,12 @@ k_owned_compact(ShardSrc src, uint32_t np, uint32_t cap, uint32_t *status, uint3
 }
 
 struct ShardDst {
-    uint32_t *succ[TS_SHARD_MAX];
+    unsigned long long *inbox[TS_SHARD_MAX];     // rank g's inbox: one region of inbox_cap messages per sender
+    uint32_t *inbox_count[TS_SHARD_MAX];         // rank g's message counts, one per sender
     unsigned long long *rows[TS_SHARD_MAX];
     const double *table_own;
+    uint32_t *out_count;                         // this rank's running message count per destination
+    uint32_t inbox_cap;
     uint32_t g_mask, g_shift, owner;
     uint32_t slots;
     unsigned long long slots_magic;
@@ -1270,36 +1306,101 @@ __device__ __forceinline__ void st_row_sys(unsigned long long *row, double mu, d
     const unsigned long long v = (unsigned long long)ver << 32;
     const unsigned long long m = (unsigned long long)__double_as_longlong(mu);
     const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
-    asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"((m & 0xFFFFFFFFull) | v), "l"((m >> 32) | v) : "memory");
-    asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"((s & 0xFFFFFFFFull) | v), "l"((s >> 32) | v) : "memory");
+    asm volatile("st.relaxed.sys.global.v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(row), "l"((m & 0xFFFFFFFFull) | v),
+                 "l"((m >> 32) | v), "l"((s & 0xFFFFFFFFull) | v), "l"((s >> 32) | v) : "memory");
 }
 
-// one thread per sorted entry; destinations m in [m_lo, m_hi) only (the scatter is done in
-// passes over ranges that the destination GPUs' L2 can hold, like k_pred)
+// Successor links, routed: a scattered 4-byte store into another GPU's memory is a partial-sector
+// write over NVLink (measured on 2 B200s: 150M of them take 185 ms, 0.8 G/s), so the links do not
+// go to their slots directly.  A block of 1024 sorted entries sorts its (local slot index,
+// successor) messages by destination rank in shared memory and appends each destination's run to
+// this sender's region of that rank's inbox with consecutive threads on consecutive addresses
+// (full sectors, large NVLink packets); the destination scatters its inbox locally
+// (k_succ_apply).  The head of every player's run also sends the player's pair from the owner's
+// table shard to the mailbox of the rank that rates the player's first match (a full 32-byte row).
+constexpr int kRouteItems = 4, kRouteTile = 256 * kRouteItems;
+
 __global__ void __launch_bounds__(256)
-k_succ(const uint32_t *keys, const uint32_t *vals, const uint32_t *n_dev, ShardDst dst, uint32_t m_lo, uint32_t m_hi,
-       unsigned long long *ctrl)
+k_succ_route(const uint32_t *keys, const uint32_t *vals, const uint32_t *n_dev, ShardDst dst, unsigned long long *ctrl)
 {
+    __shared__ uint32_t s_cnt[TS_SHARD_MAX], s_start[TS_SHARD_MAX], s_base[TS_SHARD_MAX];
+    __shared__ unsigned long long s_msg[kRouteTile];
     const uint32_t n = __ldg(n_dev);
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const uint32_t k = __ldcs(keys + i), v = __ldcs(vals + i);
-    const uint32_t m = (uint32_t)__umul64hi((unsigned long long)v, dst.slots_magic);
-    if (m < m_lo || m >= m_hi) return;
-    const uint32_t sl = v - m * dst.slots;
-    uint32_t nxt = TS_NONE;
-    if (i + 1 < n && __ldcs(keys + i + 1) == k) {
-        const uint32_t m2 = (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + i + 1), dst.slots_magic);
-        if (m2 == m) atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_DUPLICATE);
-        nxt = dst.seq_base + m2;
+    const uint32_t tile_base = blockIdx.x * kRouteTile;
+    if (tile_base >= n) return;
+    if (threadIdx.x < TS_SHARD_MAX) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t off[kRouteItems], to[kRouteItems];
+    unsigned long long msg[kRouteItems];
+#pragma unroll
+    for (int j = 0; j < kRouteItems; ++j) {
+        const uint32_t i = tile_base + j * 256 + threadIdx.x;
+        to[j] = TS_NONE;
+        if (i >= n) continue;
+        const uint32_t k = __ldcs(keys + i), v = __ldcs(vals + i);
+        const uint32_t m = (uint32_t)__umul64hi((unsigned long long)v, dst.slots_magic);
+        const uint32_t sl = v - m * dst.slots;
+        uint32_t nxt = TS_NONE;
+        if (i + 1 < n && __ldcs(keys + i + 1) == k) {
+            const uint32_t m2 = (uint32_t)__umul64hi((unsigned long long)__ldcs(vals + i + 1), dst.slots_magic);
+            if (m2 == m) atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_DUPLICATE);
+            nxt = dst.seq_base + m2;
+        }
+        const uint32_t blk = m >> 5, r = blk & dst.g_mask;
+        const uint32_t lm = ((blk >> dst.g_shift) << 5) | (m & 31u);
+        to[j] = r;
+        msg[j] = ((unsigned long long)nxt << 32) | (unsigned long long)(lm * dst.slots + sl);
+        off[j] = atomicAdd(&s_cnt[r], 1u);
+        if (i == 0 || __ldcs(keys + i - 1) != k) {            // the player's first match of the window
+            const double2 pr = __ldg(reinterpret_cast<const double2 *>(dst.table_own) + k);
+            const uint32_t pid = (k << dst.g_shift) | dst.owner;
+            st_row_sys(dst.rows[r] + (size_t)pid * 4, pr.x, pr.y, dst.seq_base + m);
+        }
     }
-    const uint32_t blk = m >> 5, r = blk & dst.g_mask;
-    const uint32_t lm = ((blk >> dst.g_shift) << 5) | (m & 31u);
-    dst.succ[r][(size_t)lm * dst.slots + sl] = nxt;
-    if (i == 0 || __ldcs(keys + i - 1) != k) {            // the player's first match of the window
-        const double2 pr = __ldg(reinterpret_cast<const double2 *>(dst.table_own) + k);
-        const uint32_t pid = (k << dst.g_shift) | dst.owner;
-        st_row_sys(dst.rows[r] + (size_t)pid * 4, pr.x, pr.y, dst.seq_base + m);
+    __syncthreads();
+    if (threadIdx.x <= dst.g_mask) {
+        const uint32_t c = s_cnt[threadIdx.x];
+        s_base[threadIdx.x] = c ? atomicAdd(&dst.out_count[threadIdx.x], c) : 0u;   // this block's place in every inbox
+    }
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (uint32_t g = 0; g <= dst.g_mask; ++g) { s_start[g] = run; run += s_cnt[g]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kRouteItems; ++j)
+        if (to[j] != TS_NONE) s_msg[s_start[to[j]] + off[j]] = msg[j];
+    __syncthreads();
+    const uint32_t total = min((uint32_t)kRouteTile, n - tile_base);
+    for (uint32_t pos = threadIdx.x; pos < total; pos += 256) {
+        uint32_t g = 0;
+        while (g < dst.g_mask && pos >= s_start[g + 1]) ++g;
+        const uint32_t idx = s_base[g] + (pos - s_start[g]);
+        if (idx < dst.inbox_cap) dst.inbox[g][(size_t)dst.owner * dst.inbox_cap + idx] = s_msg[pos];
+        else atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
+    }
+}
+
+// after all messages are out: tell every rank how many this sender left in its inbox
+__global__ void k_succ_counts(ShardDst dst)
+{
+    const uint32_t g = threadIdx.x;
+    if (g <= dst.g_mask) dst.inbox_count[g][dst.owner] = min(dst.out_count[g], dst.inbox_cap);
+}
+
+// the receiving side, local: succ[local slot] = successor for every message of every sender;
+// destinations in [lo, hi) only (passes over ranges that L2 can hold, like k_pred)
+__global__ void __launch_bounds__(256)
+k_succ_apply(const unsigned long long *inbox, const uint32_t *counts, uint32_t inbox_cap, uint32_t lo, uint32_t hi,
+             uint32_t *succ)
+{
+    const uint32_t sender = blockIdx.y;
+    const uint32_t n = __ldg(counts + sender);
+    const unsigned long long *src = inbox + (size_t)sender * inbox_cap;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned long long msg = __ldcs(src + i);
+        const uint32_t lv = (uint32_t)msg;
+        if (lv >= lo && lv < hi) succ[lv] = (uint32_t)(msg >> 32);
     }
 }
 
@@ -1314,6 +1415,25 @@ int check_view(const ts_shard_view *v, const char *who)
 }
 
 }  // namespace
+
+// the local half of the link exchange (called by ts_shard_rate before the rating kernel): rank `me`
+// scatters the messages its inbox holds into its succ slice
+int ts_shard_apply_links(const ts_shard_view *view, int me, int64_t n_local, int32_t slots, cudaStream_t s)
+{
+    const int G = view->n_shards;
+    const uint64_t entries = (uint64_t)n_local * (uint64_t)slots;
+    if (entries == 0) return 0;
+    // destination ranges of 16 Mi entries (64 MiB, half an L2) while that takes few passes over the inbox
+    uint64_t range = pred_range_entries();
+    if ((entries + range - 1) / range > 8) range = entries;
+    const unsigned blocks = (unsigned)std::min<int64_t>((view->inbox_cap + 1023) / 1024, 4096);
+    for (uint64_t lo = 0; lo < entries; lo += range)
+        k_succ_apply<<<dim3(blocks, (unsigned)G), 256, 0, s>>>(view->inbox[me], view->inbox_count[me], (uint32_t)view->inbox_cap,
+                                                            (uint32_t)lo, (uint32_t)std::min<uint64_t>(lo + range, entries),
+                                                            view->succ[me]);
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}
 
 extern "C" int64_t ts_shard_local_matches(int64_t n_matches, int32_t rank, int32_t n_shards)
 {
@@ -1347,10 +1467,14 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     }
     if (n_matches == 0) return 0;
     for (int g = 0; g < G; ++g)
-        if (!view->ids[g] || !view->meta[g] || !view->succ[g] || !view->rows[g] || !view->table[g]) {
+        if (!view->ids[g] || !view->meta[g] || !view->inbox[g] || !view->inbox_count[g] || !view->rows[g] || !view->table[g]) {
             ts_set_error("ts_shard_link: shard %d not mapped", g);
             return TS_E_ARG;
         }
+    if (view->inbox_cap < 1 || view->inbox_cap > 0x7FFFFFFFll) {
+        ts_set_error("ts_shard_link: inbox_cap out of range");
+        return TS_E_ARG;
+    }
     // capacity (pairs) of the workspace: two (key, val) buffers, one status word per 4096 pairs
     // (the sort's passes need 256), the digit totals
     const uint32_t np = (uint32_t)n_matches * (uint32_t)slots;
@@ -1363,6 +1487,10 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     }
     TS_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
+    // TSRATE_SHARD_TIMING=1: synchronise after every stage and print its time (diagnosis only)
+    const bool timing = getenv("TSRATE_SHARD_TIMING") && atoi(getenv("TSRATE_SHARD_TIMING"));
+    cudaEvent_t tev[4];
+    if (timing) { for (auto &e : tev) cudaEventCreate(&e); cudaEventRecord(tev[0], s); }
     Workspace w = carve_link((char *)workspace, (uint32_t)cap);
     uint32_t *ticket = w.totals + kMaxPasses * 256, *n_dev = ticket + 8;
     int shift = 0;
@@ -1380,6 +1508,7 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     TS_CUDA(cudaMemsetAsync(w.hist, 0, (size_t)compact_tiles * 4, s));
     k_owned_compact<<<(unsigned)compact_tiles, kSortBlock, 0, s>>>(src, np, (uint32_t)cap, w.hist, ticket, w.keys[0], w.vals[0],
                                                                  n_dev, ctx->d_ctrl);
+    if (timing) cudaEventRecord(tev[1], s);
     const int64_t local_players = (n_players - rank + G - 1) / G;
     KeySrc ks;
     ks.keys = w.keys[0];
@@ -1393,22 +1522,35 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     int buf = radix_sort(ks, (uint32_t)cap, bits_for((uint64_t)(local_players > 0 ? local_players - 1 : 0)), w, s,
                          ctx->sm_count, n_dev);
     if (buf < 0) return buf;
+    if (timing) cudaEventRecord(tev[2], s);
     ShardDst dst;
-    for (int g = 0; g < TS_SHARD_MAX; ++g) { dst.succ[g] = g < G ? view->succ[g] : nullptr; dst.rows[g] = g < G ? view->rows[g] : nullptr; }
+    for (int g = 0; g < TS_SHARD_MAX; ++g) {
+        dst.inbox[g] = g < G ? view->inbox[g] : nullptr;
+        dst.inbox_count[g] = g < G ? view->inbox_count[g] : nullptr;
+        dst.rows[g] = g < G ? view->rows[g] : nullptr;
+    }
     dst.table_own = view->table[rank];
+    dst.out_count = ticket + 16;                 // zeroed with the totals above
+    dst.inbox_cap = (uint32_t)view->inbox_cap;
     dst.g_mask = src.g_mask;
     dst.g_shift = src.g_shift;
     dst.owner = src.owner;
     dst.slots = src.slots;
     dst.slots_magic = src.slots_magic;
     dst.seq_base = (uint32_t)seq_base;
-    // destination ranges: 16 Mi succ entries per GPU and pass (64 MiB, half an L2)
-    const uint64_t range_m = (uint64_t)pred_range_entries() * (uint64_t)G / (uint64_t)slots;
-    uint64_t step = ((uint64_t)n_matches + range_m - 1) / range_m > 8 ? (uint64_t)n_matches : range_m;
-    for (uint64_t lo = 0; lo < (uint64_t)n_matches; lo += step) {
-        const uint32_t hi = (uint32_t)std::min<uint64_t>(lo + step, (uint64_t)n_matches);
-        k_succ<<<(unsigned)((cap + 255) / 256), 256, 0, s>>>(w.keys[buf], w.vals[buf], n_dev, dst, (uint32_t)lo, hi, ctx->d_ctrl);
-    }
+    k_succ_route<<<(unsigned)((cap + kRouteTile - 1) / kRouteTile), 256, 0, s>>>(w.keys[buf], w.vals[buf], n_dev, dst, ctx->d_ctrl);
+    k_succ_counts<<<1, 32, 0, s>>>(dst);
     TS_CUDA(cudaGetLastError());
+    if (timing) {
+        cudaEventRecord(tev[3], s);
+        cudaEventSynchronize(tev[3]);
+        float ms[3];
+        for (int i = 0; i < 3; ++i) cudaEventElapsedTime(&ms[i], tev[i], tev[i + 1]);
+        uint32_t owned = 0;
+        cudaMemcpy(&owned, n_dev, 4, cudaMemcpyDeviceToHost);
+        fprintf(stderr, "ts_shard_link rank %d/%d: compact %.3f ms, sort %.3f ms, route %.3f ms (%u owned of %u slots, cap %lld)\n",
+                rank, G, ms[0], ms[1], ms[2], owned, np, (long long)cap);
+        for (auto &e : tev) cudaEventDestroy(e);
+    }
     return 0;
 }

@@ -39,6 +39,7 @@ struct PushArgs {
     uint32_t n_players;
     uint32_t seq_base;
     uint32_t sleep_ns, max_spins;
+    uint32_t prefetch;
     ts_outputs out;
     unsigned long long *ctrl;
 };
@@ -58,7 +59,7 @@ __device__ __forceinline__ uint32_t local_matches(uint32_t n, uint32_t r, uint32
     return (mine - 1u) * 32u + (last_is_mine ? n - (blocks - 1u) * 32u : 32u);
 }
 
-template <int P, int L, bool EMU>
+template <int P, int L, bool EMU, bool HOIST>
 __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
 {
     constexpr int W = 32 / L;
@@ -88,17 +89,22 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
     const uint32_t stride = blocks_of_rank * kWarps;
     const uint32_t first_tile = (threadIdx.x >> 5) * blocks_of_rank + block_of_rank;
 
-    int pf = 0;
-    if (first_tile < n_tiles)
-        stage_warp_tile<P, W>(stage, pf, ids, succ, meta_arr, first_tile * W, min((uint32_t)W, n_local - first_tile * W), wl);
+    const unsigned long long pol = stream_policy();
+    auto stage_tile = [&](int b, uint32_t t) {
+        if (t < n_tiles) stage_warp_tile<P, W>(stage, b, ids, succ, meta_arr, t * W, min((uint32_t)W, n_local - t * W), wl, pol);
+    };
+    int cur_buf = 0;
+    stage_tile(0, first_tile);
+    constexpr int D = WarpStage<P, W>::kDepth;
+    if (D == 3) stage_tile(1, first_tile + stride);
     for (uint32_t tile = first_tile; tile < n_tiles; tile += stride) {
-        cp_async_wait_all();
+        cp_async_wait_all();                    // this tile's records and the next one's (issued a whole tile ago)
         __syncwarp();
-        const int cur = pf;
-        pf ^= 1;
-        if (tile + stride < n_tiles)
-            stage_warp_tile<P, W>(stage, pf, ids, succ, meta_arr, (tile + stride) * W,
-                                  min((uint32_t)W, n_local - (tile + stride) * W), wl);
+        const int cur = cur_buf, nxt = cur == D - 1 ? 0 : cur + 1;
+        cur_buf = nxt;
+        stage_tile((cur + D - 1) % D, tile + (D - 1) * stride);
+        if (D == 3 && a.prefetch && tile + stride < n_tiles)    // next tile's mailbox rows on their way into L2
+            prefetch_tile_rows<P, W>(stage, nxt, rows, 4u, min((uint32_t)W, n_local - (tile + stride) * W), a.n_players, wl);
         const uint32_t base = tile * W;
         const uint32_t cnt = min((uint32_t)W, n_local - base);
         const uint32_t lm = base + grp;                                  // local index on this rank
@@ -118,7 +124,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
         const int first = rank1 < rank0 ? 1 : 0;
         const bool is_draw = rank0 == rank1;
 
-        uint32_t pid[SPL], next[SPL];
+        uint32_t pid[SPL], next[SPL], want[SPL];
         bool used[SPL], have[SPL];
         double q_mu[SPL], q_sg[SPL];
         bool bad_id = false;
@@ -129,6 +135,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
             used[k] = pid[k] != TS_EMPTY_SLOT;
             if (used[k] && pid[k] >= a.n_players) { used[k] = false; bad_id = true; }   // corrupt id: nobody links it
             next[k] = used[k] ? stage.link[cur][grp * P + s] : TS_NONE;
+            want[k] = tag;
             have[k] = !used[k];
             q_mu[k] = 0.0; q_sg[k] = 1.0;
         }
@@ -138,21 +145,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
         // GPU's own mailbox (system scope: the writer may be another GPU)
         while (!__all_sync(0xFFFFFFFFu, done)) {
             bool ready = false;
-            if (!done) {
-                ready = true;
-#pragma unroll
-                for (int k = 0; k < SPL; ++k) {
-                    if (have[k]) continue;
-                    unsigned long long w[4];
-                    ld_row<true>(rows + (size_t)pid[k] * 4, w);
-                    if (row_has_version(w, tag)) {
-                        have[k] = true;
-                        q_mu[k] = row_mu(w);
-                        q_sg[k] = row_sigma(w);
-                    }
-                    ready &= have[k];
-                }
-            }
+            if (!done) ready = poll_rows<SPL, HOIST, true>(rows, pid, want, have, q_mu, q_sg);
             const uint32_t complete = complete_groups<L>(ready);
             if (complete == 0u) {
                 if ((++spins & 0x3FFu) == 0u) {
@@ -183,8 +176,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
                         // the player's last match of the window: back to the owner's table shard
                         st_pair_sys(a.view.table[pid[k] & a.g_mask] + (size_t)(pid[k] >> a.g_shift) * 2, mu2[k], sg2[k]);
                     }
-                    if (ok && a.out.out_queue)
-                        __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + (size_t)om * P + s, make_double2(mu2[k], sg2[k]));
+                    if (ok && a.out.out_queue) st_pair_stream(a.out.out_queue + ((size_t)om * P + s) * 2, mu2[k], sg2[k], pol);
                 }
             }
             if (go) {
@@ -200,9 +192,10 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
 }
 
 template <int P, int L>
-int launch_push(ts_ctx *ctx, const PushArgs &args, bool emulate, cudaStream_t stream)
+int launch_push(ts_ctx *ctx, const PushArgs &args, bool emulate, bool hoist, cudaStream_t stream)
 {
-    void *fn = emulate ? (void *)k_rate_push<P, L, true> : (void *)k_rate_push<P, L, false>;
+    void *fn = emulate ? (hoist ? (void *)k_rate_push<P, L, true, true> : (void *)k_rate_push<P, L, true, false>)
+                       : (hoist ? (void *)k_rate_push<P, L, false, true> : (void *)k_rate_push<P, L, false, false>);
     int per_sm = 0;
     TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kBlock, 0));
     if (per_sm < 1) { ts_set_error("sharded stream kernel does not fit on an SM"); return TS_E_CUDA; }
@@ -218,12 +211,12 @@ int launch_push(ts_ctx *ctx, const PushArgs &args, bool emulate, cudaStream_t st
 }
 
 template <int P>
-int dispatch_push(ts_ctx *ctx, const PushArgs &a, int lanes, bool emulate, cudaStream_t s)
+int dispatch_push(ts_ctx *ctx, const PushArgs &a, int lanes, bool emulate, bool hoist, cudaStream_t s)
 {
     switch (lanes) {
-    case 2: return launch_push<P, 2>(ctx, a, emulate, s);
-    case 4: return launch_push<P, 4>(ctx, a, emulate, s);
-    case 8: return launch_push<P, 8>(ctx, a, emulate, s);
+    case 2: return launch_push<P, 2>(ctx, a, emulate, hoist, s);
+    case 4: return launch_push<P, 4>(ctx, a, emulate, hoist, s);
+    case 8: return launch_push<P, 8>(ctx, a, emulate, hoist, s);
     }
     ts_set_error("ts_shard_rate: lanes_per_match must be 0, 2, 4 or 8 (got %d)", lanes);
     return TS_E_ARG;
@@ -240,6 +233,8 @@ int check_shards(const ts_shard_view *v, const char *who)
 }
 
 }  // namespace
+
+int ts_shard_apply_links(const ts_shard_view *view, int me, int64_t n_local, int32_t slots, cudaStream_t s);   // sched.cu
 
 extern "C" int ts_shard_alloc(int device, int64_t bytes, void **ptr, void *handle64)
 {
@@ -336,5 +331,17 @@ extern "C" int ts_shard_rate(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     a.ctrl = ctx->d_ctrl;
     const int lanes = lanes_per_match ? lanes_per_match : (slots == 6 ? 2 : 8);   // measured: DESIGN.md 3.2
     cudaStream_t s = (cudaStream_t)stream;
-    return slots == 6 ? dispatch_push<6>(ctx, a, lanes, emulate_all != 0, s) : dispatch_push<10>(ctx, a, lanes, emulate_all != 0, s);
+    // the links every sender left in the inbox(es) go to their slots first: local work, same stream
+    for (int g = 0; g < G; ++g) {
+        if (!(emulate_all || g == view->rank)) continue;
+        if (!view->inbox[g] || !view->inbox_count[g] || view->inbox_cap < 1) {
+            ts_set_error("ts_shard_rate: inbox of shard %d not mapped", g);
+            return TS_E_ARG;
+        }
+        if (int rc = ts_shard_apply_links(view, g, ts_shard_local_matches(n_matches, g, G), slots, s)) return rc;
+    }
+    const bool hoist = stream_hoist_mode() != 0;
+    a.prefetch = stream_prefetch_mode() != 0 ? 1u : 0u;
+    return slots == 6 ? dispatch_push<6>(ctx, a, lanes, emulate_all != 0, hoist, s)
+                      : dispatch_push<10>(ctx, a, lanes, emulate_all != 0, hoist, s);
 }

@@ -1,6 +1,8 @@
 // The scheduler of sched.cu for callers that must not allocate device memory.
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 // ---------------------------------------------------------------------------
@@ -44,6 +46,7 @@ struct StaticDevice {
     int sm_count;
 };
 StaticDevice g_static_dev[64];
+std::mutex g_static_lock;      // first calls from two host threads fill the cache one after the other
 
 // once per device, with that device current
 int static_setup(int device, StaticDevice **out)
@@ -53,6 +56,7 @@ int static_setup(int device, StaticDevice **out)
         return TS_E_ARG;
     }
     StaticDevice &d = g_static_dev[device];
+    std::lock_guard<std::mutex> guard(g_static_lock);
     if (!d.ready) {
         TS_CUDA(cudaSetDevice(device));
         void *ptr = nullptr;

@@ -52,21 +52,16 @@ struct StreamArgs {
     uint32_t seq_base;            // stream-wide number of the first match of this window
     uint32_t sleep_ns;            // back-off between polls when no group of the warp is complete
     uint32_t max_spins;           // watchdog: fruitless polls before a warp declares the stream stalled
+    uint32_t prefetch;            // 1: the rows of the next tile's players are prefetched into L2
     ts_outputs out;
     unsigned long long *ctrl;
 };
-
-// 1: the loads of all missing slots of a poll are issued before any is checked.  With the rows in
-// the local L2, checking slot by slot measured slightly faster (config 2 rate 2.19 vs 2.25 ms).
-#ifndef TS_STREAM_HOIST
-#define TS_STREAM_HOIST 0
-#endif
 
 // Warps are the unit of work: warp w of the grid takes the tiles w, w + n_warps,
 // ... of W consecutive matches, in increasing order, and never synchronises
 // with the other warps of its block -- a warp that has to wait for a dependency
 // holds up nothing but its own W matches.
-template <int P, int L>
+template <int P, int L, bool HOIST>
 __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(const StreamArgs a)
 {
     constexpr int W = 32 / L;
@@ -89,22 +84,26 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
     uint32_t rated_mask = 0;
 #pragma unroll
     for (int i = 0; i < 6; ++i) rated_mask |= a.modes.col[i] >= 0 ? (1u << i) : 0u;
+    const unsigned long long pol = stream_policy();
     const uint32_t n_tiles = (a.n_matches + W - 1) / W;
     const uint32_t stride = gridDim.x * kWarps;
     // neighbouring tiles go to different SMs
     const uint32_t first_tile = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
+    auto stage_tile = [&](int b, uint32_t t) {
+        if (t < n_tiles) stage_warp_tile<P, W>(stage, b, a.ids, a.pred, a.meta, t * W, min((uint32_t)W, a.n_matches - t * W), wl, pol);
+    };
 
-    int pf = 0;
-    if (first_tile < n_tiles)
-        stage_warp_tile<P, W>(stage, pf, a.ids, a.pred, a.meta, first_tile * W, min((uint32_t)W, a.n_matches - first_tile * W), wl);
+    int cur = 0;
+    stage_tile(0, first_tile);
+    constexpr int D = WarpStage<P, W>::kDepth;
+    if (D == 3) stage_tile(1, first_tile + stride);
     for (uint32_t tile = first_tile; tile < n_tiles; tile += stride) {
-        cp_async_wait_all();
+        cp_async_wait_all();                    // this tile's records and the next one's (issued a whole tile ago)
         __syncwarp();
-        const int cur = pf;
-        pf ^= 1;
-        if (tile + stride < n_tiles)
-            stage_warp_tile<P, W>(stage, pf, a.ids, a.pred, a.meta, (tile + stride) * W,
-                                  min((uint32_t)W, a.n_matches - (tile + stride) * W), wl);
+        const int nxt = cur == D - 1 ? 0 : cur + 1;
+        stage_tile((cur + D - 1) % D, tile + (D - 1) * stride);
+        if (D == 3 && a.prefetch && tile + stride < n_tiles)    // next tile's rows on their way into L2 while this one waits and computes
+            prefetch_tile_rows<P, W>(stage, nxt, a.vt, 4u, min((uint32_t)W, a.n_matches - (tile + stride) * W), a.n_players, wl);
         const uint32_t base = tile * W;
         const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
         const uint32_t m = base + grp;
@@ -135,6 +134,7 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
             have[k] = !used[k];
             q_mu[k] = 0.0; q_sg[k] = 1.0;
         }
+        cur = nxt;
         bool done = !live;
         // Wait loop, the same for all lanes of the warp.  Each iteration polls the rows still
         // missing; then ONE ballot tells every lane which match groups are complete, and if
@@ -150,37 +150,7 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
         uint32_t spins = 0;
         while (!__all_sync(0xFFFFFFFFu, done)) {
             bool ready = false;
-            if (!done) {
-                ready = true;
-                if constexpr (TS_STREAM_HOIST) {
-                    unsigned long long w[SPL][4];
-#pragma unroll
-                    for (int k = 0; k < SPL; ++k)
-                        if (!have[k]) ld_row(a.vt + (size_t)pid[k] * 4, w[k]);
-#pragma unroll
-                    for (int k = 0; k < SPL; ++k) {
-                        if (!have[k] && row_has_version(w[k], want[k])) {
-                            have[k] = true;
-                            q_mu[k] = row_mu(w[k]);
-                            q_sg[k] = row_sigma(w[k]);
-                        }
-                        ready &= have[k];
-                    }
-                } else {
-#pragma unroll
-                    for (int k = 0; k < SPL; ++k) {
-                        if (have[k]) continue;
-                        unsigned long long w[4];
-                        ld_row(a.vt + (size_t)pid[k] * 4, w);
-                        if (row_has_version(w, want[k])) {
-                            have[k] = true;
-                            q_mu[k] = row_mu(w);
-                            q_sg[k] = row_sigma(w);
-                        }
-                        ready &= have[k];
-                    }
-                }
-            }
+            if (!done) ready = poll_rows<SPL, HOIST, false>(a.vt, pid, want, have, q_mu, q_sg);
             const uint32_t complete = complete_groups<L>(ready);
             if (complete == 0u) {
                 if ((++spins & 0x3FFu) == 0u) {
@@ -206,8 +176,7 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
                 const int s = lane + k * L;
                 if (go && used[k]) {
                     st_row(a.vt + (size_t)pid[k] * 4, mu2[k], sg2[k], a.seq_base + m);   // first: successors are waiting
-                    if (ok && a.out.out_queue)
-                        __stcg(reinterpret_cast<double2 *>(a.out.out_queue) + (size_t)m * P + s, make_double2(mu2[k], sg2[k]));
+                    if (ok && a.out.out_queue) st_pair_stream(a.out.out_queue + ((size_t)m * P + s) * 2, mu2[k], sg2[k], pol);
                 }
             }
             if (go) {
@@ -240,29 +209,30 @@ __global__ void __launch_bounds__(256) k_vt_store(const unsigned long long *vt, 
 }
 
 template <int P, int L>
-int launch_stream(ts_ctx *ctx, const StreamArgs &args, cudaStream_t stream)
+int launch_stream(ts_ctx *ctx, const StreamArgs &args, bool hoist, cudaStream_t stream)
 {
+    void *fn = hoist ? (void *)k_rate_stream<P, L, true> : (void *)k_rate_stream<P, L, false>;
     int per_sm = 0;
-    TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rate_stream<P, L>, kBlock, 0));
+    TS_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, kBlock, 0));
     if (per_sm < 1) { ts_set_error("stream kernel does not fit on an SM"); return TS_E_CUDA; }
     per_sm = per_sm < stream_blocks_per_sm_cap() ? per_sm : stream_blocks_per_sm_cap();
     dim3 grid(ctx->sm_count * per_sm), block(kBlock);
     void *kargs[] = {(void *)&args};
     // cooperative launch only for its guarantee that the whole grid is resident
-    TS_CUDA(cudaLaunchCooperativeKernel((void *)k_rate_stream<P, L>, grid, block, kargs, 0, stream));
+    TS_CUDA(cudaLaunchCooperativeKernel(fn, grid, block, kargs, 0, stream));
     return 0;
 }
 
 template <int P>
-int dispatch_l(ts_ctx *ctx, const StreamArgs &a, int lanes, cudaStream_t s)
+int dispatch_l(ts_ctx *ctx, const StreamArgs &a, int lanes, bool hoist, cudaStream_t s)
 {
     switch (lanes) {
-    case 1: return launch_stream<P, 1>(ctx, a, s);
-    case 2: return launch_stream<P, 2>(ctx, a, s);
-    case 4: return launch_stream<P, 4>(ctx, a, s);
-    case 8: return launch_stream<P, 8>(ctx, a, s);
-    case 16: return launch_stream<P, 16>(ctx, a, s);
-    case 32: return launch_stream<P, 32>(ctx, a, s);
+    case 1: return launch_stream<P, 1>(ctx, a, hoist, s);
+    case 2: return launch_stream<P, 2>(ctx, a, hoist, s);
+    case 4: return launch_stream<P, 4>(ctx, a, hoist, s);
+    case 8: return launch_stream<P, 8>(ctx, a, hoist, s);
+    case 16: return launch_stream<P, 16>(ctx, a, hoist, s);
+    case 32: return launch_stream<P, 32>(ctx, a, hoist, s);
     }
     ts_set_error("lanes_per_match must be 0,1,2,4,8,16 or 32 (got %d)", lanes);
     return TS_E_ARG;
@@ -354,6 +324,10 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
         ts_set_error("ts_rate_stream: n_matches outside [0, 2^32 - 1)");
         return TS_E_ARG;
     }
+    if (((uintptr_t)workspace & 31u) != 0u) {
+        ts_set_error("ts_rate_stream: workspace must be 32-byte aligned (rows are read and written as 256-bit words)");
+        return TS_E_ARG;
+    }
     if (workspace_bytes < ts_rate_stream_table_workspace_bytes(table)) {
         ts_set_error("ts_rate_stream: workspace too small (%lld < %lld bytes)", (long long)workspace_bytes,
                      (long long)ts_rate_stream_table_workspace_bytes(table));
@@ -386,8 +360,10 @@ extern "C" int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t
     const int64_t u = table->n_players;
     if (flags & TS_STREAM_LOAD) k_vt_load<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(table->data, a.vt, u);
     int lanes = lanes_per_match ? lanes_per_match : (slots == 6 ? 2 : 8);   // measured: DESIGN.md 3.2
+    const bool hoist = stream_hoist_mode() != 0;
+    a.prefetch = stream_prefetch_mode() != 0 ? 1u : 0u;
     int rc = 0;
-    if (n_matches > 0) rc = slots == 6 ? dispatch_l<6>(ctx, a, lanes, s) : dispatch_l<10>(ctx, a, lanes, s);
+    if (n_matches > 0) rc = slots == 6 ? dispatch_l<6>(ctx, a, lanes, hoist, s) : dispatch_l<10>(ctx, a, lanes, hoist, s);
     if (rc) return rc;
     if (flags & TS_STREAM_STORE) k_vt_store<<<(unsigned)((u + 255) / 256), 256, 0, s>>>(a.vt, table->data, u);
     TS_CUDA(cudaGetLastError());

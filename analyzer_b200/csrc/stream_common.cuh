@@ -10,17 +10,20 @@
 
 namespace tsstream {
 
-// SYS = rows may live in a peer GPU's memory: system scope (peer accesses bypass the local L2)
+// A row is 32 bytes and 32-byte aligned: one 256-bit access (LDG.256 / STG.256, new with sm_100)
+// instead of two 128-bit ones -- half the L2 requests per poll, and half the NVLink packets when
+// the row goes to another GPU.  The elements of a vector access are performed as separate 8-byte
+// accesses in no particular order, which is all the protocol needs: every word validates itself.
+// SYS = the row may live in, or be written from, another GPU: system scope.
 template <bool SYS = false>
 __device__ __forceinline__ void ld_row(const unsigned long long *row, unsigned long long (&w)[4])
 {
-    if (SYS) {
-        asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(row) : "memory");
-        asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(row + 2) : "memory");
-    } else {
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[0]), "=l"(w[1]) : "l"(row) : "memory");
-        asm volatile("ld.relaxed.gpu.global.v2.u64 {%0, %1}, [%2];" : "=l"(w[2]), "=l"(w[3]) : "l"(row + 2) : "memory");
-    }
+    if (SYS)
+        asm volatile("ld.relaxed.sys.global.v4.u64 {%0, %1, %2, %3}, [%4];"
+                     : "=l"(w[0]), "=l"(w[1]), "=l"(w[2]), "=l"(w[3]) : "l"(row) : "memory");
+    else
+        asm volatile("ld.relaxed.gpu.global.v4.u64 {%0, %1, %2, %3}, [%4];"
+                     : "=l"(w[0]), "=l"(w[1]), "=l"(w[2]), "=l"(w[3]) : "l"(row) : "memory");
 }
 template <bool SYS = false>
 __device__ __forceinline__ void st_row(unsigned long long *row, double mu, double sigma, uint32_t ver)
@@ -30,13 +33,10 @@ __device__ __forceinline__ void st_row(unsigned long long *row, double mu, doubl
     const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
     unsigned long long w0 = (m & 0xFFFFFFFFull) | v, w1 = (m >> 32) | v;
     unsigned long long w2 = (s & 0xFFFFFFFFull) | v, w3 = (s >> 32) | v;
-    if (SYS) {
-        asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"(w0), "l"(w1) : "memory");
-        asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"(w2), "l"(w3) : "memory");
-    } else {
-        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row), "l"(w0), "l"(w1) : "memory");
-        asm volatile("st.relaxed.gpu.global.v2.u64 [%0], {%1, %2};" ::"l"(row + 2), "l"(w2), "l"(w3) : "memory");
-    }
+    if (SYS)
+        asm volatile("st.relaxed.sys.global.v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(row), "l"(w0), "l"(w1), "l"(w2), "l"(w3) : "memory");
+    else
+        asm volatile("st.relaxed.gpu.global.v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(row), "l"(w0), "l"(w1), "l"(w2), "l"(w3) : "memory");
 }
 __device__ __forceinline__ bool row_has_version(const unsigned long long (&w)[4], uint32_t ver)
 {
@@ -52,16 +52,30 @@ __device__ __forceinline__ double row_sigma(const unsigned long long (&w)[4])
     return __longlong_as_double((long long)((w[2] & 0xFFFFFFFFull) | (w[3] << 32)));
 }
 
-__device__ __forceinline__ void cp_async_8(void *smem, const void *gmem)
+// Match records (ids, links, meta) and the per-match outputs are touched once: they travel with
+// an L2 evict-first policy so that, on ladders whose rows do not fit L2, the 50-odd bytes a match
+// streams through do not push the rows out that its successors will poll.
+__device__ __forceinline__ unsigned long long stream_policy()
+{
+    unsigned long long pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void cp_async_8(void *smem, const void *gmem, unsigned long long pol)
 {
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmem) : "memory");
+    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 8, %2;" ::"r"(s), "l"(gmem), "l"(pol) : "memory");
 }
-__device__ __forceinline__ void cp_async_4(void *smem, const void *gmem)
+__device__ __forceinline__ void cp_async_4(void *smem, const void *gmem, unsigned long long pol)
 {
     unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmem) : "memory");
+    asm volatile("cp.async.ca.shared.global.L2::cache_hint [%0], [%1], 4, %2;" ::"r"(s), "l"(gmem), "l"(pol) : "memory");
 }
+__device__ __forceinline__ void st_pair_stream(double *p, double mu, double sigma, unsigned long long pol)
+{
+    asm volatile("st.global.L2::cache_hint.v2.f64 [%0], {%1, %2}, %3;" ::"l"(p), "d"(mu), "d"(sigma), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void prefetch_row_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // bit g * L of a lane mask: the first lane of every group of L lanes
@@ -98,24 +112,83 @@ __device__ __forceinline__ uint32_t group_sum_u32(uint32_t x)
 
 
 // per-warp staging buffers: a warp owns W = 32 / L consecutive matches at a time; `link` holds
-// pred (single GPU: the version to wait for) or succ (sharded ladder: where the new row goes)
+// pred (single GPU: the version to wait for) or succ (sharded ladder: where the new row goes).
+// Three buffers: the tile being rated, the next one (its records are there one tile early, so
+// that its players' rows can be prefetched into L2 while this tile waits and computes), and the
+// one after that, in flight.
+// (Two buffers, and no prefetch, where three would not fit the 48 KB of static shared memory:
+// one lane per 5v5 match.)
 template <int P, int W>
 struct WarpStage {
-    uint32_t ids[2][W * P];
-    uint32_t link[2][W * P];
-    uint32_t meta[2][W];
+    static constexpr int kDepth = ((2 * W * P + W) * 4 * 3 * 8 <= 48 * 1024) ? 3 : 2;
+    uint32_t ids[kDepth][W * P];
+    uint32_t link[kDepth][W * P];
+    uint32_t meta[kDepth][W];
 };
 
 template <int P, int W>
 __device__ __forceinline__ void stage_warp_tile(WarpStage<P, W> &st, int b, const uint32_t *ids, const uint32_t *link,
-                                                const uint32_t *meta, uint32_t base, uint32_t cnt, int wl)
+                                                const uint32_t *meta, uint32_t base, uint32_t cnt, int wl,
+                                                unsigned long long pol)
 {
     const uint32_t *src_i = ids + (size_t)base * P, *src_p = link + (size_t)base * P;
     for (uint32_t i = wl; i < cnt * (P / 2); i += 32) {
-        cp_async_8(&st.ids[b][2 * i], src_i + 2 * i);
-        cp_async_8(&st.link[b][2 * i], src_p + 2 * i);
+        cp_async_8(&st.ids[b][2 * i], src_i + 2 * i, pol);
+        cp_async_8(&st.link[b][2 * i], src_p + 2 * i, pol);
     }
-    for (uint32_t i = wl; i < cnt; i += 32) cp_async_4(&st.meta[b][i], meta + base + i);
+    for (uint32_t i = wl; i < cnt; i += 32) cp_async_4(&st.meta[b][i], meta + base + i, pol);
+}
+
+// rows of the players of a staged tile -> L2 (row_words 64-bit words per player)
+template <int P, int W>
+__device__ __forceinline__ void prefetch_tile_rows(const WarpStage<P, W> &st, int b, const unsigned long long *rows,
+                                                   uint32_t row_words, uint32_t cnt, uint32_t n_players, int wl)
+{
+    for (uint32_t i = wl; i < cnt * P; i += 32) {
+        const uint32_t pid = st.ids[b][i];
+        if (pid < n_players) prefetch_row_l2(rows + (size_t)pid * row_words);
+    }
+}
+
+// One poll of the rows a lane still misses (rows of 4 words per player at `rows`): a row is taken
+// when all four of its words carry the version the lane waits for.  HOIST: the loads of all
+// missing rows are issued before any is checked -- as many DRAM / L2 round trips in flight as
+// the lane has slots; otherwise row by row (measured faster when every row sits in L2).
+template <int SPL, bool HOIST, bool SYS>
+__device__ __forceinline__ bool poll_rows(const unsigned long long *rows, const uint32_t (&pid)[SPL],
+                                          const uint32_t (&want)[SPL], bool (&have)[SPL], double (&q_mu)[SPL],
+                                          double (&q_sg)[SPL])
+{
+    bool ready = true;
+    if constexpr (HOIST) {
+        unsigned long long w[SPL][4];
+#pragma unroll
+        for (int k = 0; k < SPL; ++k)
+            if (!have[k]) ld_row<SYS>(rows + (size_t)pid[k] * 4, w[k]);
+#pragma unroll
+        for (int k = 0; k < SPL; ++k) {
+            if (!have[k] && row_has_version(w[k], want[k])) {
+                have[k] = true;
+                q_mu[k] = row_mu(w[k]);
+                q_sg[k] = row_sigma(w[k]);
+            }
+            ready &= have[k];
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < SPL; ++k) {
+            if (have[k]) continue;
+            unsigned long long w[4];
+            ld_row<SYS>(rows + (size_t)pid[k] * 4, w);
+            if (row_has_version(w, want[k])) {
+                have[k] = true;
+                q_mu[k] = row_mu(w);
+                q_sg[k] = row_sigma(w);
+            }
+            ready &= have[k];
+        }
+    }
+    return ready;
 }
 
 // What a pass needs of the environment (rater.py:30-37), in registers.
@@ -217,6 +290,25 @@ inline int stream_sleep_ns()
         if (ns < 0) ns = 0;
     }
     return ns;
+}
+
+// TSRATE_STREAM_PREFETCH=1: the rows of the next tile's players are prefetched into L2 one tile early.
+// Off by default -- measured (scripts/ab_stream.py): where the rows do not fit L2 the kernel is bound by
+// DRAM accesses and a prefetched row is often evicted again before it is polled (125M 3v3 matches over
+// 12.5M players: rate 29.7 -> 36.9 ms); it gains 2 % on the deep Zipf chains of config 3 and nothing
+// when the rows sit in L2.
+inline int stream_prefetch_mode()
+{
+    const char *e = getenv("TSRATE_STREAM_PREFETCH");
+    return e ? atoi(e) : 0;
+}
+// TSRATE_STREAM_HOIST=0: a poll checks row by row instead of issuing the loads of all its missing rows
+// first.  With one 256-bit load per row the hoisted form is the faster one everywhere measured
+// (config 2: 2.20 -> 2.13 ms; 125M / 12.5M: 29.7 -> 29.2 ms).
+inline int stream_hoist_mode()
+{
+    const char *e = getenv("TSRATE_STREAM_HOIST");
+    return e ? atoi(e) : 1;
 }
 
 inline int stream_max_spins()

@@ -58,6 +58,7 @@ struct PairArgs {
     uint32_t seq_base;
     uint32_t sleep_ns;
     uint32_t max_spins;
+    uint32_t prefetch;            // 1: the rows of the next tile's players are prefetched into L2
     ts_outputs out;
     unsigned long long *ctrl;
 };
@@ -98,17 +99,23 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
     const uint32_t stride = gridDim.x * kWarps;
     const uint32_t first_tile = (threadIdx.x >> 5) * gridDim.x + blockIdx.x;
 
-    int pf = 0;
-    if (first_tile < n_tiles)
-        stage_warp_tile<P, W>(stage, pf, a.ids, a.pred, a.meta, first_tile * W, min((uint32_t)W, a.n_matches - first_tile * W), wl);
+    const unsigned long long pol = stream_policy();
+    auto stage_tile = [&](int b, uint32_t t) {
+        if (t < n_tiles) stage_warp_tile<P, W>(stage, b, a.ids, a.pred, a.meta, t * W, min((uint32_t)W, a.n_matches - t * W), wl, pol);
+    };
+    int cur_buf = 0;
+    stage_tile(0, first_tile);
+    constexpr int D = WarpStage<P, W>::kDepth;
+    if (D == 3) stage_tile(1, first_tile + stride);
     for (uint32_t tile = first_tile; tile < n_tiles; tile += stride) {
-        cp_async_wait_all();
+        cp_async_wait_all();                    // this tile's records and the next one's (issued a whole tile ago)
         __syncwarp();
-        const int cur = pf;
-        pf ^= 1;
-        if (tile + stride < n_tiles)
-            stage_warp_tile<P, W>(stage, pf, a.ids, a.pred, a.meta, (tile + stride) * W,
-                                  min((uint32_t)W, a.n_matches - (tile + stride) * W), wl);
+        const int cur = cur_buf, nxt = cur == D - 1 ? 0 : cur + 1;
+        cur_buf = nxt;
+        stage_tile((cur + D - 1) % D, tile + (D - 1) * stride);
+        if (D == 3 && a.prefetch && tile + stride < n_tiles)    // next tile's rows on their way into L2 (the shared pair's sector;
+            prefetch_tile_rows<P, W>(stage, nxt, a.vt, MULTI ? a.row_words : 8u,                   // the queue pair follows it)
+                                     min((uint32_t)W, a.n_matches - (tile + stride) * W), a.n_players, wl);
         const uint32_t base = tile * W;
         const uint32_t cnt = min((uint32_t)W, a.n_matches - base);
         const uint32_t m = base + grp;
@@ -436,6 +443,7 @@ void fill_args(PairArgs &a, ts_ctx *ctx, const ts_table *table, const uint32_t *
     a.seq_base = (uint32_t)seq_base;
     a.sleep_ns = stream_sleep_ns();
     a.max_spins = stream_max_spins();
+    a.prefetch = stream_prefetch_mode() != 0 ? 1u : 0u;
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;

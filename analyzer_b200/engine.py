@@ -126,6 +126,43 @@ class PlayerTable(object):
         return t
 
 
+class PackedIds(object):
+    """The id column of a batch at the width it needs: ids [N, P] as a little-endian bit
+    stream of `bits` bits each (all ones = empty slot), what ts_unpack_ids widens on the
+    device.  `packed` is a uint8 numpy array or (pinned) torch tensor."""
+
+    def __init__(self, packed, bits, n_matches, slots):
+        self.packed, self.bits, self.shape = packed, int(bits), (int(n_matches), int(slots))
+
+    @property
+    def nbytes(self):
+        return int(self.packed.numel() if isinstance(self.packed, torch.Tensor) else self.packed.size)
+
+
+def id_bits(n_players):
+    """Bits per packed id: ids 0 .. n_players - 1 and the all-ones value for an empty slot."""
+    return max(1, int(n_players).bit_length())
+
+
+def pack_ids(ids, n_players, pin=False):
+    """Host-side packing of a uint32 [N, P] id column (EMPTY_SLOT allowed) for rate_batch."""
+    ids = np.ascontiguousarray(ids).view(np.uint32)
+    n, p = ids.shape
+    bits = id_bits(n_players)
+    flat = ids.reshape(-1)
+    out = np.empty((flat.size * bits + 7) // 8, dtype=np.uint8)
+    step = 1 << 22                                   # ids per piece: a multiple of 8, so pieces end on byte boundaries
+    for lo in range(0, flat.size, step):
+        x = flat[lo:lo + step].copy()
+        x[x == L.EMPTY_SLOT] = (1 << bits) - 1
+        b = np.unpackbits(x.view(np.uint8).reshape(-1, 4), axis=1, bitorder="little")[:, :bits]
+        piece = np.packbits(b.reshape(-1), bitorder="little")
+        o = lo * bits // 8
+        out[o:o + piece.size] = piece
+    packed = torch.from_numpy(out)
+    return PackedIds(packed.pin_memory() if pin else packed, bits, n, p)
+
+
 class Schedule(object):
     """Result of Rater.schedule: device tensors in tsrate.h's terms."""
 
@@ -133,7 +170,17 @@ class Schedule(object):
         self.n_matches, self.slots = n_matches, slots
         self.round = self.order = self.round_offsets = None
         self.ids_sorted = self.meta_sorted = self.info = None
-        self.n_rounds = 0
+        self._n_rounds = None
+
+    @property
+    def n_rounds(self):
+        """Number of rounds; the first read waits for the schedule (ts_schedule itself does not)."""
+        if self._n_rounds is None:
+            info = self.info.cpu().numpy().view(np.uint32)
+            if info[2]:
+                raise L.TsError("ts_schedule: %d rounds need offsets_cap >= %d" % (info[0], info[0] + 2))
+            self._n_rounds = int(info[0])
+        return self._n_rounds
 
 
 class Rater(object):
@@ -192,14 +239,13 @@ class Rater(object):
         L.check(nbytes)
         ws = self._workspace(nbytes)
         cols = list(mode_cols) + [-1] * (16 - len(mode_cols))
-        n_rounds = C.c_uint32(0)
         with torch.cuda.device(dev):
+            # n_rounds_host = NULL: nothing here waits for the GPU; Schedule.n_rounds reads info when asked
             L.check(self._lib.ts_schedule(
                 self._ctx, _ptr(ids), _ptr(meta), n, p, int(n_players), (C.c_int8 * 16)(*cols),
                 _ptr(sch.round), _ptr(sch.order), _ptr(sch.round_offsets), cap,
                 _ptr(sch.ids_sorted), _ptr(sch.meta_sorted), _ptr(sch.info),
-                _ptr(ws), ws.numel(), C.byref(n_rounds), _stream_ptr()))
-        sch.n_rounds = int(n_rounds.value)
+                _ptr(ws), ws.numel(), None, _stream_ptr()))
         return sch
 
     def rate(self, table, sch, outputs=None, lanes_per_match=0):
@@ -286,6 +332,12 @@ class Rater(object):
             pred = self.link_pred(ids[lo:hi], meta[lo:hi], table.n_players, table.mode_cols, seq_base=lo, last=last)
             self.rate_stream(table, ids[lo:hi], meta[lo:hi], pred, None, lanes_per_match, seq_base=lo, flags=flags)
 
+    def unpack_ids(self, packed, bits, out):
+        """Packed id bytes (device uint8) -> the 32-bit ids the kernels read (out: int32 [n, p], contiguous)."""
+        with torch.cuda.device(packed.device):
+            L.check(self._lib.ts_unpack_ids(_ptr(packed), int(bits), out.numel(), _ptr(out), _stream_ptr()))
+        return out
+
     def widen_meta(self, meta8, out=None):
         """uint8 meta column (device) -> the 32-bit words the kernels read."""
         n = meta8.numel()
@@ -329,7 +381,8 @@ class Rater(object):
     def rate_batch(self, ids, meta, table, seed=None, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6),
                    want_outputs=True, lanes_per_match=0, table_out=None, path="auto", windows=None):
         """The reference-facing batch call with HOST buffers: numpy ids
-        [N, P] uint32, meta [N] uint32 or uint8 (only the low 8 bits are used; bytes
+        [N, P] uint32 (or a PackedIds: the same column at ceil(log2(U + 1)) bits per id, see
+        pack_ids -- the id column is most of the PCIe volume), meta [N] uint32 or uint8 (only the low 8 bits are used; bytes
         quarter the column's PCIe volume), table [U, C, 2] float64 (NaN = NULL),
         optional seed [U, 2].  Copies in, schedules, rates, copies back.
         Returns dict(table=..., n_rounds=..., quality=..., out_*=..., status=...).
@@ -345,8 +398,14 @@ class Rater(object):
                 return torch.from_numpy(a.view(np.uint8))      # meta shipped as bytes, widened on the device
             return torch.from_numpy(a.view(np.int32) if as_i32 else a)
 
-        ids_t, meta_t, tab_t, seed_t = host(ids, True), host(meta, True), host(table), host(seed)
-        n, p = ids_t.shape
+        packed = ids if isinstance(ids, PackedIds) else None
+        if packed is not None:
+            ids_t = packed.packed if isinstance(packed.packed, torch.Tensor) else torch.from_numpy(packed.packed)
+            n, p = packed.shape
+        else:
+            ids_t = host(ids, True)
+            n, p = ids_t.shape
+        meta_t, tab_t, seed_t = host(meta, True), host(table), host(seed)
         meta_bytes = meta_t.element_size() == 1
         # The streaming (dataflow) path wins whenever the versioned rows stay in L2 (small tables,
         # whatever the batch: 0.47 vs 0.58 ms for 500 matches) or chains are deep (several matches
@@ -361,8 +420,10 @@ class Rater(object):
         if path == "auto" and shared_col >= 0 and worth:
             # shared + queue layout: a batch that rates one queue column only gets the compact
             # 64-byte rows under one version; a batch that mixes game modes the ordinal-tagged rows
+            # (a look at the meta column on the host, for batches of the worker's size only: a large
+            # batch takes the ordinal-tagged rows, which serve one mode as well as many)
             bits = np.flatnonzero(np.bincount((meta_t.numpy() >> L.META_MODE_SHIFT) & 15, minlength=16)).tolist() \
-                if n <= 4_000_000 else None
+                if n <= 65_536 else None
             if bits is not None:
                 rated = [m for m in bits if m < len(mode_cols) and m < N_MODES and mode_cols[m] >= 0]
                 if len(rated) == 1:
@@ -385,19 +446,22 @@ class Rater(object):
             side = self._copy_stream or torch.cuda.Stream(dev)
             self._copy_stream = side
             ids_d = torch.empty((n, p), dtype=torch.int32, device=dev)
+            ids_in = torch.empty((ids_t.numel(),), dtype=torch.uint8, device=dev) if packed is not None else ids_d
             meta_d = torch.empty((n,), dtype=torch.int32, device=dev)
             meta_in = torch.empty((n,), dtype=torch.uint8, device=dev) if meta_bytes else meta_d
             tab_d = tab_t.to(dev, non_blocking=True)
             seed_d = seed_t.to(dev, non_blocking=True) if seed_t is not None else None
             ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
             last = torch.full((ptab.n_players,), -1, dtype=torch.int32, device=dev)
-            bounds = [(w * n) // windows for w in range(windows + 1)]
+            # windows start at multiples of 8 matches: packed id columns then split on byte boundaries
+            bounds = [((w * n) // windows) & ~7 for w in range(windows)] + [n]
+            cut = (lambda m: m * p * packed.bits // 8 if m < n else ids_t.numel()) if packed is not None else (lambda m: m)
             side.wait_stream(cur)
             ready = []
             with torch.cuda.stream(side):
                 for w in range(windows):
                     lo, hi = bounds[w], bounds[w + 1]
-                    ids_d[lo:hi].copy_(ids_t[lo:hi], non_blocking=True)
+                    ids_in[cut(lo):cut(hi)].copy_(ids_t[cut(lo):cut(hi)], non_blocking=True)
                     meta_in[lo:hi].copy_(meta_t[lo:hi], non_blocking=True)
                     ev = torch.cuda.Event()
                     ev.record(side)
@@ -405,6 +469,8 @@ class Rater(object):
             for w in range(windows):
                 lo, hi = bounds[w], bounds[w + 1]
                 cur.wait_event(ready[w])
+                if packed is not None:
+                    self.unpack_ids(ids_in[cut(lo):cut(hi)], packed.bits, ids_d[lo:hi])
                 if meta_bytes:
                     self.widen_meta(meta_in[lo:hi], meta_d[lo:hi])
                 flags = (L.STREAM_LOAD if w == 0 else 0) | (L.STREAM_STORE if w == windows - 1 else 0)
@@ -414,6 +480,8 @@ class Rater(object):
             n_rounds = None
         else:
             ids_d = ids_t.to(dev, non_blocking=True)
+            if packed is not None:
+                ids_d = self.unpack_ids(ids_d, packed.bits, torch.empty((n, p), dtype=torch.int32, device=dev))
             meta_d = meta_t.to(dev, non_blocking=True)
             if meta_bytes:
                 meta_d = self.widen_meta(meta_d)

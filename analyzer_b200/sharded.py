@@ -107,12 +107,18 @@ def _align(x):
     return (x + 255) & ~255
 
 
+def inbox_capacity(n_matches_cap, slots, world):
+    """Link messages one sender may leave with one receiver: its share of the slots, with room for skew."""
+    np_ = n_matches_cap * slots
+    return np_ if world == 1 else min(np_, int(np_ / (world * world) * 1.3) + (1 << 14))
+
+
 def arena_layout(n_players, n_matches_cap, slots, rank, world):
-    """Byte offsets of (rows, table, ids, meta, succ) in rank's arena, and its size.
-    Every rank computes every rank's layout: peers' pointers are base + offset."""
+    """Byte offsets of (rows, table, ids, meta, succ, inbox, inbox counts) in rank's arena, and
+    its size.  Every rank computes every rank's layout: peers' pointers are base + offset."""
     nl = local_matches(n_matches_cap, rank, world)
     sizes = (n_players * ROW_BYTES, max(1, shard_rows(n_players, rank, world)) * 16, max(1, nl) * slots * 4,
-             max(1, nl) * 4, max(1, nl) * slots * 4)
+             max(1, nl) * 4, max(1, nl) * slots * 4, world * inbox_capacity(n_matches_cap, slots, world) * 8, 64)
     offs, o = [], 0
     for sz in sizes:
         offs.append(o)
@@ -185,6 +191,8 @@ class ShardedLadder(object):
             offs, _ = self.layouts[g]
             v.rows[g], v.table[g] = self.bases[g] + offs[0], self.bases[g] + offs[1]
             v.ids[g], v.meta[g], v.succ[g] = self.bases[g] + offs[2], self.bases[g] + offs[3], self.bases[g] + offs[4]
+            v.inbox[g], v.inbox_count[g] = self.bases[g] + offs[5], self.bases[g] + offs[6]
+        v.inbox_cap = inbox_capacity(self.cap, self.slots, self.world)
         return v
 
     def _stream(self):
@@ -252,7 +260,8 @@ class ShardedLadder(object):
             for x in parts:
                 st |= int(x)
         if st & L.SHARD_OVERFLOW:
-            raise L.TsError("ts_shard_link: workspace too small for the slots this rank owns (pass a larger owned_cap)")
+            raise L.TsError("ts_shard_link: workspace or inbox too small for the slots this rank owns (skewed ladder: "
+                            "pass a larger owned_cap / n_matches_cap)")
         if st & L.SHARD_DUPLICATE:
             raise L.TsError("sharded ladder: a player is listed twice in one match")
         if st & L.SHARD_STALLED:

@@ -61,6 +61,12 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the configs block (configs 3 and 4 at full size) at N = 1")
+    ap.add_argument("--no-sharded", action="store_true", help="skip the one-ladder-over-all-ranks block at N > 1")
+    ap.add_argument("--sharded-matches", type=int, default=100_000_000)
+    ap.add_argument("--sharded-players", type=int, default=10_000_000)
+    ap.add_argument("--sharded-deadline", type=int, default=300)
+    ap.add_argument("--emulate", type=int, default=0, help="with --sharded on one GPU: play this many ranks in one process")
     return ap.parse_args()
 
 
@@ -395,6 +401,249 @@ class ClockSampler(object):
 
 
 # ---------------------------------------------------------------------------
+# BASELINE.json configs[2..3] on one GPU, each with a float128-oracle prefix check
+# ---------------------------------------------------------------------------
+def oracle_prefix_check(rater, engine, gen_args, env_draw, u, layout, n_prefix, lanes, sharded_ladder=None):
+    """Rate the first n_prefix matches of a ladder through the SAME GPU path and compare the
+    table with the sequential __float128 oracle on the host (a prefix is an exact check:
+    the first k matches of a stream do not depend on the rest).  Returns max |diff|."""
+    import numpy as np
+    import torch
+    from oracle import c_oracle as co
+    dev = rater.device
+    seed = gen_args["seed"]
+    gen = engine.make_gen(seed, u, slots=gen_args["slots"], mode=1, p_draw=gen_args["p_draw"], zipf=gen_args["zipf"])
+    ids_d, meta_d = engine.gen_matches(gen, 0, n_prefix, dev)
+    ids = ids_d.cpu().numpy().view(np.uint32)
+    meta = meta_d.cpu().numpy().view(np.uint32)
+    touched = np.unique(ids)
+    tab0 = engine.gen_table(seed, 0, u, dev)
+    prm = co.make_params(draw_probability=env_draw)
+    if layout == "ladder":
+        want = tab0.cpu().numpy()
+        co.rate_sequential(prm, ids, meta, want, -1, [-1, 0], quad=True)
+        if sharded_ladder is not None:
+            from analyzer_b200 import sharded
+            lad = sharded_ladder
+            lad.set_stream(ids_d, meta_d)
+            lad.set_table(tab0.reshape(u, 2))
+            lad.run(n_prefix, mode=1, lanes=lanes)
+            diff = 0.0
+            want_t = torch.from_numpy(want.reshape(u, 2)).to(dev)
+            for g in lad.played:
+                diff = max(diff, float((lad.table[g] - want_t[g::lad.world]).abs().max()))
+            return diff
+        pt = engine.PlayerTable.ladder(tab0, mode=1)
+        rater.rate_stream(pt, ids_d, meta_d, rater.link_pred(ids_d, meta_d, u, pt.mode_cols), None, lanes)
+        got = tab0.cpu().numpy()
+    else:       # "pair": shared + queue pair, every player starts with a stored shared rating and a NULL queue rating
+        t0 = torch.full((u, 2, 2), float("nan"), dtype=torch.float64, device=dev)
+        t0[:, 0] = tab0.reshape(u, 2)
+        want = t0.cpu().numpy()
+        co.rate_sequential(prm, ids, meta, want, 0, [-1, 1], quad=True)
+        pt = engine.PlayerTable(t0, 0, [-1, 1])
+        rater.rate_stream(pt, ids_d, meta_d, rater.link_pred(ids_d, meta_d, u, pt.mode_cols), None, lanes)
+        got = t0.cpu().numpy()
+    assert rater.error_count() == 0
+    d = np.abs(got[touched] - want[touched])
+    return float(np.nanmax(d))
+
+
+def big_traffic(kernel, n, p, k):
+    """dram bytes per launch of `kernel` at this size from the committed ncu summary, or None."""
+    tp = os.path.join(ROOT, "profiles", "r2_big_traffic.json")
+    try:
+        for row in json.load(open(tp)):
+            if row["kernel"] == kernel and row["matches"] == n and row["slots"] == p and row["pairs"] == k:
+                return row["dram_bytes_per_launch"]
+    except Exception:
+        pass
+    return None
+
+
+def config_block(rater_of, engine, name, n, u, p, zipf, p_draw, layout, lanes, peak, reps=3, n_prefix=200_000,
+                 want_rounds=True):
+    """One BASELINE.json configuration on this GPU, HBM-resident: stream path (link + rate),
+    best of `reps`, roofline of the rating kernel on the algorithmic bytes, oracle prefix check."""
+    import torch
+    rater = rater_of(p_draw)
+    dev = rater.device
+    seed = SEED + 0x100
+    gen = engine.make_gen(seed, u, slots=p, mode=1, p_draw=p_draw, zipf=zipf)
+    ids_d, meta_d = engine.gen_matches(gen, 0, n, dev)
+    base = engine.gen_table(seed, 0, u, dev)
+    k = 1 if layout == "ladder" else 2
+    if layout == "ladder":
+        tab0 = base
+        make_pt = lambda t: engine.PlayerTable.ladder(t, mode=1)
+    else:
+        tab0 = torch.full((u, 2, 2), float("nan"), dtype=torch.float64, device=dev)
+        tab0[:, 0] = base.reshape(u, 2)
+        make_pt = lambda t: engine.PlayerTable(t, 0, [-1, 1])
+    tab = tab0.clone()
+    pt = make_pt(tab)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    best = None
+    pred = None
+    for it in range(1 + reps):
+        tab.copy_(tab0)
+        pred = None
+        e0, e1, e2 = ev(), ev(), ev()
+        e0.record()
+        pred = rater.link_pred_windows(ids_d, meta_d, u, pt.mode_cols)
+        e1.record()
+        rater.rate_stream(pt, ids_d, meta_d, pred, None, lanes)
+        e2.record()
+        torch.cuda.synchronize()
+        t = (e0.elapsed_time(e1), e1.elapsed_time(e2))
+        if it > 0 and (best is None or sum(t) < sum(best)):
+            best = t
+    assert rater.error_count() == 0
+    del pred
+    b = rate_bytes_per_match(p, k)
+    achieved = b * n / (best[1] * 1e-3) / 1e9
+    kernel = "k_rate_stream" if layout == "ladder" else "k_rate_stream_pair"
+    traffic = big_traffic(kernel, n, p, k)
+    out = {"workload": name, "path": "stream", "link_ms": best[0], "rate_ms": best[1],
+           "matches_per_s": n / (sum(best) * 1e-3),
+           "roofline": {"kernel": kernel, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                        "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_match": b,
+                        "traffic_over_algorithmic": (traffic / (b * n)) if traffic else None},
+           "l2": "table %d MB, versioned rows %d MB (L2 is 126 MB)" % ((u * 16 * k) >> 20, (u * 32 * k) >> 20)}
+    if want_rounds:
+        try:
+            tab.copy_(tab0)
+            e0, e1, e2 = ev(), ev(), ev()
+            e0.record()
+            sch = rater.schedule(ids_d, meta_d, u, pt.mode_cols)
+            e1.record()
+            rater.rate(pt, sch, None, lanes)
+            e2.record()
+            torch.cuda.synchronize()
+            out["rounds"] = sch.n_rounds
+            out["rounds_path"] = {"schedule_ms": e0.elapsed_time(e1), "rate_ms": e1.elapsed_time(e2),
+                                  "roofline_frac_rate": b * n / (e1.elapsed_time(e2) * 1e-3) / 1e9 / peak}
+            del sch
+        except Exception as exc:
+            out["rounds_path"] = {"error": repr(exc)}
+    del ids_d, meta_d, tab, tab0, base, pt
+    rater._ws = None
+    torch.cuda.empty_cache()
+    out["check_max_abs_diff"] = oracle_prefix_check(
+        rater, engine, {"seed": seed, "slots": p, "p_draw": p_draw, "zipf": zipf}, p_draw, u, layout, n_prefix, lanes)
+    out["check"] = "first %d matches through the same path vs the sequential __float128 oracle" % n_prefix
+    assert out["check_max_abs_diff"] < 1e-9, out
+    rater._ws = rater._vt = None
+    torch.cuda.empty_cache()
+    return out
+
+
+# ---------------------------------------------------------------------------
+# BASELINE.json configs[4]: ONE ladder over all ranks (strong scaling)
+# ---------------------------------------------------------------------------
+def sharded_block(a, rater, engine, dist, rank, world, dev, n, u, p, steps=5, warmup=2, emulate=0, n_prefix=200_000):
+    """Rows pushed to the rank that rates the player's next match (analyzer_b200/sharded.py).
+    Every rank also rates the whole ladder alone (the one-GPU stream path) for the
+    strong-scaling baseline and the bit-for-bit check of its table shard."""
+    import torch
+    from analyzer_b200 import sharded
+    G = emulate if emulate else world
+    seed = SEED + 0x200
+    gen = engine.make_gen(seed, u, slots=p, mode=1, p_draw=a.p_draw, zipf=a.zipf)
+    ids_d, meta_d = engine.gen_matches(gen, 0, n, dev)
+    full0 = engine.gen_table(seed, 0, u, dev).reshape(u, 2)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    # one GPU alone, same ladder
+    one = None
+    single = full0.clone().reshape(u, 1, 2)
+    pt = engine.PlayerTable.ladder(single, mode=1)
+    for it in range(3):
+        single.copy_(full0.reshape(u, 1, 2))
+        e0, e1, e2 = ev(), ev(), ev()
+        e0.record()
+        pred = rater.link_pred_windows(ids_d, meta_d, u, pt.mode_cols)
+        e1.record()
+        rater.rate_stream(pt, ids_d, meta_d, pred, None, a.lanes)
+        e2.record()
+        torch.cuda.synchronize()
+        t = (e0.elapsed_time(e1), e1.elapsed_time(e2))
+        if it > 0 and (one is None or sum(t) < sum(one)):
+            one = t
+        del pred
+    assert rater.error_count() == 0
+    want = single.reshape(u, 2)
+    rater._ws = rater._vt = None
+    torch.cuda.empty_cache()
+
+    ladder = sharded.ShardedLadder(rater, u, n, p, 0 if emulate else rank, G, emulate=bool(emulate))
+    prefix_diff = oracle_prefix_check(rater, engine, {"seed": seed, "slots": p, "p_draw": a.p_draw, "zipf": a.zipf},
+                                      a.p_draw, u, "ladder", min(n_prefix, n), a.lanes, sharded_ladder=ladder)
+    ladder.set_stream(ids_d, meta_d)
+    del ids_d, meta_d
+    torch.cuda.empty_cache()
+    walls, links, rates = [], [], []
+    for it in range(warmup + steps):
+        ladder.set_table(full0)
+        barrier()
+        t0 = time.perf_counter()
+        e0, e1, e2, e3 = ev(), ev(), ev(), ev()
+        e0.record()
+        ladder.reset()
+        ladder.barrier()
+        ladder.link(n, 1)
+        e1.record()
+        ladder.barrier()
+        e2.record()
+        ladder.rate(n, 1, 0, None, a.lanes)
+        e3.record()
+        ladder.barrier()
+        dt = time.perf_counter() - t0
+        ladder.check()
+        if it >= warmup:
+            walls.append(dt * 1e3)
+            links.append(e0.elapsed_time(e1))
+            rates.append(e2.elapsed_time(e3))
+    equal = all(torch.equal(ladder.table[g], want[g::G]) for g in ladder.played)
+    maxdiff = max(float((ladder.table[g] - want[g::G]).abs().max()) for g in ladder.played)
+    t = torch.tensor([sum(walls) / len(walls), sum(links) / len(links), sum(rates) / len(rates), one[0], one[1],
+                      0.0 if equal else 1.0, maxdiff, prefix_diff], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_wall, ms_link, ms_rate, one_link, one_rate, unequal, maxdiff, prefix_diff = (float(x) for x in t.cpu())
+    ladder.close()
+    assert rater.error_count() == 0
+    remote = (G - 1) / G
+    rate_nv = remote * p * 32 * n / G                       # rows pushed to other GPUs, per GPU
+    link_nv = remote * (n * p * 4 + n * 4) + remote * (n * p * 4) / G      # id stream read from peers + succ stored to peers
+    out = {"workload": "%s synthetic %s matches over %s players, ONE ladder, table hash-sharded over %d GPUs%s" % (
+               _si(n), "3v3" if p == 6 else "5v5", _si(u), G, " (all ranks played by one GPU)" if emulate else ""),
+           "n_gpus": G, "scaling": "strong", "ms_per_step": ms_wall, "link_ms": ms_link, "rate_ms": ms_rate,
+           "matches_per_s": n / (ms_wall * 1e-3),
+           "timing": "ms_per_step = wall clock from before the mailbox reset to after the last barrier (host barriers "
+                     "included), max over ranks; link_ms / rate_ms = CUDA events around each rank's own launches, max over ranks",
+           "one_gpu": {"link_ms": one_link, "rate_ms": one_rate, "matches_per_s": n / ((one_link + one_rate) * 1e-3)},
+           "speedup_vs_one_gpu": (one_link + one_rate) / ms_wall,
+           "strong_scaling_efficiency": (one_link + one_rate) / ms_wall / G,
+           "nvlink": {"rate_bytes_per_gpu": rate_nv, "rate_gbs_per_gpu": rate_nv / (ms_rate * 1e-3) / 1e9,
+                      "link_bytes_per_gpu": link_nv, "link_gbs_per_gpu": link_nv / (ms_link * 1e-3) / 1e9,
+                      "peak_gbs_per_direction": 770.0,
+                      "note": "rows pushed to other GPUs (32 B each); id stream read from peers + succ stored to peers; "
+                              "770 GB/s = measured peer copy per direction (B200_PROFILING.md)"},
+           "bit_equal_to_one_gpu": unequal == 0.0, "max_abs_diff_vs_one_gpu": maxdiff,
+           "check_max_abs_diff": prefix_diff,
+           "check": "first %d matches through the sharded path vs the sequential __float128 oracle; full ladder "
+                    "compared bit for bit with the one-GPU stream path" % min(n_prefix, n)}
+    assert unequal == 0.0 and prefix_diff < 1e-9, out
+    return out
+
+
+# ---------------------------------------------------------------------------
 def run_b200(a):
     import numpy as np
     import torch
@@ -430,11 +679,10 @@ def run_b200(a):
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
     timings = {"stream": ([], []), "rounds": ([], [])}
-    n_rounds = 0
+    last_sch = [None]
     final = {}
 
     def step(path, timed):
-        nonlocal n_rounds
         table.copy_(table0)
         flush.fill_(1)                       # evict ids/table from L2 between steps
         e0, e1, e2 = ev(), ev(), ev()
@@ -447,7 +695,7 @@ def run_b200(a):
             sch = rater.schedule(ids_d, meta_d, u, ptab.mode_cols)
             e1.record()
             rater.rate(ptab, sch, None, a.lanes)
-            n_rounds = sch.n_rounds
+            last_sch[0] = sch              # its round count is read after the timed region: nothing in a step waits for the GPU
         e2.record()
         if timed:
             torch.cuda.synchronize()
@@ -474,6 +722,8 @@ def run_b200(a):
     t_wall = time.perf_counter() - t_wall
     clocks = sampler.stop()
     final[a.path] = table.clone()
+    n_rounds = last_sch[0].n_rounds if last_sch[0] is not None else 0
+    last_sch[0] = None
     assert rater.error_count() == 0
     # both paths rate the same ladder: their tables must agree to rounding
     assert float((final["stream"] - final["rounds"]).abs().max()) < 1e-9, "stream and rounds paths disagree"
@@ -493,7 +743,8 @@ def run_b200(a):
     # ---- e2e: the reference-facing call with pinned host buffers -----------
     e2e = None
     if not a.skip_e2e:
-        ids_h = ids_d.cpu().pin_memory()
+        # the id column at the width it needs (ceil(log2(U + 1)) bits per id, widened on the device) ...
+        ids_h = engine.pack_ids(ids_d.cpu().numpy().view(np.uint32), u, pin=True)
         meta_h = meta_d.cpu().to(torch.uint8).pin_memory()    # the meta word uses 8 bits: shipped as bytes
         tab_h = table0.cpu().pin_memory()
         out_h = torch.empty_like(tab_h).pin_memory()
@@ -513,14 +764,11 @@ def run_b200(a):
             dt = float(t.cpu()[0])
         # the e2e result must be the same table the device-resident path produced
         assert torch.equal(out_h, final[a.path].cpu()), "e2e table differs from the HBM-resident run"
-        h2d = ids_h.numel() * 4 + meta_h.numel() * meta_h.element_size() + tab_h.numel() * 8
+        h2d = ids_h.nbytes + meta_h.numel() * meta_h.element_size() + tab_h.numel() * 8
         e2e = {"value": n * world / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": out_h.numel() * 8 + 8 + 16, "ms_per_step": dt * 1e3, "steps": k_e2e}
-
-    if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return 0
+               "d2h_bytes_per_step": out_h.numel() * 8 + 8 + 16, "ms_per_step": dt * 1e3, "steps": k_e2e,
+               "ingest": "ids packed at %d bits each (ts_unpack_ids), meta as bytes (ts_widen_meta), table float64; "
+                         "copies pipelined with link + rate over windows" % ids_h.bits}
 
     peak, peak_src = hbm_peak()
     b_rate = rate_bytes_per_match(p, 1)
@@ -575,6 +823,32 @@ def run_b200(a):
     }
     if e2e:
         line["e2e"] = e2e
+    if world > 1 and not a.no_sharded:
+        # BASELINE.json configs[4] (strong scaling): ONE ladder over all ranks, on the same process group.
+        # A deadline guards the contract: whatever happens in there, rank 0 prints its line and every rank exits 0.
+        del ids_d, meta_d, table, table0, flush, final
+        rater._ws = rater._vt = None
+        torch.cuda.empty_cache()
+
+        def give_up():
+            if rank == 0:
+                line["sharded"] = {"error": "no result within %d s" % a.sharded_deadline}
+                print(json.dumps(line), flush=True)
+            os._exit(0)
+
+        timer = threading.Timer(a.sharded_deadline, give_up)
+        timer.daemon = True
+        timer.start()
+        try:
+            line["sharded"] = sharded_block(a, rater, engine, dist, rank, world, dev, a.sharded_matches,
+                                            a.sharded_players, p)
+        except Exception as exc:
+            line["sharded"] = {"error": repr(exc)}
+        timer.cancel()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
     if world == 1 and p in (6, 10):
         try:
             line["faithful"] = faithful_rate(rater, engine, ids_d, meta_d, table0, u, a.lanes)
@@ -603,6 +877,34 @@ def run_b200(a):
         except Exception as exc:   # the C oracle is optional context, never the product
             cb["c_error"] = repr(exc)
         line["cpu_baseline"] = cb
+    if world == 1 and not a.no_configs:
+        # the other single-GPU configurations BASELINE.json names, at their stated sizes
+        del ids_d, meta_d, table, table0, flush, final
+        rater._ws = rater._vt = None
+        torch.cuda.empty_cache()
+        raters = {a.p_draw: rater}
+
+        def rater_of(p_draw):
+            if p_draw not in raters:
+                raters[p_draw] = engine.Rater(engine.Env(draw_probability=p_draw), local)
+            return raters[p_draw]
+
+        cfgs = {}
+        for key, kw in (
+                ("config3", dict(name="100M 5v5 matches over 10M players, Zipf activity, 2% draws (BASELINE.json configs[2])",
+                                 n=100_000_000, u=10_000_000, p=10, zipf=True, p_draw=0.02, layout="ladder")),
+                ("config4_ladder", dict(name="one of the 8 ladders of BASELINE.json configs[3]: 125M 3v3 matches over 12.5M "
+                                             "players, K=1 pair per player", n=125_000_000, u=12_500_000, p=6, zipf=False,
+                                        p_draw=0.0, layout="ladder")),
+                ("config4_ladder_k2", dict(name="the same ladder with the reference's shared + queue pair per player (K=2: one "
+                                                "32-byte sector of table per player)", n=125_000_000, u=12_500_000, p=6,
+                                           zipf=False, p_draw=0.0, layout="pair", want_rounds=False))):
+            try:
+                cfgs[key] = config_block(rater_of, engine, lanes=a.lanes, peak=peak, **kw)
+            except Exception as exc:
+                cfgs[key] = {"error": repr(exc)}
+                torch.cuda.empty_cache()
+        line["configs"] = cfgs
     print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
@@ -610,74 +912,30 @@ def run_b200(a):
 
 
 def run_sharded(a):
-    """One ladder, table sharded by player id over the ranks' GPUs; every rank
-    holds the match stream, links the players it owns (one MIN all-reduce
-    assembles the links) and rates the tiles t with t % world == rank."""
+    """--sharded: only the one-ladder-over-all-ranks block (sharded_block), at --matches / --players;
+    on one GPU --emulate G plays G ranks in one process."""
     import torch
-    import torch.distributed as dist
-    from analyzer_b200 import engine, sharded
-
+    from analyzer_b200 import engine
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    dist = None
     if world > 1:
+        import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
-    else:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ.setdefault("MASTER_PORT", "29555")
-        dist.init_process_group("gloo", rank=0, world_size=1)
-    n, u, p = a.matches, a.players, a.slots
     rater = engine.Rater(engine.Env(draw_probability=a.p_draw), local)
-    gen = engine.make_gen(SEED, u, slots=p, mode=1, p_draw=a.p_draw, zipf=a.zipf)
-    ids_d, meta_d = engine.gen_matches(gen, 0, n, dev)
-    full = engine.gen_table(SEED, 0, u, dev).reshape(u, 2)
-    mine0 = sharded.split_table(full, rank, world)
-    mine = mine0.clone()
-    ladder = sharded.ShardedLadder(rater, u, rank, world)
-    ev = lambda: torch.cuda.Event(enable_timing=True)
-    link_ms, rate_ms = [], []
-    for it in range(a.warmup + a.steps):
-        mine.copy_(mine0)
-        torch.cuda.synchronize()
-        dist.barrier()
-        e0, e1 = ev(), ev()
-        e0.record()
-        pred = ladder.link(ids_d, meta_d, [-1, 0])      # owned players per rank + one MIN all-reduce
-        e1.record()
-        torch.cuda.synchronize()
-        dist.barrier()
-        t0 = time.perf_counter()          # the rate phase spans host barriers: wall clock between syncs
-        ladder.rate(mine, ids_d, meta_d, pred, mode=1, lanes=a.lanes)
-        dist.barrier()
-        dt = time.perf_counter() - t0
-        if it >= a.warmup:
-            link_ms.append(e0.elapsed_time(e1))
-            rate_ms.append(dt * 1e3)
-    t = torch.tensor([sum(link_ms) / len(link_ms), sum(rate_ms) / len(rate_ms)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_link, ms_rate = (float(x) for x in t.cpu())
-    assert rater.error_count() == 0
+    out = sharded_block(a, rater, engine, dist, rank, world, dev, a.matches, a.players, a.slots, steps=a.steps,
+                        warmup=a.warmup, emulate=a.emulate if world == 1 else 0)
     if rank == 0:
-        remote = (world - 1) / world
-        nv_bytes = remote * p * 64 * n / world          # per GPU, rows read + written remotely (32 B each way)
-        line = {"metric": METRIC, "value": n / ((ms_link + ms_rate) * 1e-3), "unit": UNIT, "n_gpus": world,
-                "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_link + ms_rate, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": workload_name(a) + ", table hash-sharded over %d GPUs (NVLink peer memory)" % world,
-                           "seed": hex(SEED), "path": "stream-sharded",
-                           "note": "link phase: each rank sorts / links the players it owns, one MIN all-reduce; rate "
-                                   "phase split by warp tile, no inter-GPU barrier or collective; rate_ms is wall "
-                                   "clock between host barriers"},
-                "phases": {"schedule_ms": ms_link, "rate_ms": ms_rate, "rate_only_matches_per_s": n / (ms_rate * 1e-3)},
-                "nvlink": {"bytes_per_gpu_per_step": nv_bytes, "achieved_gbs_per_gpu": nv_bytes / (ms_rate * 1e-3) / 1e9,
-                           "peak_gbs_per_direction": 770.0, "note": "remote row reads + writes; 770 GB/s = measured peer copy "
-                           "per direction (B200_PROFILING.md)"}}
+        line = {"metric": METRIC, "value": out["matches_per_s"], "unit": UNIT, "n_gpus": world, "steps": a.steps,
+                "warmup": a.warmup, "ms_per_step": out["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": out["workload"], "seed": hex(SEED), "path": "stream-sharded"}, "sharded": out}
         print(json.dumps(line))
-    ladder.close()
-    dist.destroy_process_group()
+    if dist is not None:
+        dist.destroy_process_group()
     return 0
 
 

@@ -113,8 +113,12 @@ int64_t ts_schedule_workspace_bytes(int64_t n_matches, int32_t slots);
  * match_seq); round_offsets[offsets_cap] with bucket r at
  * [round_offsets[r], round_offsets[r+1]), r = 0 (gated) .. n_rounds;
  * ids_sorted[N][P] / meta_sorted[N] = the records permuted into that order;
- * info.  Synchronises the stream once (to size the final sort).
- * On success *n_rounds_host (optional) receives n_rounds. */
+ * info.  With n_rounds_host == NULL the call only enqueues work: the number of
+ * rounds stays on the device (the final sort sizes itself there), and if
+ * round_offsets is too small for it, info->overflow is set, ts_rate on that
+ * schedule rates nothing and counts one value error.  With n_rounds_host the
+ * call synchronises the stream once, stores n_rounds there and returns
+ * TS_E_WORKSPACE on overflow. */
 int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches,
                 int32_t slots, int64_t n_players, const int8_t mode_col[16],
                 uint32_t *round, uint32_t *order, uint32_t *round_offsets, int64_t offsets_cap,
@@ -133,11 +137,16 @@ int ts_schedule(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t 
  *   - n_matches * slots must not exceed TS_STATIC_MAX_SLOT_ENTRIES, else
  *     TS_E_WORKSPACE (ts_last_error says so);
  *   - the first call on a device resolves the array's device address and caches
- *     it: make that call before any stream capture;
+ *     it: make that call before any stream capture, and from one host thread at a
+ *     time per device (the cache is filled under a lock, but two first calls would
+ *     also share the scratch, see below);
+ *   - like ts_schedule it synchronises `stream` once when n_rounds_host is given,
+ *     and only enqueues work when it is NULL;
  *   - all calls share the array; it is not cleared between calls except for what
  *     the scheduler needs zeroed, which each call clears on `stream` itself;
  *     calls whose GPU work can overlap race -- serialise them;
- *   - performs no cudaMalloc / cudaFree / allocating library call. */
+ *   - performs no cudaMalloc / cudaFree / allocating library call (the test
+ *     checks that the free device memory is the same before and after). */
 #define TS_STATIC_MAX_SLOT_ENTRIES 65536
 int ts_schedule_static(int device, const uint32_t *ids, const uint32_t *meta, int64_t n_matches,
                        int32_t slots, int64_t n_players, const int8_t mode_col[16],
@@ -218,9 +227,12 @@ int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, cons
  * match the pair goes back to the owner's table shard.  No inter-GPU barrier and no
  * collective while rating.
  * Links: ts_shard_link reads the whole id stream once (its peers' slices over NVLink),
- * keeps the slots of the players it owns, sorts them, and stores succ[m][s] (the
- * stream-wide number of that player's next rated match, TS_NONE if none) straight into
- * the slice of the rank that rates m, together with every owned player's first row.
+ * keeps the slots of the players it owns, sorts them, and sends succ[m][s] (the
+ * stream-wide number of that player's next rated match, TS_NONE if none) to the rank
+ * that rates m -- as messages appended to that rank's inbox in large coalesced pieces,
+ * which ts_shard_rate scatters into the succ slice locally before it rates (scattered
+ * 4-byte stores into a peer's memory are partial-sector writes and crawl) -- together
+ * with every owned player's first row.  TS_SHARD_OVERFLOW: workspace or inbox too small.
  * A player listed twice in one match is not supported here (TS_SHARD_DUPLICATE).
  *
  * All arrays of a ts_shard_view are device pointers valid on THIS GPU: index rank =
@@ -238,6 +250,9 @@ typedef struct ts_shard_view {
     uint32_t *succ[TS_SHARD_MAX];            /* [n_local(g)][slots], written by the players' owners */
     unsigned long long *rows[TS_SHARD_MAX];  /* mailbox: n_players rows of four 64-bit words      */
     double *table[TS_SHARD_MAX];             /* [ceil((n_players - g) / G)][2]                    */
+    unsigned long long *inbox[TS_SHARD_MAX]; /* link messages for rank g: [G senders][inbox_cap]  */
+    uint32_t *inbox_count[TS_SHARD_MAX];     /* [G]: messages each sender left in rank g's inbox  */
+    int64_t inbox_cap;                       /* about n_matches * slots / G^2, with room for skew */
 } ts_shard_view;
 /* ts_shard_status bits */
 #define TS_SHARD_STALLED 1    /* a match's rows never arrived (watchdog): tables unusable      */
@@ -288,6 +303,12 @@ int ts_seed_table(const double *rank_points_ranked, const double *rank_points_bl
  * column as bytes (a quarter of its PCIe volume) and widen it on the device.
  * No counterpart in the reference (it has no columnar format). */
 int ts_widen_meta(const uint8_t *meta8, int64_t n_matches, uint32_t *meta, void *stream);
+/* The id column at the width it needs: `count` ids packed as a little-endian bit stream of
+ * `bits` bits each (bits = ceil(log2(n_players + 1)); the all-ones value is TS_EMPTY_SLOT),
+ * widened to the uint32 the kernels read.  worker.py:176-191 loads nothing wider than a
+ * player's identity per participant; for a million players this is 20/32 of the PCIe volume
+ * of the column that bounds the end-to-end call.  No counterpart in the reference. */
+int ts_unpack_ids(const uint8_t *packed, int32_t bits, int64_t count, uint32_t *ids, void *stream);
 
 /* Synthetic ladders of BASELINE.json's configs (SURVEY.md 8d "Generator"):
  * counter-based, so any window [first, first+count) can be produced on its

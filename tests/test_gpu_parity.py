@@ -148,8 +148,17 @@ def test_schedule_edge_cases(eng, rater, c_oracle):
     assert _check_schedule(c_oracle, sch, ids, meta, cols, 6) == 3
     # too small an offsets array is reported, not overrun
     from analyzer_b200._lib import TsError
+    # round_offsets too small: ts_schedule does not wait for the GPU, so the overflow is flagged on the
+    # device -- reading n_rounds raises, and ts_rate on such a schedule rates nothing and counts an error
+    sch = rater.schedule(_dev(ids), _dev(meta), 6, cols, offsets_cap=3)
     with pytest.raises(TsError):
-        rater.schedule(_dev(ids), _dev(meta), 6, cols, offsets_cap=3)
+        sch.n_rounds
+    tab_d = _dev(np.tile(np.array([1500.0, 300.0]), (6, 1, 1)))
+    before = tab_d.clone()
+    rater.reset_errors()
+    rater.rate(eng.PlayerTable(tab_d, -1, cols), sch)
+    assert rater.error_counts() == (0, 1) and torch.equal(tab_d, before)
+    rater.reset_errors()
     # other team sizes (2v2, 8v8): the run-time-slots form of the rounds kernel
     rng = np.random.default_rng(3)
     for slots in (4, 16):

@@ -264,6 +264,20 @@ def test_rate_batch_pipelined_windows(eng):
     d = r.rate_batch(ids_h.numpy().view(np.uint32), meta_h.numpy().astype(np.uint8), tab_h.numpy(), shared_col=-1,
                      mode_cols=[-1, 0], path="rounds")
     assert np.abs(a["table"] - d["table"]).max() < TOL
+    # the id column shipped at the width it needs (15 bits for this table) and widened on the device
+    packed = eng.pack_ids(ids_h.numpy().view(np.uint32), u, pin=True)
+    assert packed.nbytes < ids_h.numel() * 4 * 0.7
+    back = r.unpack_ids(packed.packed.cuda(), packed.bits, torch.empty_like(ids_h, device="cuda"))
+    assert torch.equal(back.cpu(), ids_h)
+    for windows in (5, 1):
+        e = r.rate_batch(packed, meta8, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=windows)
+        assert np.array_equal(a["table"], e["table"]) and e["errors"] == 0
+    # ragged records (empty slots) survive the packing
+    ids_r = ids_h.numpy().view(np.uint32).copy()
+    ids_r[::7, 2] = 0xFFFFFFFF
+    f = r.rate_batch(ids_r, meta8, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=1)
+    g = r.rate_batch(eng.pack_ids(ids_r, u), meta8, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=3)
+    assert np.array_equal(f["table"], g["table"])
     r.close()
 
 

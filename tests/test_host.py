@@ -99,3 +99,22 @@ def test_ingest_columns(rater_mod):
     bad = rp.new_player(skill_tier=None)
     with pytest.raises(KeyError):
         rater_mod.ingest([rp.new_match("ranked", [(True, [mk(bad)]), (False, [mk(b)])])])
+
+
+def test_pack_ids_bit_stream_round_trip():
+    """engine.pack_ids: ids at ceil(log2(U + 1)) bits each, little-endian bit stream, all ones = empty slot."""
+    from analyzer_b200 import engine
+    rng = np.random.default_rng(3)
+    for u in (2, 5, 255, 256, 1000, 1 << 20, 1_000_000, 12_500_000):
+        bits = engine.id_bits(u)
+        assert (1 << bits) - 1 >= u and (bits == 1 or (1 << (bits - 1)) - 1 < u)
+        n, p = 1003, 6
+        ids = rng.integers(0, u, size=(n, p)).astype(np.uint32)
+        ids[rng.random((n, p)) < 0.05] = 0xFFFFFFFF
+        ids[0, 0], ids[1, 1] = 0, u - 1
+        pk = engine.pack_ids(ids, u)
+        assert pk.bits == bits and pk.shape == (n, p) and pk.nbytes == (n * p * bits + 7) // 8
+        stream = np.unpackbits(pk.packed.numpy(), bitorder="little")[:n * p * bits].reshape(n * p, bits)
+        vals = (stream.astype(np.uint64) << np.arange(bits, dtype=np.uint64)).sum(axis=1).astype(np.uint32)
+        vals[vals == (1 << bits) - 1] = 0xFFFFFFFF
+        assert np.array_equal(vals.reshape(n, p), ids)
