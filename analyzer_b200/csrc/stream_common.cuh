@@ -119,7 +119,7 @@ __device__ __forceinline__ uint32_t group_sum_u32(uint32_t x)
 // (Two buffers, and no prefetch, where three would not fit the 48 KB of static shared memory:
 // one lane per 5v5 match.)
 template <int P, int W>
-struct WarpStage {
+struct alignas(16) WarpStage {
     static constexpr int kDepth = ((2 * W * P + W) * 4 * 3 * 8 <= 48 * 1024) ? 3 : 2;
     uint32_t ids[kDepth][W * P];
     uint32_t link[kDepth][W * P];
