@@ -9,7 +9,8 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(_HERE, "libtsrate.so")
+# TSRATE_LIB: another build of the same library (tuning variants, scripts/build_variants.sh)
+LIB_PATH = os.environ.get("TSRATE_LIB") or os.path.join(_HERE, "libtsrate.so")
 SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "stream_pair.cu", "shard.cu", "static_sched.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-shared", "-Xcompiler", "-fPIC"]
@@ -140,7 +141,7 @@ def lib():
         L.ts_shard_local_matches.restype = C.c_int64
         L.ts_shard_local_matches.argtypes = [C.c_int64, C.c_int32, C.c_int32]
         L.ts_shard_link_workspace_bytes.restype = C.c_int64
-        L.ts_shard_link_workspace_bytes.argtypes = [C.c_int64]
+        L.ts_shard_link_workspace_bytes.argtypes = [C.c_int64, C.c_int64]
         L.ts_shard_reset.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_void_p]
         L.ts_shard_link.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_int32, C.c_int64, C.c_int8,
                                     C.c_int64, C.c_void_p, C.c_int64, C.c_void_p]

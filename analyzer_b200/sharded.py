@@ -226,7 +226,7 @@ class ShardedLadder(object):
         np_ = n_matches * self.slots
         if owned_cap is None:       # a rank owns ~1/world of the slots; skewed ladders may need more
             owned_cap = np_ if self.world == 1 else min(np_, int(np_ / self.world * 1.25) + (1 << 16))
-        nbytes = L.check(self.lib.ts_shard_link_workspace_bytes(owned_cap))
+        nbytes = L.check(self.lib.ts_shard_link_workspace_bytes(np_, owned_cap))
         if self._ws is None or self._ws.numel() < nbytes:
             self._ws = None
             self._ws = torch.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", self.device))

@@ -259,9 +259,10 @@ typedef struct ts_shard_view {
 #define TS_SHARD_OVERFLOW 2   /* ts_shard_link: workspace too small for the owned slots        */
 #define TS_SHARD_DUPLICATE 4  /* a player is listed twice in one match                          */
 int64_t ts_shard_local_matches(int64_t n_matches, int32_t rank, int32_t n_shards);
-/* workspace for ts_shard_link that holds `owned_cap` (player, slot) pairs; a rank owns
- * about n_matches * slots / n_shards of them (all of them in the worst case) */
-int64_t ts_shard_link_workspace_bytes(int64_t owned_cap);
+/* workspace for ts_shard_link on a window of n_slot_entries = n_matches * slots: 8 bytes per slot
+ * entry (staging of the compaction) plus the sort's buffers for `owned_cap` (player, slot) pairs;
+ * a rank owns about n_slot_entries / n_shards of them (all of them in the worst case) */
+int64_t ts_shard_link_workspace_bytes(int64_t n_slot_entries, int64_t owned_cap);
 int ts_shard_alloc(int device, int64_t bytes, void **ptr, void *handle64);
 int ts_shard_open(int device, const void *handle64, void **ptr);
 int ts_shard_close(void *ptr);

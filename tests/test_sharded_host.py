@@ -94,4 +94,4 @@ def test_shard_entry_points_refuse_bad_views():
     assert b"power of two" in lib.ts_last_error()
     assert lib.ts_shard_rate(None, C.byref(v), 10, 6, 10, 1, 0, None, 0, 0, None) == -1
     assert lib.ts_shard_local_matches(-1, 0, 2) < 0
-    assert lib.ts_shard_link_workspace_bytes(1 << 20) > (1 << 20) * 16
+    assert lib.ts_shard_link_workspace_bytes(1 << 22, 1 << 20) > (1 << 20) * 16 + (1 << 22) * 8
