@@ -31,7 +31,7 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_stream_stalled", "ts_rate_stream_table_workspace_bytes",
            "ts_seed_table", "ts_widen_meta", "ts_unpack_ids", "ts_error_counts",
            "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_shard_local_matches",
-           "ts_shard_link_workspace_bytes", "ts_shard_reset", "ts_shard_link", "ts_shard_rate", "ts_shard_status"]
+           "ts_shard_link_workspace_bytes", "ts_shard_inbox_cap", "ts_shard_reset", "ts_shard_link", "ts_shard_rate", "ts_shard_status"]
 SHARD_BLOCK, SHARD_MAX = 32, 16
 SHARD_STALLED, SHARD_OVERFLOW, SHARD_DUPLICATE = 1, 2, 4
 
@@ -140,6 +140,8 @@ def lib():
         L.ts_shard_free.argtypes = [C.c_void_p]
         L.ts_shard_local_matches.restype = C.c_int64
         L.ts_shard_local_matches.argtypes = [C.c_int64, C.c_int32, C.c_int32]
+        L.ts_shard_inbox_cap.restype = C.c_int64
+        L.ts_shard_inbox_cap.argtypes = [C.c_int64, C.c_int32, C.c_int32]
         L.ts_shard_link_workspace_bytes.restype = C.c_int64
         L.ts_shard_link_workspace_bytes.argtypes = [C.c_int64, C.c_int64]
         L.ts_shard_reset.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_void_p]

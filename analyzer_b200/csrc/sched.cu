@@ -1331,12 +1331,13 @@ k_owned_gather(const unsigned long long *staging, const uint32_t *offsets, uint3
 }
 
 struct ShardDst {
-    unsigned long long *inbox[TS_SHARD_MAX];     // rank g's inbox: one region of inbox_cap messages per sender
-    uint32_t *inbox_count[TS_SHARD_MAX];         // rank g's message counts, one per sender
+    unsigned long long *inbox[TS_SHARD_MAX];     // rank g's inbox: [n_ranges][G senders][region_cap] messages
+    uint32_t *inbox_count[TS_SHARD_MAX];         // rank g's message counts, [n_ranges][G senders]
     unsigned long long *rows[TS_SHARD_MAX];
     const double *table_own;
-    uint32_t *out_count;                         // this rank's running message count per destination
-    uint32_t inbox_cap;
+    uint32_t *out_count;                         // this rank's running message count per bucket (destination, range)
+    uint32_t region_cap;                         // messages one sender may leave in one (destination, range) region
+    uint32_t n_ranges, range_shift;              // a destination's slots in ranges of 2^range_shift: one L2-sized scatter each
     uint32_t g_mask, g_shift, owner;
     uint32_t slots;
     unsigned long long slots_magic;
@@ -1353,24 +1354,27 @@ __device__ __forceinline__ void st_row_sys(unsigned long long *row, double mu, d
 }
 
 // Successor links, routed: a scattered 4-byte store into another GPU's memory is a partial-sector
-// write over NVLink (measured on 2 B200s: 150M of them take 185 ms, 0.8 G/s), so the links do not
-// go to their slots directly.  A block of 1024 sorted entries sorts its (local slot index,
-// successor) messages by destination rank in shared memory and appends each destination's run to
-// this sender's region of that rank's inbox with consecutive threads on consecutive addresses
-// (full sectors, large NVLink packets); the destination scatters its inbox locally
-// (k_succ_apply).  The head of every player's run also sends the player's pair from the owner's
-// table shard to the mailbox of the rank that rates the player's first match (a full 32-byte row).
-constexpr int kRouteItems = 4, kRouteTile = 256 * kRouteItems;
+// write over NVLink (measured on 2 B200s: 150M of them take 185 ms, 0.8 G/s; scripts/nvlink_probe.py),
+// so the links do not go to their slots directly.  A block of kRouteTile sorted entries sorts its
+// (local slot index, successor) messages by bucket = (destination rank, range of the destination's
+// slots) in shared memory and appends each bucket's run to this sender's region of that rank's inbox
+// with consecutive threads on consecutive addresses (full sectors, large NVLink packets); the
+// destination scatters its inbox locally, one L2-sized range at a time (k_succ_apply), so every
+// sector of succ goes to HBM once, complete.  The head of every player's run also sends the
+// player's pair from the owner's table shard to the mailbox of the rank that rates the player's
+// first match (a full 32-byte row).
+constexpr int kRouteItems = 8, kRouteTile = 256 * kRouteItems, kRouteBuckets = 256;
 
 __global__ void __launch_bounds__(256)
 k_succ_route(const uint32_t *keys, const uint32_t *vals, const uint32_t *n_dev, ShardDst dst, unsigned long long *ctrl)
 {
-    __shared__ uint32_t s_cnt[TS_SHARD_MAX], s_start[TS_SHARD_MAX], s_base[TS_SHARD_MAX];
+    __shared__ uint32_t s_cnt[kRouteBuckets], s_start[kRouteBuckets + 1], s_base[kRouteBuckets];
     __shared__ unsigned long long s_msg[kRouteTile];
     const uint32_t n = __ldg(n_dev);
     const uint32_t tile_base = blockIdx.x * kRouteTile;
     if (tile_base >= n) return;
-    if (threadIdx.x < TS_SHARD_MAX) s_cnt[threadIdx.x] = 0;
+    const uint32_t n_buckets = (dst.g_mask + 1u) * dst.n_ranges;
+    s_cnt[threadIdx.x] = 0;
     __syncthreads();
     uint32_t off[kRouteItems], to[kRouteItems];
     unsigned long long msg[kRouteItems];
@@ -1390,9 +1394,10 @@ k_succ_route(const uint32_t *keys, const uint32_t *vals, const uint32_t *n_dev, 
         }
         const uint32_t blk = m >> 5, r = blk & dst.g_mask;
         const uint32_t lm = ((blk >> dst.g_shift) << 5) | (m & 31u);
-        to[j] = r;
-        msg[j] = ((unsigned long long)nxt << 32) | (unsigned long long)(lm * dst.slots + sl);
-        off[j] = atomicAdd(&s_cnt[r], 1u);
+        const uint32_t lv = lm * dst.slots + sl;
+        to[j] = r * dst.n_ranges + min(lv >> dst.range_shift, dst.n_ranges - 1u);
+        msg[j] = ((unsigned long long)nxt << 32) | (unsigned long long)lv;
+        off[j] = atomicAdd(&s_cnt[to[j]], 1u);
         if (i == 0 || __ldcs(keys + i - 1) != k) {            // the player's first match of the window
             const double2 pr = __ldg(reinterpret_cast<const double2 *>(dst.table_own) + k);
             const uint32_t pid = (k << dst.g_shift) | dst.owner;
@@ -1400,13 +1405,25 @@ k_succ_route(const uint32_t *keys, const uint32_t *vals, const uint32_t *n_dev, 
         }
     }
     __syncthreads();
-    if (threadIdx.x <= dst.g_mask) {
+    if (threadIdx.x < n_buckets) {
         const uint32_t c = s_cnt[threadIdx.x];
-        s_base[threadIdx.x] = c ? atomicAdd(&dst.out_count[threadIdx.x], c) : 0u;   // this block's place in every inbox
+        s_base[threadIdx.x] = c ? atomicAdd(&dst.out_count[threadIdx.x], c) : 0u;   // this block's place in every region
     }
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 32) {                                    // exclusive scan of the bucket counts, one warp
         uint32_t run = 0;
-        for (uint32_t g = 0; g <= dst.g_mask; ++g) { s_start[g] = run; run += s_cnt[g]; }
+        for (uint32_t b0 = 0; b0 < n_buckets; b0 += 32) {
+            const uint32_t b = b0 + threadIdx.x;
+            const uint32_t c = b < n_buckets ? s_cnt[b] : 0u;
+            uint32_t incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if (threadIdx.x >= (unsigned)o) incl += y;
+            }
+            if (b < n_buckets) s_start[b] = run + incl - c;
+            run += __shfl_sync(0xFFFFFFFFu, incl, 31);
+        }
+        if (threadIdx.x == 0) s_start[n_buckets] = run;
     }
     __syncthreads();
 #pragma unroll
@@ -1415,35 +1432,49 @@ k_succ_route(const uint32_t *keys, const uint32_t *vals, const uint32_t *n_dev, 
     __syncthreads();
     const uint32_t total = min((uint32_t)kRouteTile, n - tile_base);
     for (uint32_t pos = threadIdx.x; pos < total; pos += 256) {
-        uint32_t g = 0;
-        while (g < dst.g_mask && pos >= s_start[g + 1]) ++g;
-        const uint32_t idx = s_base[g] + (pos - s_start[g]);
-        if (idx < dst.inbox_cap) dst.inbox[g][(size_t)dst.owner * dst.inbox_cap + idx] = s_msg[pos];
+        uint32_t lo = 0, hi = n_buckets;                       // the bucket whose run holds pos
+        while (hi - lo > 1) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (s_start[mid] <= pos) lo = mid; else hi = mid;
+        }
+        const uint32_t idx = s_base[lo] + (pos - s_start[lo]);
+        const uint32_t g = lo / dst.n_ranges, range = lo - g * dst.n_ranges;
+        if (idx < dst.region_cap)
+            dst.inbox[g][((size_t)range * (dst.g_mask + 1u) + dst.owner) * dst.region_cap + idx] = s_msg[pos];
         else atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
     }
 }
 
-// after all messages are out: tell every rank how many this sender left in its inbox
+// after all messages are out: tell every rank how many this sender left in each of its regions
 __global__ void k_succ_counts(ShardDst dst)
 {
-    const uint32_t g = threadIdx.x;
-    if (g <= dst.g_mask) dst.inbox_count[g][dst.owner] = min(dst.out_count[g], dst.inbox_cap);
+    const uint32_t b = threadIdx.x;
+    if (b >= (dst.g_mask + 1u) * dst.n_ranges) return;
+    const uint32_t g = b / dst.n_ranges, range = b - g * dst.n_ranges;
+    dst.inbox_count[g][range * (dst.g_mask + 1u) + dst.owner] = min(dst.out_count[b], dst.region_cap);
 }
 
-// the receiving side, local: succ[local slot] = successor for every message of every sender;
-// destinations in [lo, hi) only (passes over ranges that L2 can hold, like k_pred)
+// the receiving side, local: succ[local slot] = successor for every message of every sender in one range
 __global__ void __launch_bounds__(256)
-k_succ_apply(const unsigned long long *inbox, const uint32_t *counts, uint32_t inbox_cap, uint32_t lo, uint32_t hi,
-             uint32_t *succ)
+k_succ_apply(const unsigned long long *regions, const uint32_t *counts, uint32_t region_cap, uint32_t *succ)
 {
     const uint32_t sender = blockIdx.y;
     const uint32_t n = __ldg(counts + sender);
-    const unsigned long long *src = inbox + (size_t)sender * inbox_cap;
+    const unsigned long long *src = regions + (size_t)sender * region_cap;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned long long msg = __ldcs(src + i);
-        const uint32_t lv = (uint32_t)msg;
-        if (lv >= lo && lv < hi) succ[lv] = (uint32_t)(msg >> 32);
+        succ[(uint32_t)msg] = (uint32_t)(msg >> 32);
     }
+}
+
+// How a rank's succ slice of `entries` slots is cut into ranges: 2^shift slots each, 16 Mi (64 MiB,
+// half an L2) unless that makes more buckets than the routing kernel sorts.
+void shard_ranges(uint64_t entries, int n_shards, uint32_t *n_ranges, uint32_t *shift)
+{
+    uint32_t sh = 24;
+    while (((entries + (1ull << sh) - 1) >> sh) * (uint64_t)n_shards > (uint64_t)kRouteBuckets) ++sh;
+    *shift = sh;
+    *n_ranges = (uint32_t)std::max<uint64_t>(1, (entries + (1ull << sh) - 1) >> sh);
 }
 
 int check_view(const ts_shard_view *v, const char *who)
@@ -1460,21 +1491,31 @@ int check_view(const ts_shard_view *v, const char *who)
 
 // the local half of the link exchange (called by ts_shard_rate before the rating kernel): rank `me`
 // scatters the messages its inbox holds into its succ slice
-int ts_shard_apply_links(const ts_shard_view *view, int me, int64_t n_local, int32_t slots, cudaStream_t s)
+int ts_shard_apply_links(const ts_shard_view *view, int me, int64_t n_matches, int32_t slots, cudaStream_t s)
 {
     const int G = view->n_shards;
-    const uint64_t entries = (uint64_t)n_local * (uint64_t)slots;
-    if (entries == 0) return 0;
-    // destination ranges of 16 Mi entries (64 MiB, half an L2) while that takes few passes over the inbox
-    uint64_t range = pred_range_entries();
-    if ((entries + range - 1) / range > 8) range = entries;
-    const unsigned blocks = (unsigned)std::min<int64_t>((view->inbox_cap + 1023) / 1024, 4096);
-    for (uint64_t lo = 0; lo < entries; lo += range)
-        k_succ_apply<<<dim3(blocks, (unsigned)G), 256, 0, s>>>(view->inbox[me], view->inbox_count[me], (uint32_t)view->inbox_cap,
-                                                            (uint32_t)lo, (uint32_t)std::min<uint64_t>(lo + range, entries),
-                                                            view->succ[me]);
+    uint32_t n_ranges = 1, shift = 24;
+    shard_ranges((uint64_t)ts_shard_local_matches(n_matches, 0, G) * (uint64_t)slots, G, &n_ranges, &shift);
+    const uint32_t region_cap = (uint32_t)(view->inbox_cap / n_ranges);
+    const unsigned blocks = (unsigned)std::min<uint32_t>((region_cap + 1023u) / 1024u, 2048u);
+    for (uint32_t r = 0; r < n_ranges; ++r)
+        k_succ_apply<<<dim3(blocks, (unsigned)G), 256, 0, s>>>(view->inbox[me] + (size_t)r * G * region_cap,
+                                                            view->inbox_count[me] + (size_t)r * G, region_cap, view->succ[me]);
     TS_CUDA(cudaGetLastError());
     return 0;
+}
+
+// Messages one sender may leave in one receiver's inbox for a window of n_matches: per range of the
+// receiver's slots its share of the range (a G-th, with room for uneven ownership), times the ranges.
+extern "C" int64_t ts_shard_inbox_cap(int64_t n_matches, int32_t slots, int32_t n_shards)
+{
+    if (n_matches < 0 || slots < 2 || n_shards < 1 || n_shards > TS_SHARD_MAX) return TS_E_ARG;
+    const uint64_t entries = (uint64_t)ts_shard_local_matches(n_matches, 0, n_shards) * (uint64_t)slots;
+    uint32_t n_ranges = 1, shift = 24;
+    shard_ranges(entries, n_shards, &n_ranges, &shift);
+    const uint64_t per_range = std::min<uint64_t>(entries, 1ull << shift);
+    const uint64_t region = n_shards == 1 ? per_range : std::min<uint64_t>(per_range, per_range * 13 / (10 * (uint64_t)n_shards) + 4096);
+    return (int64_t)(std::max<uint64_t>(region, 1) * n_ranges + kRouteBuckets);
 }
 
 extern "C" int64_t ts_shard_local_matches(int64_t n_matches, int32_t rank, int32_t n_shards)
@@ -1515,7 +1556,7 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
             ts_set_error("ts_shard_link: shard %d not mapped", g);
             return TS_E_ARG;
         }
-    if (view->inbox_cap < 1 || view->inbox_cap > 0x7FFFFFFFll) {
+    if (view->inbox_cap < kRouteBuckets || view->inbox_cap > 0x7FFFFFFFll) {
         ts_set_error("ts_shard_link: inbox_cap out of range");
         return TS_E_ARG;
     }
@@ -1577,8 +1618,11 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
         dst.rows[g] = g < G ? view->rows[g] : nullptr;
     }
     dst.table_own = view->table[rank];
-    dst.out_count = ticket + 16;                 // zeroed with the totals above
-    dst.inbox_cap = (uint32_t)view->inbox_cap;
+    // ranges of the largest slice (the slices differ by one block of 32 matches at most); same on every rank
+    shard_ranges((uint64_t)ts_shard_local_matches(n_matches, 0, G) * (uint64_t)slots, G, &dst.n_ranges, &dst.range_shift);
+    dst.region_cap = (uint32_t)(view->inbox_cap / dst.n_ranges);
+    dst.out_count = w.hist;                      // the sort's tile status rows are free again
+    TS_CUDA(cudaMemsetAsync(dst.out_count, 0, kRouteBuckets * 4, s));
     dst.g_mask = src.g_mask;
     dst.g_shift = src.g_shift;
     dst.owner = src.owner;
@@ -1586,7 +1630,7 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     dst.slots_magic = src.slots_magic;
     dst.seq_base = (uint32_t)seq_base;
     k_succ_route<<<(unsigned)((cap + kRouteTile - 1) / kRouteTile), 256, 0, s>>>(w.keys[buf], w.vals[buf], n_dev, dst, ctx->d_ctrl);
-    k_succ_counts<<<1, 32, 0, s>>>(dst);
+    k_succ_counts<<<1, kRouteBuckets, 0, s>>>(dst);
     TS_CUDA(cudaGetLastError());
     if (timing) {
         cudaEventRecord(tev[3], s);

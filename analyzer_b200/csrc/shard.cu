@@ -234,7 +234,7 @@ int check_shards(const ts_shard_view *v, const char *who)
 
 }  // namespace
 
-int ts_shard_apply_links(const ts_shard_view *view, int me, int64_t n_local, int32_t slots, cudaStream_t s);   // sched.cu
+int ts_shard_apply_links(const ts_shard_view *view, int me, int64_t n_matches, int32_t slots, cudaStream_t s);   // sched.cu
 
 extern "C" int ts_shard_alloc(int device, int64_t bytes, void **ptr, void *handle64)
 {
@@ -338,7 +338,7 @@ extern "C" int ts_shard_rate(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
             ts_set_error("ts_shard_rate: inbox of shard %d not mapped", g);
             return TS_E_ARG;
         }
-        if (int rc = ts_shard_apply_links(view, g, ts_shard_local_matches(n_matches, g, G), slots, s)) return rc;
+        if (int rc = ts_shard_apply_links(view, g, n_matches, slots, s)) return rc;
     }
     const bool hoist = stream_hoist_mode() != 0;
     a.prefetch = stream_prefetch_mode() != 0 ? 1u : 0u;

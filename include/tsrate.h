@@ -250,15 +250,17 @@ typedef struct ts_shard_view {
     uint32_t *succ[TS_SHARD_MAX];            /* [n_local(g)][slots], written by the players' owners */
     unsigned long long *rows[TS_SHARD_MAX];  /* mailbox: n_players rows of four 64-bit words      */
     double *table[TS_SHARD_MAX];             /* [ceil((n_players - g) / G)][2]                    */
-    unsigned long long *inbox[TS_SHARD_MAX]; /* link messages for rank g: [G senders][inbox_cap]  */
-    uint32_t *inbox_count[TS_SHARD_MAX];     /* [G]: messages each sender left in rank g's inbox  */
-    int64_t inbox_cap;                       /* about n_matches * slots / G^2, with room for skew */
+    unsigned long long *inbox[TS_SHARD_MAX]; /* link messages for rank g: G * inbox_cap of 8 bytes */
+    uint32_t *inbox_count[TS_SHARD_MAX];     /* 256 words: messages per (range of slots, sender)  */
+    int64_t inbox_cap;                       /* per sender: about n_matches * slots / G^2, with room for skew */
 } ts_shard_view;
 /* ts_shard_status bits */
 #define TS_SHARD_STALLED 1    /* a match's rows never arrived (watchdog): tables unusable      */
 #define TS_SHARD_OVERFLOW 2   /* ts_shard_link: workspace too small for the owned slots        */
 #define TS_SHARD_DUPLICATE 4  /* a player is listed twice in one match                          */
 int64_t ts_shard_local_matches(int64_t n_matches, int32_t rank, int32_t n_shards);
+/* inbox_cap to allocate for windows of up to n_matches (8 bytes per message, G senders per inbox) */
+int64_t ts_shard_inbox_cap(int64_t n_matches, int32_t slots, int32_t n_shards);
 /* workspace for ts_shard_link on a window of n_slot_entries = n_matches * slots: 8 bytes per slot
  * entry (staging of the compaction) plus the sort's buffers for `owned_cap` (player, slot) pairs;
  * a rank owns about n_slot_entries / n_shards of them (all of them in the worst case) */
