@@ -61,7 +61,8 @@ class TsShardView(C.Structure):
     _fields_ = [("rank", C.c_int32), ("n_shards", C.c_int32),
                 ("ids", C.c_void_p * 16), ("meta", C.c_void_p * 16), ("succ", C.c_void_p * 16),
                 ("rows", C.c_void_p * 16), ("table", C.c_void_p * 16), ("inbox", C.c_void_p * 16),
-                ("inbox_count", C.c_void_p * 16), ("inbox_cap", C.c_int64)]
+                ("inbox_count", C.c_void_p * 16), ("inbox_cap", C.c_int64), ("ring", C.c_void_p * 16),
+                ("ring_final", C.c_void_p * 16), ("ring_tail", C.c_void_p * 16), ("ring_cap", C.c_int64)]
 
 
 class TsGen(C.Structure):

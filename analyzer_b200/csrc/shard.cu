@@ -3,15 +3,27 @@
 //
 // Same dataflow rating as stream.cu -- matches in stream order, a match waits for
 // the rows of its players -- but rows are PUSHED to where they will be read:
-// every GPU has a mailbox of versioned rows (one per player), a rated match stores
-// each new row, tagged with the number of that player's NEXT match, into the
-// mailbox of the GPU that rates that match, and a match polls only its own GPU's
-// mailbox until every row carries the match's own number.  A hop between GPUs is
-// therefore one one-way NVLink store plus a local L2 poll; nothing ever polls
-// across NVLink.  After a player's last match the pair goes to the owner's table
-// shard (player p: GPU p % G, row p / G).  The tags are the only synchronisation
-// between GPUs: no barrier, no collective, no fence (every 8-byte word of a row
-// carries the tag, and 64-bit accesses are single-copy atomic).
+// every GPU has a mailbox of versioned rows (one per player), a rated match sends
+// each new row, tagged with the number of that player's NEXT match, to the GPU that
+// rates that match, and a match polls only its own GPU's mailbox until every row
+// carries the match's own number.  Nothing ever polls across NVLink.  After a
+// player's last match the pair goes back to the owner's table shard (player p:
+// GPU p % G, row p / G).  The tags are the only synchronisation between GPUs: no
+// barrier, no collective, no fence (every 8-byte word of a row carries the tag,
+// and 64-bit accesses are single-copy atomic).
+//
+// How a row crosses NVLink: NOT as a store to its mailbox slot.  Stores scattered
+// over several peers' memory collapse on B200 -- measured (scripts/nvlink_probe.py):
+// 8.4 G random 32-byte stores/s into one peer's 320 MB, 0.14 G/s when they spread
+// over seven peers, while stores to consecutive addresses keep 13 G/s (435 GB/s)
+// towards seven peers.  So a row for another GPU is a 32-byte MESSAGE (the pair,
+// the tag, the player) appended to this sender's ring in the receiver's memory --
+// the lanes of a warp that send to the same GPU reserve consecutive places with one
+// local atomic -- and a few ROUTER blocks of the receiver's own grid read their
+// rings in order and put every message into its mailbox row (or table row, for a
+// last match) with a local store.  A message validates itself like a row (a marker
+// byte in each of its four words); the sender's final count, published by its last
+// block, tells the routers when a ring is drained.
 //
 // Work split: blocks of 32 consecutive matches go round-robin to the GPUs, so
 // every GPU holds 1/G of the records and neighbouring blocks run in parallel.
@@ -40,6 +52,9 @@ struct PushArgs {
     uint32_t seq_base;
     uint32_t sleep_ns, max_spins;
     uint32_t prefetch;
+    uint32_t router_blocks;       // blocks of every rank's grid that route incoming messages (0 when there is one rank)
+    uint32_t window_gen;          // number of this window + 1: what this launch's final counts carry
+    uint32_t ring_cap;            // messages one sender may leave in one receiver's ring
     ts_outputs out;
     unsigned long long *ctrl;
 };
@@ -47,6 +62,94 @@ struct PushArgs {
 __device__ __forceinline__ void st_pair_sys(double *p, double mu, double sigma)
 {
     asm volatile("st.relaxed.sys.global.v2.f64 [%0], {%1, %2};" ::"l"(p), "d"(mu), "d"(sigma) : "memory");
+}
+
+// A message: four 64-bit words, each [marker:8 | 24 bits of (player, tag)][32 bits of (mu, sigma)].
+// tag TS_NONE = the player's last match of the window: the pair goes to the owner's table shard.
+constexpr unsigned long long kMsgMarker = 0xA5ull;
+// ring_tail section of a rank (own use only), 32-bit words: [0..15] places reserved so far in every
+// receiver's ring (they grow over all windows of a run), [16] rating blocks done in this launch,
+// [32..47] messages this rank has consumed from every sender's ring up to the end of the last window.
+// A final count is a 64-bit word [window number + 1 | count], so that the one of an earlier window
+// is never taken for this window's.
+constexpr int kTailDone = TS_SHARD_MAX, kTailConsumed = 2 * TS_SHARD_MAX;
+
+__device__ __forceinline__ void st_message(unsigned long long *slot, uint32_t pid, uint32_t tag, double mu, double sigma)
+{
+    const unsigned long long m = (unsigned long long)__double_as_longlong(mu);
+    const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
+    const unsigned long long x0 = pid & 0xFFFFFFu, x1 = (pid >> 24) | ((tag & 0xFFFFu) << 8), x2 = tag >> 16;
+    const unsigned long long w0 = (kMsgMarker << 56) | (x0 << 32) | (m & 0xFFFFFFFFull);
+    const unsigned long long w1 = (kMsgMarker << 56) | (x1 << 32) | (m >> 32);
+    const unsigned long long w2 = (kMsgMarker << 56) | (x2 << 32) | (s & 0xFFFFFFFFull);
+    const unsigned long long w3 = (kMsgMarker << 56) | (s >> 32);
+    asm volatile("st.relaxed.sys.global.v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(slot), "l"(w0), "l"(w1), "l"(w2), "l"(w3) : "memory");
+}
+
+// Router warp: drains one sender's ring in this rank's memory.  The warps that share a ring take its
+// chunks of 32 * kRouteUnroll messages round-robin; a lane delivers each of its messages as soon as
+// that message is there, whatever the rest of the chunk does.
+constexpr int kRouteUnroll = 4;
+
+__device__ void route_ring(const PushArgs &a, uint32_t me, uint32_t sender, uint32_t phase, uint32_t n_phases, int wl)
+{
+    const unsigned long long *ring = a.view.ring[me] + (size_t)sender * a.ring_cap * 4;
+    const unsigned long long *final_word = a.view.ring_final[me] + sender;
+    unsigned long long *rows = a.view.rows[me];
+    double *table = a.view.table[me];
+    uint32_t *consumed = a.view.ring_tail[me] + kTailConsumed + sender;
+    const uint32_t start = *consumed;             // where the earlier windows of this run ended
+    uint32_t total = 0xFFFFFFFFu;                 // unknown until the sender's last block has published it
+    uint32_t spins = 0;
+    for (uint32_t chunk = phase;; chunk += n_phases) {
+        const uint32_t base = start + chunk * (32u * kRouteUnroll);
+        bool got[kRouteUnroll];
+#pragma unroll
+        for (int u = 0; u < kRouteUnroll; ++u) got[u] = false;
+        for (;;) {
+            if (total == 0xFFFFFFFFu) {
+                unsigned long long f;
+                asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(f) : "l"(final_word) : "memory");
+                if ((uint32_t)(f >> 32) == a.window_gen) total = min((uint32_t)f, a.ring_cap);
+            }
+            if (base >= total) {                  // everything this warp is responsible for has been delivered
+                if (phase == 0 && wl == 0) *consumed = total;      // the next window starts here (stream order: visible to the next launch)
+                return;
+            }
+            unsigned long long w[kRouteUnroll][4];
+#pragma unroll
+            for (int u = 0; u < kRouteUnroll; ++u) {
+                const uint32_t i = base + u * 32 + wl;
+                if (!got[u] && i < total) ld_row<true>(ring + (size_t)i * 4, w[u]);
+            }
+            bool all = true;
+#pragma unroll
+            for (int u = 0; u < kRouteUnroll; ++u) {
+                const uint32_t i = base + u * 32 + wl;
+                if (got[u]) continue;
+                if (i >= total) { if (total != 0xFFFFFFFFu) got[u] = true; else all = false; continue; }
+                if ((w[u][0] >> 56) == kMsgMarker && (w[u][1] >> 56) == kMsgMarker && (w[u][2] >> 56) == kMsgMarker &&
+                    (w[u][3] >> 56) == kMsgMarker) {
+                    const uint32_t x0 = (uint32_t)(w[u][0] >> 32) & 0xFFFFFFu, x1 = (uint32_t)(w[u][1] >> 32) & 0xFFFFFFu,
+                                   x2 = (uint32_t)(w[u][2] >> 32) & 0xFFFFFFu;
+                    const uint32_t pid = x0 | ((x1 & 0xFFu) << 24), tag = (x1 >> 8) | (x2 << 16);
+                    const double mu = __longlong_as_double((long long)((w[u][0] & 0xFFFFFFFFull) | (w[u][1] << 32)));
+                    const double sg = __longlong_as_double((long long)((w[u][2] & 0xFFFFFFFFull) | (w[u][3] << 32)));
+                    if (tag != TS_NONE) st_row<true>(rows + (size_t)pid * 4, mu, sg, tag);
+                    else st_pair_sys(table + (size_t)(pid >> a.g_shift) * 2, mu, sg);
+                    got[u] = true;
+                } else {
+                    all = false;
+                }
+            }
+            if (__all_sync(0xFFFFFFFFu, all)) break;
+            if ((++spins & 0x3FFu) == 0u) {
+                if (spins >= a.max_spins && wl == 0) atomicExch(&a.ctrl[CTRL_STALLED], 1ull);
+                if (ld_relaxed_u64(&a.ctrl[CTRL_STALLED]) != 0ull) return;
+            }
+            __nanosleep(a.sleep_ns);
+        }
+    }
 }
 
 // matches of the window that live on rank r
@@ -72,8 +175,19 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
     const int grp = wl / L;
     WarpStage<P, W> &stage = stage_all[threadIdx.x >> 5];
     const uint32_t me = EMU ? (blockIdx.x & a.g_mask) : (uint32_t)a.view.rank;
-    const uint32_t block_of_rank = EMU ? (blockIdx.x >> a.g_shift) : blockIdx.x;
-    const uint32_t blocks_of_rank = EMU ? (gridDim.x >> a.g_shift) : gridDim.x;
+    const uint32_t grid_block = EMU ? (blockIdx.x >> a.g_shift) : blockIdx.x;
+    const uint32_t grid_blocks = EMU ? (gridDim.x >> a.g_shift) : gridDim.x;
+    if (grid_block < a.router_blocks) {
+        // router: warp rw of this rank's routers serves sender (rw % senders), phase rw / senders
+        const uint32_t senders = a.g_mask, rw = grid_block * kWarps + (threadIdx.x >> 5);
+        const uint32_t n_phases = (a.router_blocks * kWarps) / senders;
+        if (rw >= n_phases * senders) return;
+        const uint32_t si = rw % senders;
+        route_ring(a, me, si < me ? si : si + 1u, rw / senders, n_phases, wl);
+        return;
+    }
+    const uint32_t block_of_rank = grid_block - a.router_blocks;
+    const uint32_t blocks_of_rank = grid_blocks - a.router_blocks;
     const uint32_t *ids = a.view.ids[me], *meta_arr = a.view.meta[me], *succ = a.view.succ[me];
     unsigned long long *rows = a.view.rows[me];
     PassEnv env;
@@ -164,20 +278,38 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
             const int status = rate_pass<P, L, SPL>(env, lane, first, draw_eff, pid, used, bad_id, q_mu, q_sg, mu2, sg2,
                                                     d_q, ss_q, n);
             const bool ok = status == TS_ST_OK;
+            // Where every new row goes: the GPU that rates the player's next match (under that match's
+            // number), or the player's owner after the last match of the window.  Own GPU: a local store.
+            // Another GPU: a message in its ring -- the lanes that send to the same GPU take consecutive
+            // places, reserved by one of them with a local atomic (all reservations of a pass are issued
+            // before any is used).
+            uint32_t to[SPL], grp_mask[SPL], place[SPL];
+#pragma unroll
+            for (int k = 0; k < SPL; ++k) {
+                const bool send = go && used[k];
+                to[k] = !send ? 0xFFu : (next[k] != TS_NONE ? ((next[k] - a.seq_base) >> 5) & a.g_mask : pid[k] & a.g_mask);
+                if (to[k] == me) {
+                    if (next[k] != TS_NONE) st_row<true>(rows + (size_t)pid[k] * 4, mu2[k], sg2[k], next[k]);
+                    else st_pair_sys(a.view.table[me] + (size_t)(pid[k] >> a.g_shift) * 2, mu2[k], sg2[k]);
+                    to[k] = 0xFFu;
+                }
+                grp_mask[k] = __match_any_sync(0xFFFFFFFFu, to[k]);
+                place[k] = 0;
+                if (to[k] != 0xFFu && wl == __ffs(grp_mask[k]) - 1)
+                    place[k] = atomicAdd(a.view.ring_tail[me] + to[k], (uint32_t)__popc(grp_mask[k]));
+            }
 #pragma unroll
             for (int k = 0; k < SPL; ++k) {
                 const int s = lane + k * L;
-                if (go && used[k]) {
-                    if (next[k] != TS_NONE) {
-                        // to the mailbox of the GPU that rates the player's next match, under that match's number
-                        const uint32_t to = ((next[k] - a.seq_base) >> 5) & a.g_mask;
-                        st_row<true>(a.view.rows[to] + (size_t)pid[k] * 4, mu2[k], sg2[k], next[k]);
-                    } else {
-                        // the player's last match of the window: back to the owner's table shard
-                        st_pair_sys(a.view.table[pid[k] & a.g_mask] + (size_t)(pid[k] >> a.g_shift) * 2, mu2[k], sg2[k]);
-                    }
-                    if (ok && a.out.out_queue) st_pair_stream(a.out.out_queue + ((size_t)om * P + s) * 2, mu2[k], sg2[k], pol);
+                const uint32_t at = __shfl_sync(0xFFFFFFFFu, place[k], __ffs(grp_mask[k]) - 1) +
+                                    __popc(grp_mask[k] & ((1u << wl) - 1u));
+                if (to[k] != 0xFFu) {
+                    if (at < a.ring_cap)
+                        st_message(a.view.ring[to[k]] + ((size_t)me * a.ring_cap + at) * 4, pid[k], next[k], mu2[k], sg2[k]);
+                    else atomicOr(&a.ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
                 }
+                if (go && used[k] && ok && a.out.out_queue)
+                    st_pair_stream(a.out.out_queue + ((size_t)om * P + s) * 2, mu2[k], sg2[k], pol);
             }
             if (go) {
                 if (lane == 0) {
@@ -186,6 +318,24 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
                     else if (a.out.quality) a.out.quality[om] = match_quality(d_q, ss_q, n, env.beta2);
                 }
                 done = true;
+            }
+        }
+    }
+    // The last rating block of this rank to finish tells every receiver how many messages this
+    // sender left in its ring (the routers there stop when they have delivered that many).
+    if (a.g_mask != 0u) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t *tail = a.view.ring_tail[me];
+            __threadfence();
+            if (atomicAdd(tail + kTailDone, 1u) == blocks_of_rank - 1u) {
+                __threadfence();
+                tail[kTailDone] = 0;                               // for the next launch
+                for (uint32_t g = 0; g <= a.g_mask; ++g) {
+                    if (g == me) continue;
+                    const unsigned long long f = ((unsigned long long)a.window_gen << 32) | atomicAdd(tail + g, 0u);
+                    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(a.view.ring_final[g] + me), "l"(f) : "memory");
+                }
             }
         }
     }
@@ -203,8 +353,21 @@ int launch_push(ts_ctx *ctx, const PushArgs &args, bool emulate, bool hoist, cud
     unsigned blocks = (unsigned)(ctx->sm_count * per_sm);
     if (emulate) blocks &= ~(unsigned)args.g_mask;         // the same number of blocks for every played rank
     if (blocks == 0) { ts_set_error("ts_shard_rate: more ranks to play than resident blocks"); return TS_E_UNSUPPORTED; }
+    // router blocks per rank: a sixteenth of the rank's grid (TSRATE_SHARD_ROUTERS overrides), at least one
+    // warp per sender, and rating blocks must remain
+    PushArgs a = args;
+    const unsigned per_rank = emulate ? blocks >> a.g_shift : blocks;
+    a.router_blocks = 0;
+    if (a.g_mask != 0u) {
+        const char *e = getenv("TSRATE_SHARD_ROUTERS");
+        unsigned want = e ? (unsigned)atoi(e) : per_rank / 16u;
+        const unsigned least = (a.g_mask + 7u) / 8u;
+        want = want < least ? least : want;
+        if (want + 1u > per_rank) { ts_set_error("ts_shard_rate: too few resident blocks for %u ranks", a.g_mask + 1u); return TS_E_UNSUPPORTED; }
+        a.router_blocks = want;
+    }
     dim3 grid(blocks), block(kBlock);
-    void *kargs[] = {(void *)&args};
+    void *kargs[] = {(void *)&a};
     // cooperative launch only for its guarantee that the whole grid is resident
     TS_CUDA(cudaLaunchCooperativeKernel(fn, grid, block, kargs, 0, stream));
     return 0;
@@ -274,6 +437,15 @@ extern "C" int ts_shard_reset(ts_ctx *ctx, const ts_shard_view *view, int64_t n_
     TS_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
     TS_CUDA(cudaMemsetAsync(view->rows[view->rank], 0xFF, (size_t)n_players * 32, s));
+    if (view->n_shards > 1) {          // no message, no final count, no reservation
+        if (!view->ring[view->rank] || !view->ring_final[view->rank] || !view->ring_tail[view->rank] || view->ring_cap < 1) {
+            ts_set_error("ts_shard_reset: rings not mapped");
+            return TS_E_ARG;
+        }
+        TS_CUDA(cudaMemsetAsync(view->ring[view->rank], 0, (size_t)view->n_shards * (size_t)view->ring_cap * 32, s));
+        TS_CUDA(cudaMemsetAsync(view->ring_final[view->rank], 0, TS_SHARD_MAX * 8, s));
+        TS_CUDA(cudaMemsetAsync(view->ring_tail[view->rank], 0, 3 * TS_SHARD_MAX * 4, s));
+    }
     TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_STALLED, 0, sizeof(unsigned long long), s));
     TS_CUDA(cudaMemsetAsync(ctx->d_ctrl + CTRL_SHARD, 0, sizeof(unsigned long long), s));
     return 0;
@@ -307,11 +479,16 @@ extern "C" int ts_shard_rate(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     }
     if (n_matches == 0) return 0;
     for (int g = 0; g < G; ++g) {
-        const bool need_records = emulate_all || g == view->rank;
-        if (!view->rows[g] || !view->table[g] || (need_records && (!view->ids[g] || !view->meta[g] || !view->succ[g]))) {
+        const bool mine = emulate_all || g == view->rank;
+        if (!view->rows[g] || !view->table[g] || (mine && (!view->ids[g] || !view->meta[g] || !view->succ[g])) ||
+            (G > 1 && (!view->ring[g] || !view->ring_final[g] || (mine && !view->ring_tail[g])))) {
             ts_set_error("ts_shard_rate: shard %d not mapped", g);
             return TS_E_ARG;
         }
+    }
+    if (G > 1 && (view->ring_cap < 1 || view->ring_cap > 0x7FFFFFFFll)) {
+        ts_set_error("ts_shard_rate: ring_cap out of range");
+        return TS_E_ARG;
     }
     TS_CUDA(cudaSetDevice(ctx->device));
     PushArgs a;
@@ -326,6 +503,9 @@ extern "C" int ts_shard_rate(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     a.seq_base = (uint32_t)seq_base;
     a.sleep_ns = stream_sleep_ns();
     a.max_spins = stream_max_spins();
+    a.router_blocks = 0;
+    a.ring_cap = (uint32_t)(G > 1 ? view->ring_cap : 0);
+    a.window_gen = (uint32_t)(seq_base / TS_SHARD_BLOCK) + 1u;
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;

@@ -112,12 +112,23 @@ def inbox_capacity(n_matches_cap, slots, world):
     return L.check(L.lib().ts_shard_inbox_cap(n_matches_cap, slots, world))
 
 
-def arena_layout(n_players, n_matches_cap, slots, rank, world):
-    """Byte offsets of (rows, table, ids, meta, succ, inbox, inbox counts) in rank's arena, and
-    its size.  Every rank computes every rank's layout: peers' pointers are base + offset."""
+def ring_capacity(n_players, n_total, slots, world):
+    """Row messages one sender may leave with one receiver over a whole ladder of n_total matches:
+    its share of the rows that change GPU, plus the last rows going home, with room for skew."""
+    if world == 1:
+        return 1
+    return int((n_total * slots + n_players) / (world * world) * 1.3) + (1 << 16)
+
+
+def arena_layout(n_players, n_matches_cap, slots, rank, world, n_total=None):
+    """Byte offsets of (rows, table, ids, meta, succ, inbox, inbox counts, ring, ring finals, ring
+    tails) in rank's arena, and its size.  Every rank computes every rank's layout: peers'
+    pointers are base + offset."""
     nl = local_matches(n_matches_cap, rank, world)
+    ring = ring_capacity(n_players, n_total if n_total is not None else n_matches_cap, slots, world)
     sizes = (n_players * ROW_BYTES, max(1, shard_rows(n_players, rank, world)) * 16, max(1, nl) * slots * 4,
-             max(1, nl) * 4, max(1, nl) * slots * 4, world * inbox_capacity(n_matches_cap, slots, world) * 8, 1024)
+             max(1, nl) * 4, max(1, nl) * slots * 4, world * inbox_capacity(n_matches_cap, slots, world) * 8, 1024,
+             world * ring * 32, 128, 256)
     offs, o = [], 0
     for sz in sizes:
         offs.append(o)
@@ -133,7 +144,9 @@ class _Raw(object):
 
 
 class ShardedLadder(object):
-    def __init__(self, rater, n_players, n_matches_cap, slots, rank=0, world=1, group=None, emulate=False):
+    def __init__(self, rater, n_players, n_matches_cap, slots, rank=0, world=1, group=None, emulate=False, n_total=None):
+        """n_matches_cap: the largest window; n_total: matches of the whole ladder when it is rated in
+        several windows (the message rings are sized for the run; default: one window)."""
         if world & (world - 1) or not 1 <= world <= L.SHARD_MAX:
             raise ValueError("world size must be a power of two <= %d" % L.SHARD_MAX)
         if n_matches_cap * slots >= 0xFFFF0000:
@@ -143,7 +156,8 @@ class ShardedLadder(object):
         self.lib = L.lib()
         self.device = rater.device.index or 0
         dev = torch.device("cuda", self.device)
-        self.layouts = [arena_layout(n_players, n_matches_cap, slots, g, world) for g in range(world)]
+        self.n_total = n_total if n_total is not None else n_matches_cap
+        self.layouts = [arena_layout(n_players, n_matches_cap, slots, g, world, self.n_total) for g in range(world)]
         self.bases = [0] * world
         self.opened, self.own = [], None
         self._keep = []
@@ -192,7 +206,9 @@ class ShardedLadder(object):
             v.rows[g], v.table[g] = self.bases[g] + offs[0], self.bases[g] + offs[1]
             v.ids[g], v.meta[g], v.succ[g] = self.bases[g] + offs[2], self.bases[g] + offs[3], self.bases[g] + offs[4]
             v.inbox[g], v.inbox_count[g] = self.bases[g] + offs[5], self.bases[g] + offs[6]
+            v.ring[g], v.ring_final[g], v.ring_tail[g] = self.bases[g] + offs[7], self.bases[g] + offs[8], self.bases[g] + offs[9]
         v.inbox_cap = inbox_capacity(self.cap, self.slots, self.world)
+        v.ring_cap = ring_capacity(self.n_players, self.n_total, self.slots, self.world)
         return v
 
     def _stream(self):

@@ -220,12 +220,16 @@ int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, cons
  * Table: player p is owned by rank p % G (local row p / G): the owner holds the
  * player's (mu, sigma) before the first and after the last match of a window.
  * Rows travel to where they are needed: every rank has a mailbox of n_players
- * versioned rows (32 bytes each); the rank that rates a player's match stores the new
- * row, tagged with the number of the player's NEXT match, into the mailbox of the rank
- * that will rate that match (one one-way NVLink store), and a match polls only its own
- * GPU's mailbox until every row carries the match's own number.  After a player's last
- * match the pair goes back to the owner's table shard.  No inter-GPU barrier and no
- * collective while rating.
+ * versioned rows (32 bytes each); the rank that rates a player's match sends the new
+ * row, tagged with the number of the player's NEXT match, to the rank that will rate
+ * that match, and a match polls only its own GPU's mailbox until every row carries the
+ * match's own number.  A row for another GPU is a 32-byte message appended to the
+ * sender's ring in the receiver's memory (consecutive addresses: scattered stores over
+ * several peers' memory collapse on B200), and router blocks of the receiver's own grid
+ * put it into its mailbox row.  After a player's last match the pair goes back to the
+ * owner's table shard the same way.  No inter-GPU barrier and no collective while
+ * rating.  ts_shard_reset clears mailbox, rings and counts before a ladder's first window;
+ * every window's messages are appended behind the earlier ones (size ring_cap for the run).
  * Links: ts_shard_link reads the whole id stream once (its peers' slices over NVLink),
  * keeps the slots of the players it owns, sorts them, and sends succ[m][s] (the
  * stream-wide number of that player's next rated match, TS_NONE if none) to the rank
@@ -253,6 +257,10 @@ typedef struct ts_shard_view {
     unsigned long long *inbox[TS_SHARD_MAX]; /* link messages for rank g: G * inbox_cap of 8 bytes */
     uint32_t *inbox_count[TS_SHARD_MAX];     /* 256 words: messages per (range of slots, sender)  */
     int64_t inbox_cap;                       /* per sender: about n_matches * slots / G^2, with room for skew */
+    unsigned long long *ring[TS_SHARD_MAX];  /* row messages for rank g: [G senders][ring_cap] of 32 bytes   */
+    unsigned long long *ring_final[TS_SHARD_MAX]; /* [16]: every sender's final message count for rank g      */
+    uint32_t *ring_tail[TS_SHARD_MAX];       /* [48], own rank only: places reserved, blocks done, consumed   */
+    int64_t ring_cap;                        /* per sender: about (n_matches * slots + n_players) / G^2 + skew */
 } ts_shard_view;
 /* ts_shard_status bits */
 #define TS_SHARD_STALLED 1    /* a match's rows never arrived (watchdog): tables unusable      */

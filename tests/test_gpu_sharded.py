@@ -93,7 +93,7 @@ def test_emulated_windows_equal_one_shot():
     full = engine.gen_table(seed, 0, u, dev).reshape(u, 2)
     want, _ = _single(engine, r, ids, meta, full, u)
     win = 32 * world * 100                      # windows start at multiples of 32 * world
-    ladder = sharded.ShardedLadder(r, u, win, slots, 0, world, emulate=True)
+    ladder = sharded.ShardedLadder(r, u, win, slots, 0, world, emulate=True, n_total=n)    # rings sized for the whole run
     ladder.set_table(full)
     for lo in range(0, n, win):
         hi = min(n, lo + win)
