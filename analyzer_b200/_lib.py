@@ -62,7 +62,7 @@ class TsShardView(C.Structure):
                 ("ids", C.c_void_p * 16), ("meta", C.c_void_p * 16), ("succ", C.c_void_p * 16),
                 ("rows", C.c_void_p * 16), ("table", C.c_void_p * 16), ("inbox", C.c_void_p * 16),
                 ("inbox_count", C.c_void_p * 16), ("inbox_cap", C.c_int64), ("ring", C.c_void_p * 16),
-                ("ring_final", C.c_void_p * 16), ("ring_tail", C.c_void_p * 16), ("ring_cap", C.c_int64)]
+                ("ring_final", C.c_void_p * 16), ("ring_tail", C.c_void_p * 16), ("ring_cap", C.c_int64), ("ring_epoch", C.c_int64)]
 
 
 class TsGen(C.Structure):

@@ -54,6 +54,8 @@ struct PushArgs {
     uint32_t prefetch;
     uint32_t router_blocks;       // blocks of every rank's grid that route incoming messages (0 when there is one rank)
     uint32_t window_gen;          // number of this window + 1: what this launch's final counts carry
+    uint32_t epoch;               // 1..255: the marker byte of this run's messages
+    uint32_t direct;              // 1: rows go straight into the receiver's mailbox (no rings, no routers)
     uint32_t ring_cap;            // messages one sender may leave in one receiver's ring
     ts_outputs out;
     unsigned long long *ctrl;
@@ -66,7 +68,7 @@ __device__ __forceinline__ void st_pair_sys(double *p, double mu, double sigma)
 
 // A message: four 64-bit words, each [marker:8 | 24 bits of (player, tag)][32 bits of (mu, sigma)].
 // tag TS_NONE = the player's last match of the window: the pair goes to the owner's table shard.
-constexpr unsigned long long kMsgMarker = 0xA5ull;
+// (the marker is the run's epoch, 1..255, counted by ts_shard_reset: a ring need not be cleared between runs)
 // ring_tail section of a rank (own use only), 32-bit words: [0..15] places reserved so far in every
 // receiver's ring (they grow over all windows of a run), [16] rating blocks done in this launch,
 // [32..47] messages this rank has consumed from every sender's ring up to the end of the last window.
@@ -74,7 +76,8 @@ constexpr unsigned long long kMsgMarker = 0xA5ull;
 // is never taken for this window's.
 constexpr int kTailDone = TS_SHARD_MAX, kTailConsumed = 2 * TS_SHARD_MAX;
 
-__device__ __forceinline__ void st_message(unsigned long long *slot, uint32_t pid, uint32_t tag, double mu, double sigma)
+__device__ __forceinline__ void st_message(unsigned long long *slot, uint32_t pid, uint32_t tag, double mu, double sigma,
+                                           unsigned long long kMsgMarker)
 {
     const unsigned long long m = (unsigned long long)__double_as_longlong(mu);
     const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
@@ -128,6 +131,7 @@ __device__ void route_ring(const PushArgs &a, uint32_t me, uint32_t sender, uint
                 const uint32_t i = base + u * 32 + wl;
                 if (got[u]) continue;
                 if (i >= total) { if (total != 0xFFFFFFFFu) got[u] = true; else all = false; continue; }
+                const unsigned long long kMsgMarker = a.epoch;
                 if ((w[u][0] >> 56) == kMsgMarker && (w[u][1] >> 56) == kMsgMarker && (w[u][2] >> 56) == kMsgMarker &&
                     (w[u][3] >> 56) == kMsgMarker) {
                     const uint32_t x0 = (uint32_t)(w[u][0] >> 32) & 0xFFFFFFu, x1 = (uint32_t)(w[u][1] >> 32) & 0xFFFFFFu,
@@ -288,9 +292,9 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
             for (int k = 0; k < SPL; ++k) {
                 const bool send = go && used[k];
                 to[k] = !send ? 0xFFu : (next[k] != TS_NONE ? ((next[k] - a.seq_base) >> 5) & a.g_mask : pid[k] & a.g_mask);
-                if (to[k] == me) {
-                    if (next[k] != TS_NONE) st_row<true>(rows + (size_t)pid[k] * 4, mu2[k], sg2[k], next[k]);
-                    else st_pair_sys(a.view.table[me] + (size_t)(pid[k] >> a.g_shift) * 2, mu2[k], sg2[k]);
+                if (to[k] == me || (a.direct && to[k] != 0xFFu)) {
+                    if (next[k] != TS_NONE) st_row<true>(a.view.rows[to[k]] + (size_t)pid[k] * 4, mu2[k], sg2[k], next[k]);
+                    else st_pair_sys(a.view.table[to[k]] + (size_t)(pid[k] >> a.g_shift) * 2, mu2[k], sg2[k]);
                     to[k] = 0xFFu;
                 }
                 grp_mask[k] = __match_any_sync(0xFFFFFFFFu, to[k]);
@@ -305,7 +309,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
                                     __popc(grp_mask[k] & ((1u << wl) - 1u));
                 if (to[k] != 0xFFu) {
                     if (at < a.ring_cap)
-                        st_message(a.view.ring[to[k]] + ((size_t)me * a.ring_cap + at) * 4, pid[k], next[k], mu2[k], sg2[k]);
+                        st_message(a.view.ring[to[k]] + ((size_t)me * a.ring_cap + at) * 4, pid[k], next[k], mu2[k], sg2[k], a.epoch);
                     else atomicOr(&a.ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
                 }
                 if (go && used[k] && ok && a.out.out_queue)
@@ -323,7 +327,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
     }
     // The last rating block of this rank to finish tells every receiver how many messages this
     // sender left in its ring (the routers there stop when they have delivered that many).
-    if (a.g_mask != 0u) {
+    if (a.g_mask != 0u && !a.direct) {
         __syncthreads();
         if (threadIdx.x == 0) {
             uint32_t *tail = a.view.ring_tail[me];
@@ -358,7 +362,7 @@ int launch_push(ts_ctx *ctx, const PushArgs &args, bool emulate, bool hoist, cud
     PushArgs a = args;
     const unsigned per_rank = emulate ? blocks >> a.g_shift : blocks;
     a.router_blocks = 0;
-    if (a.g_mask != 0u) {
+    if (a.g_mask != 0u && !a.direct) {
         const char *e = getenv("TSRATE_SHARD_ROUTERS");
         unsigned want = e ? (unsigned)atoi(e) : per_rank / 16u;
         const unsigned least = (a.g_mask + 7u) / 8u;
@@ -442,7 +446,9 @@ extern "C" int ts_shard_reset(ts_ctx *ctx, const ts_shard_view *view, int64_t n_
             ts_set_error("ts_shard_reset: rings not mapped");
             return TS_E_ARG;
         }
-        TS_CUDA(cudaMemsetAsync(view->ring[view->rank], 0, (size_t)view->n_shards * (size_t)view->ring_cap * 32, s));
+        // a run's messages carry its epoch as marker: the rings are cleared only when the epochs start over
+        if (view->ring_epoch <= 1)
+            TS_CUDA(cudaMemsetAsync(view->ring[view->rank], 0, (size_t)view->n_shards * (size_t)view->ring_cap * 32, s));
         TS_CUDA(cudaMemsetAsync(view->ring_final[view->rank], 0, TS_SHARD_MAX * 8, s));
         TS_CUDA(cudaMemsetAsync(view->ring_tail[view->rank], 0, 3 * TS_SHARD_MAX * 4, s));
     }
@@ -506,6 +512,16 @@ extern "C" int ts_shard_rate(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     a.router_blocks = 0;
     a.ring_cap = (uint32_t)(G > 1 ? view->ring_cap : 0);
     a.window_gen = (uint32_t)(seq_base / TS_SHARD_BLOCK) + 1u;
+    a.epoch = (uint32_t)view->ring_epoch;
+    // Rows straight into the receivers' mailboxes while the peers' mailboxes together stay small enough
+    // for scattered stores (measured: 8.4 G stores/s into 320 MB of one peer, 5.7 G/s into 960 MB of three,
+    // 0.14 G/s into 2.2 GB of seven); beyond that, messages in rings.  TSRATE_SHARD_DIRECT=0/1 overrides.
+    const char *ed = getenv("TSRATE_SHARD_DIRECT");
+    a.direct = ed ? (atoi(ed) != 0) : ((int64_t)(G - 1) * n_players * 32 <= (512ll << 20));
+    if (G > 1 && !a.direct && (a.epoch < 1u || a.epoch > 255u)) {
+        ts_set_error("ts_shard_rate: ring_epoch must be 1..255 (ts_shard_reset hands it out)");
+        return TS_E_ARG;
+    }
     if (outputs) a.out = *outputs;
     else a.out = ts_outputs{nullptr, nullptr, nullptr, nullptr, nullptr};
     a.ctrl = ctx->d_ctrl;

@@ -196,6 +196,7 @@ class ShardedLadder(object):
             self.succ[g] = arena[offs[4]:offs[4] + nl * slots * 4].view(torch.int32).view(nl, slots)
         self._ws = None
         self._gbuf = None
+        self.epoch = 0
 
     def view(self, rank=None):
         v = L.TsShardView()
@@ -209,6 +210,7 @@ class ShardedLadder(object):
             v.ring[g], v.ring_final[g], v.ring_tail[g] = self.bases[g] + offs[7], self.bases[g] + offs[8], self.bases[g] + offs[9]
         v.inbox_cap = inbox_capacity(self.cap, self.slots, self.world)
         v.ring_cap = ring_capacity(self.n_players, self.n_total, self.slots, self.world)
+        v.ring_epoch = self.epoch
         return v
 
     def _stream(self):
@@ -232,6 +234,7 @@ class ShardedLadder(object):
             self.table[g].copy_(full.reshape(-1, 2)[g::self.world])
 
     def reset(self):
+        self.epoch = self.epoch + 1 if self.epoch < 255 else 1      # the marker of this run's messages; 1 = rings cleared
         with torch.cuda.device(self.device):
             for g in self.played:
                 v = self.view(g)

@@ -261,6 +261,7 @@ typedef struct ts_shard_view {
     unsigned long long *ring_final[TS_SHARD_MAX]; /* [16]: every sender's final message count for rank g      */
     uint32_t *ring_tail[TS_SHARD_MAX];       /* [48], own rank only: places reserved, blocks done, consumed   */
     int64_t ring_cap;                        /* per sender: about (n_matches * slots + n_players) / G^2 + skew */
+    int64_t ring_epoch;                      /* 1..255, the same on all ranks: +1 for every ts_shard_reset, 1 again after 255 */
 } ts_shard_view;
 /* ts_shard_status bits */
 #define TS_SHARD_STALLED 1    /* a match's rows never arrived (watchdog): tables unusable      */

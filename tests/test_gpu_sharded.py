@@ -26,10 +26,13 @@ def _single(engine, r, ids, meta, full, u, outputs=None):
     return single.reshape(u, 2), pred
 
 
-@pytest.mark.parametrize("world", [1, 2, 4, 8])
+@pytest.mark.parametrize("world,direct", [(1, "1"), (2, "1"), (2, "0"), (4, "0"), (8, "1"), (8, "0")])
 @pytest.mark.parametrize("slots,zipf,p_draw", CASES)
-def test_emulated_ranks_equal_single_gpu_and_oracle(c_oracle, world, slots, zipf, p_draw):
+def test_emulated_ranks_equal_single_gpu_and_oracle(c_oracle, monkeypatch, world, direct, slots, zipf, p_draw):
+    """direct = "1": rows stored straight into the receiver's mailbox; "0": as messages through the
+    rings and the receiver's router blocks (what larger ladders on more GPUs use)."""
     from analyzer_b200 import engine, sharded
+    monkeypatch.setenv("TSRATE_SHARD_DIRECT", direct)
     co = c_oracle
     dev = torch.device("cuda", 0)
     n, u, seed = 60_011, 3_001, 0xA11CE005
@@ -82,9 +85,11 @@ def test_emulated_ranks_equal_single_gpu_and_oracle(c_oracle, world, slots, zipf
     r.close()
 
 
-def test_emulated_windows_equal_one_shot():
+@pytest.mark.parametrize("direct", ["0", "1"])
+def test_emulated_windows_equal_one_shot(monkeypatch, direct):
     """A ladder rated window after window (the owners' table shards carry the state) equals one shot."""
     from analyzer_b200 import engine, sharded
+    monkeypatch.setenv("TSRATE_SHARD_DIRECT", direct)
     dev = torch.device("cuda", 0)
     world, slots = 4, 6
     n, u, seed = 40_000, 2_003, 0xA11CE006
@@ -157,17 +162,20 @@ def _worker(rank, world, port, results):
         want, _ = _single(engine, r, ids, meta, full, u)
         ladder = sharded.ShardedLadder(r, u, n, slots, rank, world)
         ladder.set_stream(ids, meta)
-        ladder.set_table(full)
-        ladder.run(n, mode=1)
-        errs = r.error_count()
-        mine = ladder.table[rank]
-        same = torch.equal(mine, want[rank::world]) and errs == 0        # bit for bit
-        if not same:
-            diff = (mine - want[rank::world]).abs()
-            print("sharded mismatch: rank", rank, "slots", slots, "errs", errs, "rows differing",
-                  int((diff > 0).any(dim=1).sum()), "max", float(diff.max()), flush=True)
-        ok = ok and same
-        dist.barrier()
+        for direct in ("1", "0"):           # rows straight into the peer's mailbox / as ring messages
+            os.environ["TSRATE_SHARD_DIRECT"] = direct
+            ladder.set_table(full)
+            ladder.run(n, mode=1)
+            errs = r.error_count()
+            mine = ladder.table[rank]
+            same = torch.equal(mine, want[rank::world]) and errs == 0        # bit for bit
+            if not same:
+                diff = (mine - want[rank::world]).abs()
+                print("sharded mismatch: rank", rank, "slots", slots, "direct", direct, "errs", errs, "rows differing",
+                      int((diff > 0).any(dim=1).sum()), "max", float(diff.max()), flush=True)
+            ok = ok and same
+            dist.barrier()
+        os.environ.pop("TSRATE_SHARD_DIRECT", None)
         ladder.close()
         r.close()
     results[rank] = ok
