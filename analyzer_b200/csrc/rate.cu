@@ -248,11 +248,11 @@ __global__ void __launch_bounds__(kBlock) k_rate(const RateArgs a)
             double v_s = 0.0, w_s = 0.0, rc_s = 0.0, v_q, w_q;
             if (SHARED) {
                 rc_s = rsqrt(c2_s);
-                if (!trunc_vw(d_s * rc_s, margin * rc_s, is_draw, a.prm.draw_is_zero != 0, v_s, w_s))
+                if (!trunc_vw(d_s * rc_s, margin * rc_s, is_draw, a.prm.draw_is_zero, v_s, w_s))
                     status = status ? status : TS_ST_FP_ERROR;
             }
             const double rc_q = rsqrt(c2_q);
-            if (!trunc_vw(d_q * rc_q, margin * rc_q, is_draw, a.prm.draw_is_zero != 0, v_q, w_q))
+            if (!trunc_vw(d_q * rc_q, margin * rc_q, is_draw, a.prm.draw_is_zero, v_q, w_q))
                 status = status ? status : TS_ST_FP_ERROR;
 
             const uint32_t m = (live && want_order) ? stage.order[cur][grp] : 0u;

@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
     env.margin_full = a.prm.draw_margin[P];
     env.margins = a.prm.draw_margin;
     env.seed = nullptr;
-    env.draw_is_zero = a.prm.draw_is_zero != 0;
+    env.draw_is_zero = a.prm.draw_is_zero;
     const uint32_t n_local = local_matches(a.n_matches, me, a.g_mask, a.g_shift);
     const uint32_t n_tiles = (n_local + W - 1) / W;
     const uint32_t stride = blocks_of_rank * kWarps;

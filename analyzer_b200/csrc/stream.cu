@@ -80,7 +80,7 @@ __global__ void __launch_bounds__(kBlock, TS_STREAM_MIN_BLOCKS) k_rate_stream(co
     env.margin_full = a.prm.draw_margin[P];
     env.margins = a.prm.draw_margin;
     env.seed = a.seed;
-    env.draw_is_zero = a.prm.draw_is_zero != 0;
+    env.draw_is_zero = a.prm.draw_is_zero;
     uint32_t rated_mask = 0;
 #pragma unroll
     for (int i = 0; i < 6; ++i) rated_mask |= a.modes.col[i] >= 0 ? (1u << i) : 0u;

@@ -196,7 +196,7 @@ struct PassEnv {
     double tau2, beta2, tb2, margin_full;
     const double *margins;       // draw margin by number of players (ragged teams)
     const double *seed;          // get_trueskill_seed per player, or nullptr
-    bool draw_is_zero;
+    int draw_is_zero;            // 0: draw margin in use; 1: draw_probability = 0, analytic limit; 2: such a draw fails
 };
 
 // One rating pass of the ladder layout (one (mu, sigma) pair per player; rater.py:132-169 with

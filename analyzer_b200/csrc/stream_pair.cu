@@ -284,8 +284,8 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_stream_pair(const PairArgs a
             double v_s = 0.0, w_s = 0.0, v_q = 0.0, w_q = 0.0;
             const double rc_s = rsqrt(c2_s), rc_q = rsqrt(c2_q);
             if (status == TS_ST_OK &&
-                (!trunc_vw(d_s * rc_s, margin * rc_s, draw_eff, a.prm.draw_is_zero != 0, v_s, w_s) ||
-                 !trunc_vw(d_q * rc_q, margin * rc_q, draw_eff, a.prm.draw_is_zero != 0, v_q, w_q)))
+                (!trunc_vw(d_s * rc_s, margin * rc_s, draw_eff, a.prm.draw_is_zero, v_s, w_s) ||
+                 !trunc_vw(d_q * rc_q, margin * rc_q, draw_eff, a.prm.draw_is_zero, v_q, w_q)))
                 status = TS_ST_FP_ERROR;
             const bool ok = status == TS_ST_OK;
 #pragma unroll

@@ -40,7 +40,7 @@ __device__ __forceinline__ double v_win_table(double x)
     return fma(q2, u8, fma(q1, u4, q0));
 }
 
-__device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, bool draw_is_zero, double &v, double &w)
+__device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, int draw_is_zero, double &v, double &w)
 {
     if (!is_draw) {
         const double x = t - eps;
@@ -57,6 +57,7 @@ __device__ __forceinline__ bool trunc_vw(double t, double eps, bool is_draw, boo
         if (x > 30.0 && w >= 0.0) { v = 0.0; w = 0.0; return true; }
         return false;
     }
+    if (draw_is_zero == 2) return false;   // the integrator asked for a draw at draw_probability = 0 to fail like the float backend
     if (draw_is_zero) {   // draw_probability = 0: limit of v_draw/w_draw for eps -> 0
         v = -t;
         w = 1.0;

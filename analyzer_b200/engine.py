@@ -52,7 +52,12 @@ class Env(object):
     """rater.py:30-37 -- beta, tau, draw_probability of the TrueSkill environment."""
 
     def __init__(self, beta=10.0 / 30 * 3000, tau=1000 / 100.0, draw_probability=0.0,
-                 mu=1500, sigma=1000):
+                 mu=1500, sigma=1000, zero_draw="limit"):
+        """zero_draw: what a draw (both winner flags equal) does at draw_probability = 0 -- "limit":
+        the analytic limit v = -t, w = 1 (what the 50-digit backend was found to land on; unpinned by
+        the reference); "raise": FloatingPointError for the batch, like the package's float backend."""
+        assert zero_draw in ("limit", "raise")
+        self.zero_draw = zero_draw
         self.mu, self.sigma = mu, sigma          # unused by the rating path (rater.py:121,132)
         self.beta, self.tau, self.draw_probability = float(beta), float(tau), float(draw_probability)
 
@@ -61,7 +66,7 @@ class Env(object):
         p.beta, p.tau = self.beta, self.tau
         for n in range(L.MAX_SLOTS + 1):
             p.draw_margin[n] = draw_margin(self.draw_probability, n, self.beta) if n else 0.0
-        p.draw_is_zero = 1 if self.draw_probability == 0 else 0
+        p.draw_is_zero = (2 if self.zero_draw == "raise" else 1) if self.draw_probability == 0 else 0
         return p
 
 

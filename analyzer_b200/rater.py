@@ -245,6 +245,167 @@ def _write_back(b, res):
             setattr(items, sg_col, sg)
 
 
+# ---------------------------------------------------------------------------
+# columnar ingest of the ROW STREAM (what the query of worker.py:176-191 yields,
+# one row per participant) and the rows its single commit (worker.py:194) flushes
+# -- no per-object, per-attribute Python anywhere
+# ---------------------------------------------------------------------------
+ROW_FIELDS = ("match", "game_mode", "n_rosters", "roster", "winner", "went_afk", "player", "skill_tier",
+              "rank_points_ranked", "rank_points_blitz", "trueskill_mu", "trueskill_sigma", "queue")
+
+
+class RowBatch(object):
+    """Columns of a batch ingested from participant rows, plus what maps results back to rows."""
+    __slots__ = ("ids", "meta", "table", "seed", "slots", "match_keys", "player_keys", "row_match", "row_slot",
+                 "row_player", "n_rows")
+
+
+_VST = np.array([vst_points[t] for t in range(-1, 30)])
+
+
+def _seed_columns(ranked, blitz, tier):
+    """get_trueskill_seed (rater.py:42-62) for whole columns; NaN = None.  A tier outside -1..29
+    with no rank points (the reference's KeyError) gives a NaN seed: such a player fails its
+    first rated match with a ValueError status instead."""
+    best = np.fmax(np.where(ranked == 0, np.nan, ranked), np.where(blitz == 0, np.nan, blitz))     # NaN only if both are
+    has = ~np.isnan(best)
+    t = np.asarray(tier, dtype=np.int64)
+    ok = (t >= -1) & (t <= 29)
+    s23 = UNKNOWN_PLAYER_SIGMA * (2.0 / 3.0)
+    out = np.empty((len(t), 2))
+    out[:, 0] = np.where(has, best + s23, np.where(ok, _VST[np.clip(t, -1, 29) + 1] + UNKNOWN_PLAYER_SIGMA, np.nan))
+    out[:, 1] = np.where(has, s23, np.where(ok, float(UNKNOWN_PLAYER_SIGMA), np.nan))
+    return out
+
+
+def _first_appearance(keys):
+    """(unique keys in order of first appearance, row -> index, first row of every key)"""
+    uk, first, inv = np.unique(keys, return_index=True, return_inverse=True)
+    order = np.argsort(first, kind="stable")
+    rank = np.empty(len(uk), dtype=np.int64)
+    rank[order] = np.arange(len(uk))
+    return uk[order], rank[inv], first[order]
+
+
+def ingest_rows(rows):
+    """Participant rows -> columns.  `rows`: a mapping (or numpy structured array) of equally long
+    columns, one entry per participant in the order the query yields them (matches by created_at,
+    worker.py:177):
+
+        match               any integer key of the match (first appearance fixes the stream order)
+        game_mode           0..5 in rater.py:70-82's order (casual, ranked, blitz, br, 5v5_casual,
+                            5v5_ranked), anything else = unsupported
+        n_rosters           len(match.rosters)                     (rater.py:91-93)
+        roster              0 / 1: which of the two rosters the participant is on
+        winner              that roster's .winner                   (rater.py:144)
+        went_afk            participant.went_afk                    (rater.py:95-100)
+        player              any integer key of the player (the identity the session's identity map shares)
+        skill_tier, rank_points_ranked, rank_points_blitz          (rater.py:42-62; NaN = None)
+        trueskill_mu, trueskill_sigma                              the player's shared pair (NaN = NULL)
+        queue               float64 [rows, 6, 2]: the player's six trueskill_<mode>_mu/_sigma pairs
+
+    Returns a RowBatch for Rater.rate_batch(b.ids, b.meta, b.table, seed=b.seed, shared_col=0,
+    mode_cols=(1, ..., 6)); updates(b, result) turns the result into the rows to write."""
+    col = rows.__getitem__
+    match, player = np.asarray(col("match"), dtype=np.int64), np.asarray(col("player"), dtype=np.int64)
+    n_rows = match.shape[0]
+    b = RowBatch()
+    b.n_rows = n_rows
+    b.match_keys, row_match, first_row_of_match = _first_appearance(match)
+    b.player_keys, row_player, first_row_of_player = _first_appearance(player)
+    n, n_p = len(b.match_keys), len(b.player_keys)
+    u = max(n_p, 1)
+    # meta word per match (rater.py:70-106)
+    mode = np.asarray(col("game_mode"), dtype=np.int64)[first_row_of_match]
+    supported = (mode >= 0) & (mode <= 5)
+    roster = np.asarray(col("roster"), dtype=np.int64)
+    winner = np.asarray(col("winner"), dtype=bool)
+    invalid = np.asarray(col("n_rosters"))[first_row_of_match] != 2
+    afk = np.zeros(n, dtype=bool)
+    afk[row_match[np.asarray(col("went_afk")) == 1]] = True
+    live = supported & ~invalid & ~afk
+    won = np.zeros((2, n), dtype=bool)                       # winner flags matter for rated matches only
+    placed = (roster == 0) | (roster == 1)
+    w_rows = np.flatnonzero(winner & placed)
+    won[roster[w_rows], row_match[w_rows]] = True
+    bits = np.where(supported, mode, L.MODE_UNSUPPORTED) << L.META_MODE_SHIFT
+    bits = bits | np.where(supported & invalid, L.META_INVALID, 0) | np.where(supported & afk, L.META_AFK, 0)
+    bits = bits | np.where(live & won[0], L.META_WIN_A, 0) | np.where(live & won[1], L.META_WIN_B, 0)
+    b.meta = bits.astype(np.uint32)
+    # slot of every row: position inside its (match, roster) group, in row order
+    grp = row_match * 2 + np.where(placed, roster, 0)
+    order = np.argsort(grp, kind="stable")
+    g_sorted = grp[order]
+    start = np.flatnonzero(np.r_[True, g_sorted[1:] != g_sorted[:-1]])
+    pos = np.empty(n_rows, dtype=np.int64)
+    pos[order] = np.arange(n_rows) - np.repeat(start, np.diff(np.r_[start, n_rows]))
+    widest = int(pos[placed].max()) + 1 if placed.any() else 1
+    if widest > 5:
+        raise ValueError("rosters of more than 5 participants are not supported by the kernel")
+    b.slots = slots = 6 if widest <= 3 else 10
+    row_slot = np.where(placed, roster * (slots // 2) + pos, -1)
+    ids = np.full((n, slots), L.EMPTY_SLOT, dtype=np.uint32)
+    use = np.flatnonzero(placed & live[row_match])
+    ids[row_match[use], row_slot[use]] = row_player[use]
+    b.ids, b.row_match, b.row_slot, b.row_player = ids, row_match, row_slot, row_player
+    # player table (pre-batch values: the same in every row of a player) and seeds
+    table = np.full((u, 8, 2), np.nan)
+    table[:n_p, 0, 0] = np.asarray(col("trueskill_mu"), dtype=np.float64)[first_row_of_player]
+    table[:n_p, 0, 1] = np.asarray(col("trueskill_sigma"), dtype=np.float64)[first_row_of_player]
+    table[:n_p, 1:7] = np.asarray(col("queue"), dtype=np.float64)[first_row_of_player]
+    table[np.isnan(table[:, :, 0])] = np.nan                        # a NULL mu makes the pair NULL
+    seed = np.full((u, 2), np.nan)
+    seed[:n_p] = _seed_columns(np.asarray(col("rank_points_ranked"), dtype=np.float64)[first_row_of_player],
+                               np.asarray(col("rank_points_blitz"), dtype=np.float64)[first_row_of_player],
+                               np.asarray(col("skill_tier"))[first_row_of_player])
+    b.table, b.seed = table, seed
+    return b
+
+
+def updates(b, res):
+    """What the single commit of worker.py:194 flushes after rate_match ran over the batch, as
+    arrays aligned with the input rows / matches / players of `b` (NaN or False mask = not written):
+
+        match_quality [N], match_written [N]                         match.trueskill_quality (rater.py:103,141)
+        part_mu, part_sigma, part_delta [rows], part_written [rows]   participant.trueskill_* (rater.py:150-157)
+        items_mode [rows] (0..5), items_mu, items_sigma [rows]        participant_items <mode> pair (rater.py:167,169)
+        items_any_afk [rows], items_written [rows]                    participant_items.any_afk (rater.py:99,105,110)
+        player_table [U, 8, 2], player_touched [U]                    player.trueskill_* pairs (shared + six queues)
+    """
+    status = np.asarray(res["status"])
+    n = status.shape[0]
+    rated = status == L.ST_OK
+    gated = (status == L.ST_AFK) | (status == L.ST_INVALID)
+    out = {}
+    out["match_quality"] = np.where(rated, np.asarray(res["quality"]), np.where(gated, 0.0, np.nan))
+    out["match_written"] = rated | gated
+    rm, rs = b.row_match, b.row_slot
+    on = (rs >= 0) & rated[rm]
+    sh, de, qu = np.asarray(res["out_shared"]), np.asarray(res["out_delta"]), np.asarray(res["out_queue"])
+    safe_slot = np.where(rs >= 0, rs, 0)
+    pick = lambda a: np.where(on, a[rm, safe_slot], np.nan)
+    out["part_mu"], out["part_sigma"] = pick(sh[:, :, 0]), pick(sh[:, :, 1])
+    out["part_delta"] = pick(de)
+    out["part_written"] = on
+    out["items_mode"] = ((b.meta >> L.META_MODE_SHIFT) & 15)[rm].astype(np.int64)
+    out["items_mu"], out["items_sigma"] = pick(qu[:, :, 0]), pick(qu[:, :, 1])
+    out["items_any_afk"] = gated[rm]
+    out["items_written"] = (rated | gated)[rm]
+    touched = np.zeros(b.table.shape[0], dtype=bool)
+    touched[b.row_player[on]] = True
+    out["player_table"] = np.asarray(res["table"])
+    out["player_touched"] = touched
+    return out
+
+
+def rate_rows(rows, device=0):
+    """ingest_rows + one GPU pass + updates: the row-stream form of worker.py:176-194."""
+    b = ingest_rows(rows)
+    res = _rater(device).rate_batch(b.ids, b.meta, b.table, seed=b.seed, shared_col=0,
+                                    mode_cols=(1, 2, 3, 4, 5, 6), want_outputs=True)
+    return b, updates(b, res)
+
+
 def rate_matches(matches, device=0):
     """Rate a chronologically ordered batch of match object graphs in one GPU
     pass (the loop of worker.py:176-192).  Mutates the objects; returns None.

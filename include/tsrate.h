@@ -50,8 +50,14 @@ enum {
 
 /* Environment of rater.py:30-37 (beta, tau, draw_probability), with the draw
  * margin calc_draw_margin() would give for a match of n players precomputed
- * by the host (n = index).  draw_is_zero selects the analytic draw limit
- * (v = -t, w = 1) that the reference reaches at draw_probability = 0. */
+ * by the host (n = index).  draw_is_zero = 1 selects the analytic draw limit
+ * (v = -t, w = 1) for a draw (both rosters' winner flags equal) at
+ * draw_probability = 0: what a 50-digit evaluation of the package's formulas lands
+ * on, as far as that could be checked here -- the pinned trueskill 0.4.4 / mpmath
+ * 0.19 were not available, so this branch is parity-unpinned by the reference
+ * (its float backend raises FloatingPointError there).  draw_is_zero = 2 makes
+ * such a match TS_ST_FP_ERROR instead, for an integrator who wants the raising
+ * behaviour; 0 = draw_probability > 0 (margins in use). */
 typedef struct ts_params {
     double beta;
     double tau;

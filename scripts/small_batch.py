@@ -90,3 +90,28 @@ for m in ms:
     rater.rate_match(m)
 dt = time.perf_counter() - t0
 print("rate_match per match (worker.py unchanged), 300 calls: %.3f ms per call (%.3g matches/s)" % (dt / 300 * 1e3, 300 / dt))
+
+# the same 500-match batch as a row stream (what the query of worker.py:176-191 yields, one row per
+# participant): numpy ingest, GPU call, numpy updates -- no per-object Python
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from tests import helpers as H
+for rep in range(3):
+    ms = graphs(500, 2500, 20 + rep)
+    for m in ms:                      # helpers.rows_from_matches reads the port's attribute names
+        for r_ in m.rosters:
+            for p_ in r_.participants:
+                for c in ("trueskill_5v5_casual", "trueskill_5v5_ranked"):
+                    for o in (p_.player[0], p_.participant_items[0]):
+                        if not hasattr(o, c + "_mu"):
+                            setattr(o, c + "_mu", None); setattr(o, c + "_sigma", None)
+    rows, _ = H.rows_from_matches(ms)
+    t0 = time.perf_counter()
+    b = rater.ingest_rows(rows)
+    t1 = time.perf_counter()
+    res = rater._rater(0).rate_batch(b.ids, b.meta, b.table, seed=b.seed, shared_col=0, mode_cols=(1, 2, 3, 4, 5, 6),
+                                     want_outputs=True)
+    t2 = time.perf_counter()
+    up = rater.updates(b, res)
+    t3 = time.perf_counter()
+    print("rate_rows(500 matches as %d participant rows): %.2f ms = ingest_rows %.2f + rate_batch %.2f + updates %.2f" % (
+        b.n_rows, (t3 - t0) * 1e3, (t1 - t0) * 1e3, (t2 - t1) * 1e3, (t3 - t2) * 1e3))

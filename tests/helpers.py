@@ -114,3 +114,38 @@ def small_ladder(rng, n_matches, n_players, slots=6, modes=(1,), p_draw=0.0, p_a
             mode = 15
         meta[m] = bits | (mode << 4)
     return ids, meta
+
+
+def rows_from_matches(matches):
+    """The flat participant rows the query of worker.py:176-191 would yield for these object graphs
+    (one row per participant, matches in order), as columns for analyzer_b200.rater.ingest_rows."""
+    mode_index = {name: i for i, (name, _) in enumerate(rp.MODE_COLUMNS)}
+    cols = {k: [] for k in ("match", "game_mode", "n_rosters", "roster", "winner", "went_afk", "player", "skill_tier",
+                            "rank_points_ranked", "rank_points_blitz", "trueskill_mu", "trueskill_sigma", "queue")}
+    parts = []
+    nan = float("nan")
+    for m, match in enumerate(matches):
+        for t, roster in enumerate(match.rosters):
+            for part in roster.participants:
+                p = part.player[0]
+                cols["match"].append(1000 + 7 * m)
+                cols["game_mode"].append(mode_index.get(match.game_mode, 99))
+                cols["n_rosters"].append(len(match.rosters))
+                cols["roster"].append(t)
+                cols["winner"].append(bool(roster.winner))
+                cols["went_afk"].append(int(part.went_afk))
+                cols["player"].append(id(p))
+                cols["skill_tier"].append(p.skill_tier)
+                cols["rank_points_ranked"].append(nan if p.rank_points_ranked is None else p.rank_points_ranked)
+                cols["rank_points_blitz"].append(nan if p.rank_points_blitz is None else p.rank_points_blitz)
+                cols["trueskill_mu"].append(nan if p.trueskill_mu is None else p.trueskill_mu)
+                cols["trueskill_sigma"].append(nan if p.trueskill_sigma is None else p.trueskill_sigma)
+                q = []
+                for _, col in rp.MODE_COLUMNS:
+                    mu = getattr(p, col + "_mu")
+                    q.append((nan, nan) if mu is None else (mu, getattr(p, col + "_sigma")))
+                cols["queue"].append(q)
+                parts.append(part)
+    out = {k: np.array(v) for k, v in cols.items()}
+    out["queue"] = np.array(cols["queue"], dtype=np.float64).reshape(-1, 6, 2)
+    return out, parts

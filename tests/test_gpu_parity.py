@@ -300,3 +300,22 @@ def test_player_id_outside_the_table_is_refused(eng, rater):
     for want_outputs in (True, False):
         with pytest.raises(ValueError):
             rater.rate_batch(bad, meta, tab, shared_col=-1, mode_cols=[-1, 0], want_outputs=want_outputs)
+
+
+def test_zero_probability_draw_switch(eng):
+    """draw_probability = 0 and both winner flags equal: by default the analytic limit (mu of equal
+    teams unchanged, sigma shrinks); with zero_draw="raise" the match fails like the float backend."""
+    ids = np.array([[0, 1, 2, 3, 4, 5]], dtype=np.uint32)
+    meta = np.array([3 | (1 << 4)], dtype=np.uint32)
+    table = np.tile(np.array([2000.0, 100.0]), (6, 1, 1))
+    r = eng.Rater(eng.Env(), 0)
+    out = r.rate_batch(ids, meta, table, shared_col=-1, mode_cols=[-1, 0])
+    assert np.abs(out["table"][:, 0, 0] - 2000.0).max() < 1e-9
+    assert np.abs(out["table"][:, 0, 1] - 100.41498062126155).max() < 1e-9       # SURVEY.md Appendix B
+    r.close()
+    r = eng.Rater(eng.Env(zero_draw="raise"), 0)
+    with pytest.raises(FloatingPointError):
+        r.rate_batch(ids, meta, table, shared_col=-1, mode_cols=[-1, 0])
+    meta[0] = 1 | (1 << 4)                     # a win is unaffected
+    assert r.rate_batch(ids, meta, table, shared_col=-1, mode_cols=[-1, 0])["errors"] == 0
+    r.close()

@@ -138,3 +138,52 @@ def test_seed_policy_on_device(rater):
             assert bad[i] == 0 and tuple(seed[i]) == want, (i, seed[i], want)
         except KeyError:
             assert bad[i] == 1 and np.isnan(seed[i]).all()
+
+
+def test_rate_rows_equals_rate_matches(rater):
+    """worker.py:176-194 as a row stream: ingest_rows + one GPU pass + updates gives, row for row, what
+    rate_matches writes into the object graphs of the same batch."""
+    rng = np.random.default_rng(33)
+    n_players = 70
+    tier, ranked, blitz = H.random_seed_fields(rng, n_players)
+    ids, meta = H.small_ladder(rng, 500, n_players, slots=10, modes=(0, 1, 2, 3, 4, 5), p_draw=0.1, p_afk=0.1,
+                               p_invalid=0.0, p_unsupported=0.04, ragged=True)
+    table = np.full((n_players, H.N_COLS, 2), np.nan)
+    table[::4, H.SHARED_COL] = (1650.0, 180.0)
+    table[::8, 2] = (1700.0, 150.0)
+    matches = H.run_objects(lambda m: None, ids, meta, table, tier, ranked, blitz)["matches"]
+    rows, parts = H.rows_from_matches(matches)           # the rows BEFORE rating
+    b, up = rater.rate_rows(rows)
+    rater.rate_matches(matches)                          # mutates the object graphs
+    assert len(parts) == b.n_rows
+    for m, match in enumerate(matches):
+        q = match.trueskill_quality
+        assert (q is None) == (not up["match_written"][m])
+        if q is not None:
+            assert abs(q - up["match_quality"][m]) < 1e-15
+    for i, part in enumerate(parts):
+        assert (part.trueskill_mu is None) == (not up["part_written"][i])
+        if part.trueskill_mu is not None:
+            assert part.trueskill_mu == up["part_mu"][i] and part.trueskill_sigma == up["part_sigma"][i]
+            assert part.trueskill_delta == up["part_delta"][i]
+        items = part.participant_items[0]
+        assert (items.any_afk is None) == (not up["items_written"][i])
+        if items.any_afk is not None:
+            assert bool(items.any_afk) == bool(up["items_any_afk"][i])
+        if up["part_written"][i]:
+            col = rp.MODE_COLUMNS[int(up["items_mode"][i])][1]
+            assert getattr(items, col + "_mu") == up["items_mu"][i] and getattr(items, col + "_sigma") == up["items_sigma"][i]
+    row_of = {int(k): j for j, k in enumerate(b.player_keys)}
+    seen = set()
+    for part in parts:
+        p = part.player[0]
+        if id(p) in seen:
+            continue
+        seen.add(id(p))
+        j = row_of[id(p)]
+        if up["player_touched"][j]:
+            assert p.trueskill_mu == up["player_table"][j, 0, 0] and p.trueskill_sigma == up["player_table"][j, 0, 1]
+            for mi, (_, col) in enumerate(rp.MODE_COLUMNS):
+                mu = getattr(p, col + "_mu")
+                if mu is not None:
+                    assert mu == up["player_table"][j, 1 + mi, 0]

@@ -118,3 +118,36 @@ def test_pack_ids_bit_stream_round_trip():
         vals = (stream.astype(np.uint64) << np.arange(bits, dtype=np.uint64)).sum(axis=1).astype(np.uint32)
         vals[vals == (1 << bits) - 1] = 0xFFFFFFFF
         assert np.array_equal(vals.reshape(n, p), ids)
+
+
+def test_ingest_rows_equals_object_ingest():
+    """The row-stream ingest (numpy, no per-object Python) builds the same columns as the walk over
+    the object graphs: ids through the player keys, meta, table and seeds row by row."""
+    from analyzer_b200 import rater
+    from tests import helpers as H
+    rng = np.random.default_rng(9)
+    n_players = 80
+    tier, ranked, blitz = H.random_seed_fields(rng, n_players)
+    ids, meta = H.small_ladder(rng, 400, n_players, slots=10, modes=(0, 1, 2, 3, 4, 5), p_draw=0.1, p_afk=0.1,
+                               p_invalid=0.0, p_unsupported=0.05, ragged=True)
+    table = np.full((n_players, H.N_COLS, 2), np.nan)
+    table[::3, H.SHARED_COL] = (1650.0, 180.0)
+    table[::6, 2] = (1700.0, 150.0)
+    matches = H.run_objects(lambda m: None, ids, meta, table, tier, ranked, blitz)["matches"]
+    a = rater.ingest(matches)
+    rows, _ = H.rows_from_matches(matches)
+    b = rater.ingest_rows(rows)
+    assert b.slots == a.slots and np.array_equal(a.meta, b.meta)
+    key_of_a = np.array([id(p) for p in a.players] + [0], dtype=np.int64)
+    key_of_b = np.r_[b.player_keys, 0]
+    ka = key_of_a[np.where(a.ids == 0xFFFFFFFF, len(a.players), a.ids)]
+    kb = key_of_b[np.where(b.ids == 0xFFFFFFFF, len(b.player_keys), b.ids)]
+    assert np.array_equal(ka, kb)
+    row_of = {int(k): i for i, k in enumerate(b.player_keys)}
+    modes_seen = sorted(set(int(m >> 4) & 15 for m in a.meta if not m & 12 and (int(m >> 4) & 15) < 6))
+    for i, p in enumerate(a.players):
+        j = row_of[id(p)]
+        for c in [0] + [1 + m for m in modes_seen]:            # the object ingest loads the rated queues only
+            assert np.array_equal(a.table[i, c], b.table[j, c], equal_nan=True), (i, c)
+        if np.isnan(a.table[i, 0, 0]):
+            assert np.array_equal(a.seed[i], b.seed[j], equal_nan=True)
