@@ -222,6 +222,57 @@ def test_large_index_range(eng):
     r.rate(pb, sch)
     assert r.error_count() == 0
     assert float((tab_a - tab_b).abs().max()) < TOL
+    # ... and not only with each other: a prefix of a stream is an exact check (the first k matches do
+    # not depend on the rest), so the first 2M matches go through the same calls and against the
+    # sequential oracle -- fp64 over all of them, __float128 over the first 300k
+    from oracle import c_oracle as co
+    prm = co.make_params(draw_probability=0.02)
+    for k, quad in ((2_000_000, False), (300_000, True)):
+        tab_p = eng.gen_table(3, 0, u, dev)
+        want = tab_p.cpu().numpy()
+        pp = eng.PlayerTable.ladder(tab_p, mode=1)
+        r.rate_stream(pp, ids[:k], meta[:k], r.link_pred(ids[:k], meta[:k], u, cols))
+        out = co.rate_sequential(prm, ids[:k].cpu().numpy().view(np.uint32), meta[:k].cpu().numpy().view(np.uint32), want,
+                                 -1, cols, quad=quad)
+        assert out["errors"] == 0 and r.error_count() == 0
+        assert float(np.abs(tab_p.cpu().numpy() - want).max()) < TOL
+    r.close()
+
+
+def test_config2_full_size_against_the_oracles(eng):
+    """BASELINE.json configs[1] at its full size (10M 3v3 matches, 1M players): the schedule bit for
+    bit against the sequential schedule oracle, both GPU paths' final tables against the sequential
+    fp64 oracle over the whole ladder, and against the __float128 one over the first million matches."""
+    from oracle import c_oracle as co
+    dev = torch.device("cuda", 0)
+    n, u, seed = 10_000_000, 1_000_000, 0xA11CE002
+    r = eng.Rater(eng.Env(), 0)
+    ids_d, meta_d = eng.gen_matches(eng.make_gen(seed, u, slots=6, mode=1), 0, n, dev)
+    tab_s = eng.gen_table(seed, 0, u, dev)
+    tab_r = tab_s.clone()
+    table0 = tab_s.cpu().numpy()
+    ps, pr = eng.PlayerTable.ladder(tab_s, mode=1), eng.PlayerTable.ladder(tab_r, mode=1)
+    r.rate_stream(ps, ids_d, meta_d, r.link_pred(ids_d, meta_d, u, ps.mode_cols))
+    sch = r.schedule(ids_d, meta_d, u, pr.mode_cols)
+    r.rate(pr, sch)
+    assert r.error_count() == 0
+    ids, meta = ids_d.cpu().numpy().view(np.uint32), meta_d.cpu().numpy().view(np.uint32)
+    rnd, order, offs, R = co.schedule(ids, meta, pr.mode_cols, u)
+    assert sch.n_rounds == R
+    assert np.array_equal(sch.round.cpu().numpy().view(np.uint32), rnd)
+    assert np.array_equal(sch.order.cpu().numpy().view(np.uint32), order)
+    assert np.array_equal(sch.round_offsets.cpu().numpy().view(np.uint32)[:R + 2], offs)
+    want = table0.copy()
+    assert co.rate_sequential(co.make_params(), ids, meta, want, -1, pr.mode_cols[:6], quad=False)["errors"] == 0
+    assert float(np.abs(tab_s.cpu().numpy() - want).max()) < TOL
+    assert float(np.abs(tab_r.cpu().numpy() - want).max()) < TOL
+    k = 1_000_000
+    want = table0.copy()
+    co.rate_sequential(co.make_params(), ids[:k], meta[:k], want, -1, pr.mode_cols[:6], quad=True)
+    tab_p = torch.from_numpy(table0.copy()).to(dev)
+    pp = eng.PlayerTable.ladder(tab_p, mode=1)
+    r.rate_stream(pp, ids_d[:k], meta_d[:k], r.link_pred(ids_d[:k], meta_d[:k], u, pp.mode_cols))
+    assert float(np.abs(tab_p.cpu().numpy() - want).max()) < TOL
     r.close()
 
 
