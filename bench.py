@@ -287,9 +287,33 @@ def object_api_rate(ids_d, meta_d, n=5000):
     dt_cpu = (time.perf_counter() - t0) / len(g2)
     err = max(abs(a.participants[0].trueskill_mu - b.participants[0].trueskill_mu)
               for a, b in zip(g[:400], g2) if b.participants[0].trueskill_mu is not None)
+    # the same batch as a ROW STREAM (what the query of worker.py:176-191 yields, one row per participant):
+    # numpy ingest, one GPU call, numpy update rows -- no per-object Python (rater.ingest_rows / updates)
+    p = ids.shape[1]
+    rows_n = n * p
+    nan = np.full(rows_n, np.nan)
+    rows = dict(match=np.repeat(np.arange(n), p), game_mode=np.full(rows_n, 1), n_rosters=np.full(rows_n, 2),
+                roster=np.tile(np.repeat([0, 1], p // 2), n), went_afk=np.zeros(rows_n, dtype=np.int64),
+                winner=((meta[:, None] >> np.repeat([0, 1], p // 2)[None, :]) & 1).astype(bool).reshape(-1),
+                player=ids.reshape(-1).astype(np.int64), skill_tier=(ids.reshape(-1) % 30).astype(np.int64),
+                rank_points_ranked=nan, rank_points_blitz=nan, trueskill_mu=nan, trueskill_sigma=nan,
+                queue=np.full((rows_n, 6, 2), np.nan))
+    gpu_rater.rate_rows({k: v[:64 * p] for k, v in rows.items()})          # warm-up
+    t0 = time.perf_counter()
+    b, up = gpu_rater.rate_rows(rows)
+    dt_rows = time.perf_counter() - t0
+    first = next(i for i in range(n) if g[i].participants[0].trueskill_mu is not None)
+    err_rows = abs(g[first].participants[0].trueskill_mu - up["part_mu"][first * p])
+    small = {k: v[:500 * p] for k, v in rows.items()}
+    t0 = time.perf_counter()
+    gpu_rater.rate_rows(small)
+    dt_small = time.perf_counter() - t0
     return {"rate_matches_per_s": n / dt_gpu, "batch": n, "reference_loop_per_s": 1.0 / dt_cpu,
             "note": "faithful shared + queue path (rounds), %d-match batch of object graphs, 3000 players; "
-                    "Python ingest + write-back included" % n, "check_max_abs_diff": err}
+                    "Python ingest + write-back included" % n, "check_max_abs_diff": err,
+            "rate_rows_per_s": n / dt_rows, "rate_rows_500_match_batch_ms": dt_small * 1e3,
+            "rate_rows_note": "the same batch as participant rows: ingest_rows + one GPU call + updates (numpy, no per-object "
+                              "Python); 500-match batch = the reference worker's BATCHSIZE", "rate_rows_check_abs_diff": err_rows}
 
 
 def cpu_c_baselines(ids, meta, table, n_players):
