@@ -326,6 +326,43 @@ __device__ __forceinline__ void st_relaxed_u32(uint32_t *p, uint32_t v)
     asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+#ifndef TS_SORT_LATE_LOOKBACK
+#define TS_SORT_LATE_LOOKBACK 0
+#endif
+#ifndef TS_SORT_SPIN_NS
+#define TS_SORT_SPIN_NS 40
+#endif
+
+// Decoupled look-back of thread d = digit d: sum the counts of the tiles before `tile` back to the
+// nearest published prefix, publish this tile's prefix, and leave in gbase[d] where this tile's
+// run of digit d starts in the output, minus its tile-local start.
+// kLookBack > 1 loads the statuses of several predecessors together (independent L2 round trips)
+// before consuming them in order; measured slower (config 2 link 2.59 -> 2.70 ms at 4, 2.76 at 8):
+// the loop mostly waits for the tile just before to publish, it does not walk far.
+__device__ __forceinline__ void lookback(uint32_t *status, uint32_t tile, uint32_t d, uint32_t run, uint32_t dstart,
+                                         const uint32_t *digit_base, uint32_t *gbase)
+{
+    uint32_t excl = 0;
+    for (uint32_t j = tile; j > 0;) {
+        uint32_t v[kLookBack];
+#pragma unroll
+        for (int q = 0; q < kLookBack; ++q)
+            v[q] = j > (uint32_t)q ? ld_relaxed_u32(status + (size_t)(j - 1 - q) * 256 + d) : kStPrefix;   // before tile 0: prefix 0
+        bool found = false, pending = false;
+#pragma unroll
+        for (int q = 0; q < kLookBack; ++q) {
+            if (found || pending) continue;
+            if (v[q] & kStPrefix) { excl += v[q] & kStMask; found = true; }
+            else if (v[q] & kStCount) { excl += v[q] & kStMask; --j; }
+            else pending = true;
+        }
+        if (found) break;
+        if (pending) __nanosleep(TS_SORT_SPIN_NS);  // that tile has not published yet: do not hog the issue slots
+    }
+    if (tile > 0) st_relaxed_u32(status + (size_t)tile * 256 + d, (excl + run) | kStPrefix);
+    gbase[d] = __ldg(digit_base + d) + excl - dstart;
+}
+
 // n_dev (optional): the number of entries lives on the device (the owned slots of a sharded ladder)
 __global__ void __launch_bounds__(kSortBlock, TS_SORT_MIN_BLOCKS)
 k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n_in, const uint32_t *n_dev, int shift,
@@ -376,6 +413,7 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
         off[k] = __shfl_sync(0xFFFFFFFFu, prev, leader) + __popc(peers & ((1u << lane) - 1u));
     }
     __syncthreads();
+    uint32_t my_run, my_dstart;
     {
         const uint32_t d = threadIdx.x;
         uint32_t run = 0;
@@ -385,7 +423,7 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
             wcount[w][d] = run;
             run += c;
         }
-        // publish this tile's count of digit d, then find the tiles before it
+        // publish this tile's count of digit d; the tiles before it are looked at later
         uint32_t *row = status + (size_t)tile * 256;
         st_relaxed_u32(row + d, run | (tile == 0 ? kStPrefix : kStCount));
         uint32_t incl = run;   // exclusive scan of the 256 digit totals across the block (tile-local starts)
@@ -400,32 +438,20 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) before += (w < warp) ? warp_tot[w] : 0u;
         const uint32_t dstart = before + incl - run;
-        // Look-back.  kLookBack > 1 loads the statuses of several predecessors together (independent L2
-        // round trips) before consuming them in order; measured slower (config 2 link 2.59 -> 2.70 ms at 4,
-        // 2.76 at 8): the loop mostly waits for the tile just before to publish, it does not walk far.
-        uint32_t excl = 0;
-        for (uint32_t j = tile; j > 0;) {
-            uint32_t v[kLookBack];
-#pragma unroll
-            for (int q = 0; q < kLookBack; ++q)
-                v[q] = j > (uint32_t)q ? ld_relaxed_u32(status + (size_t)(j - 1 - q) * 256 + d) : kStPrefix;   // before tile 0: prefix 0
-            bool found = false, pending = false;
-#pragma unroll
-            for (int q = 0; q < kLookBack; ++q) {
-                if (found || pending) continue;
-                if (v[q] & kStPrefix) { excl += v[q] & kStMask; found = true; }
-                else if (v[q] & kStCount) { excl += v[q] & kStMask; --j; }
-                else pending = true;
-            }
-            if (found) break;
-            if (pending) __nanosleep(40);  // that tile has not published yet: do not hog the issue slots
-        }
-        if (tile > 0) st_relaxed_u32(row + d, (excl + run) | kStPrefix);
-        gbase[d] = __ldg(digit_base + d) + excl - dstart;
 #pragma unroll
         for (int w = 0; w < kWarps; ++w) wcount[w][d] += dstart;
+        my_run = run;
+        my_dstart = dstart;
     }
     __syncthreads();
+    // Look-back first, then the tile goes into digit order in shared memory.  The other order
+    // (TS_SORT_LATE_LOOKBACK=1: reorder while the tiles before publish) measured slower -- config 2 link
+    // 2.58 -> 2.82 ms: what the tiles behind wait for is this tile's prefix, and that came later.  The
+    // back-off of the spin (TS_SORT_SPIN_NS 40 / 100 / 200) makes no difference.
+#if !TS_SORT_LATE_LOOKBACK
+    lookback(status, tile, threadIdx.x, my_run, my_dstart, digit_base, gbase);
+    __syncthreads();
+#endif
 #pragma unroll
     for (int k = 0; k < kSortItems; ++k) {
         uint32_t idx = wbase + k * 32 + lane;
@@ -435,6 +461,9 @@ k_radix_onesweep(KeySrc src, const uint32_t *vals_in, int ident_vals, uint32_t n
             sval[pos] = ident_vals ? idx : __ldg(vals_in + idx);
         }
     }
+#if TS_SORT_LATE_LOOKBACK
+    lookback(status, tile, threadIdx.x, my_run, my_dstart, digit_base, gbase);
+#endif
     __syncthreads();
     const uint32_t cnt = min((uint32_t)kSortTile, n - tile_base);
     for (uint32_t i = threadIdx.x; i < cnt; i += kSortBlock) {
