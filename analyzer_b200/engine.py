@@ -440,6 +440,16 @@ class Rater(object):
             # rating kernel): T(W) ~ first copy + W * fixed + total work has its minimum near
             # 2.5M matches per window (scripts/e2e_windows.py, scripts/e2e_timeline.py)
             windows = max(1, min(8, n // 2_500_000)) if (stream and not want_outputs) else 1
+            if windows >= 3:
+                # growing parts (1 : 2 : ... : W): the GPU starts after a tenth of the copy instead of a
+                # quarter, and the copies, faster than the GPU work, stay ahead (6.91 -> 6.58 ms at 10M matches)
+                windows = list(range(1, windows + 1))
+        # windows: a count (equal parts) or the parts themselves as fractions of the batch (a short first
+        # window lets the GPU start early; the copies are faster than the GPU work, so it is not starved later)
+        fractions = None
+        if not isinstance(windows, int):
+            fractions = [float(f) for f in windows]
+            windows = len(fractions)
         self.reset_errors()
         if stream and windows > 1:
             # Pipelined ingest: the match stream is copied window by window on a side
@@ -459,7 +469,14 @@ class Rater(object):
             ptab = PlayerTable(tab_d, shared_col, list(mode_cols), seed_d)
             last = torch.full((ptab.n_players,), -1, dtype=torch.int32, device=dev)
             # windows start at multiples of 8 matches: packed id columns then split on byte boundaries
-            bounds = [((w * n) // windows) & ~7 for w in range(windows)] + [n]
+            if fractions is None:
+                bounds = [((w * n) // windows) & ~7 for w in range(windows)] + [n]
+            else:
+                acc, bounds = 0.0, [0]
+                for f in fractions[:-1]:
+                    acc += f / sum(fractions)
+                    bounds.append(max(bounds[-1], min(n, int(acc * n)) & ~7))
+                bounds.append(n)
             cut = (lambda m: m * p * packed.bits // 8 if m < n else ids_t.numel()) if packed is not None else (lambda m: m)
             side.wait_stream(cur)
             ready = []

@@ -31,3 +31,12 @@ for form, ids_in in (("ids packed at %d bits" % ids_pk.bits, ids_pk), ("ids as 3
                      windows=windows)
         best = min(best, time.perf_counter() - t0)
     print("windows=%2d: %.3f ms  %.3g matches/s" % (windows, best * 1e3, n / best), flush=True)
+
+print("uneven windows (fractions of the batch), packed ids")
+for fr in ([1, 3, 3, 3], [1, 2, 3, 4], [1, 2, 2, 2, 3], [0.5, 1.5, 2.5, 2.5, 3], [1, 3, 6], [1, 4, 5], [2, 3, 5], [0.5, 1, 2, 3, 3.5]):
+    best = 1e9
+    for it in range(4):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        r.rate_batch(ids_pk, meta_h, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, table_out=out_h, windows=fr)
+        best = min(best, time.perf_counter() - t0)
+    print("windows=%s: %.3f ms  %.3g matches/s" % (fr, best * 1e3, n / best), flush=True)
