@@ -320,7 +320,7 @@ def test_rate_batch_pipelined_windows(eng):
     assert packed.nbytes < ids_h.numel() * 4 * 0.7
     back = r.unpack_ids(packed.packed.cuda(), packed.bits, torch.empty_like(ids_h, device="cuda"))
     assert torch.equal(back.cpu(), ids_h)
-    for windows in (5, 1):
+    for windows in (5, 1, [1, 2, 3, 4], [0.5, 0.5]):          # equal parts, or growing ones given as fractions
         e = r.rate_batch(packed, meta8, tab_h, shared_col=-1, mode_cols=[-1, 0], want_outputs=False, windows=windows)
         assert np.array_equal(a["table"], e["table"]) and e["errors"] == 0
     # ragged records (empty slots) survive the packing
