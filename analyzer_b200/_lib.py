@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 # TSRATE_LIB: another build of the same library (tuning variants, scripts/build_variants.sh)
 LIB_PATH = os.environ.get("TSRATE_LIB") or os.path.join(_HERE, "libtsrate.so")
-SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "stream_pair.cu", "shard.cu", "static_sched.cu"]
+SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "stream_pair.cu", "slots.cu", "shard.cu", "static_sched.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-shared", "-Xcompiler", "-fPIC"]
 
@@ -29,7 +29,7 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_static", "ts_schedule_static_max_slot_entries",
            "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream",
            "ts_stream_stalled", "ts_rate_stream_table_workspace_bytes",
-           "ts_seed_table", "ts_widen_meta", "ts_unpack_ids", "ts_error_counts",
+           "ts_seed_table", "ts_widen_meta", "ts_unpack_ids", "ts_error_counts", "ts_slot_rows_bytes", "ts_link_succ", "ts_rate_slots",
            "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_shard_local_matches",
            "ts_shard_link_workspace_bytes", "ts_shard_inbox_cap", "ts_shard_reset", "ts_shard_link", "ts_shard_rate", "ts_shard_status"]
 SHARD_BLOCK, SHARD_MAX = 32, 16
@@ -152,6 +152,12 @@ def lib():
                                     C.c_int64, C.POINTER(TsOutputs), C.c_int32, C.c_int32, C.c_void_p]
         L.ts_shard_status.argtypes = [C.c_void_p, C.c_void_p]
         L.ts_error_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_void_p]
+        L.ts_slot_rows_bytes.restype = C.c_int64
+        L.ts_slot_rows_bytes.argtypes = [C.c_int64, C.c_int32]
+        L.ts_link_succ.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.POINTER(TsTable), C.c_uint32,
+                                   C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        L.ts_rate_slots.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
+                                    C.c_uint32, C.POINTER(TsOutputs), C.c_int32, C.c_void_p, C.c_void_p]
         L.ts_stream_stalled.argtypes = [C.c_void_p, C.c_void_p]
         L.ts_seed_table.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double,
                                     C.POINTER(C.c_double), C.c_void_p, C.c_void_p, C.c_void_p]

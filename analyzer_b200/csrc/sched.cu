@@ -1224,6 +1224,113 @@ extern "C" int ts_link_pred(ts_ctx *ctx, const uint32_t *ids, const uint32_t *me
 }
 
 // ---------------------------------------------------------------------------
+// Links for the slot-indexed form of the streaming rating kernel (csrc/slots.cu): succ[v] = slot
+// index (m' * P + s') of the same player's next rated match, TS_NONE after the last; the head of
+// every player's run gets the player's pair from the table as its row.  Same sorted runs as pred,
+// looked at in the other direction; same L2-sized destination ranges for the scatter.
+// ---------------------------------------------------------------------------
+namespace {
+
+__device__ __forceinline__ void st_row_gpu(unsigned long long *row, double mu, double sigma, uint32_t ver)
+{
+    const unsigned long long v = (unsigned long long)ver << 32;
+    const unsigned long long m = (unsigned long long)__double_as_longlong(mu);
+    const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
+    asm volatile("st.relaxed.gpu.global.v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(row), "l"((m & 0xFFFFFFFFull) | v),
+                 "l"((m >> 32) | v), "l"((s & 0xFFFFFFFFull) | v), "l"((s >> 32) | v) : "memory");
+}
+
+__global__ void __launch_bounds__(256)
+k_succ_slots(const uint32_t *keys, const uint32_t *vals, uint32_t n, unsigned long long slots_magic, uint32_t sentinel,
+             uint32_t v_lo, uint32_t v_hi, int heads, const double *table, uint32_t epoch, uint32_t *succ,
+             unsigned long long *rows, unsigned long long *ctrl)
+{
+    // four consecutive sorted entries per thread, plus the one before and the one after them
+    const uint32_t i0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
+    if (i0 >= n) return;
+    uint32_t k[6], v[6];
+#pragma unroll
+    for (int j = 0; j < 6; ++j) {
+        const int64_t i = (int64_t)i0 + j - 1;
+        const bool in = i >= 0 && i < (int64_t)n;
+        k[j] = in ? __ldcs(keys + i) : 0xFFFFFFFFu;
+        v[j] = in ? __ldcs(vals + i) : 0u;
+    }
+#pragma unroll
+    for (int j = 1; j <= 4; ++j) {
+        if (i0 + j - 1 >= n || k[j] >= sentinel) continue;                  // empty slot / gated match / id outside the table
+        uint32_t nxt = TS_NONE;
+        if (i0 + j < n && k[j + 1] == k[j]) {
+            nxt = v[j + 1];
+            if ((uint32_t)__umul64hi((unsigned long long)nxt, slots_magic) == (uint32_t)__umul64hi((unsigned long long)v[j], slots_magic))
+                atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_DUPLICATE);   // the player twice in one match
+        }
+        if (v[j] >= v_lo && v[j] < v_hi) succ[v[j]] = nxt;
+        if (heads && (i0 + j - 1 == 0 || k[j - 1] != k[j])) {               // the player's first match of the window
+            const double2 pr = __ldg(reinterpret_cast<const double2 *>(table) + k[j]);
+            st_row_gpu(rows + (size_t)v[j] * 4, pr.x, pr.y, epoch);
+        }
+    }
+}
+
+}  // namespace
+
+extern "C" int ts_link_succ(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
+                            const ts_table *table, uint32_t epoch, uint32_t *succ, void *rows, void *workspace,
+                            int64_t workspace_bytes, void *stream)
+{
+    if (!ctx || !table || !table->data || (n_matches > 0 && (!ids || !meta || !succ || !rows || !workspace))) {
+        ts_set_error("ts_link_succ: null argument");
+        return TS_E_ARG;
+    }
+    if (table->row_pairs != 1 || table->shared_col >= 0) {
+        ts_set_error("ts_link_succ: the table must be a single-pair ladder (row_pairs == 1, shared_col == -1)");
+        return TS_E_UNSUPPORTED;
+    }
+    const int64_t n_players = table->n_players;
+    if (slots < 2 || slots > TS_MAX_SLOTS || (slots & 1) || n_matches < 0 ||
+        (uint64_t)n_matches * (uint64_t)slots >= 0xFFFF0000ull || n_players < 1 || n_players >= 0xFFFFFFFFll) {
+        ts_set_error("ts_link_succ: bad sizes (n_matches * slots must stay below 2^32 - 2^16)");
+        return TS_E_ARG;
+    }
+    if (epoch == 0u || epoch == TS_NONE || ((uintptr_t)rows & 31u) != 0u) {
+        ts_set_error("ts_link_succ: epoch must be neither 0 nor 0xFFFFFFFF, rows 32-byte aligned");
+        return TS_E_ARG;
+    }
+    if (n_matches == 0) return 0;
+    if (workspace_bytes < ts_link_workspace_bytes(n_matches, slots)) {
+        ts_set_error("ts_link_succ: workspace too small");
+        return TS_E_WORKSPACE;
+    }
+    TS_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const uint32_t np = (uint32_t)n_matches * (uint32_t)slots;
+    Workspace w = carve_link((char *)workspace, np);
+    KeySrc src;
+    src.keys = ids;
+    src.meta = meta;
+    for (int i = 0; i < 16; ++i) src.modes.col[i] = i < 6 ? table->mode_col[i] : (int8_t)-1;
+    src.slots = (uint32_t)slots;
+    src.sentinel = (uint32_t)n_players;
+    src.from_ids = 1;
+    src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
+    src.rated_mask = 0;
+    for (int i = 0; i < 6; ++i) if (src.modes.col[i] >= 0) src.rated_mask |= 1u << i;
+    int buf = radix_sort(src, np, bits_for((uint64_t)n_players), w, s, ctx->sm_count);
+    if (buf < 0) return buf;
+    uint32_t range = pred_range_entries();
+    if (((uint64_t)np + range - 1) / range > 8) range = 0xFFFFFFFFu;
+    for (uint64_t lo = 0; lo < np; lo += range) {
+        const uint32_t hi = (uint32_t)std::min<uint64_t>(lo + range, np);
+        k_succ_slots<<<(np + 1023) / 1024, 256, 0, s>>>(w.keys[buf], w.vals[buf], np, src.slots_magic, src.sentinel, (uint32_t)lo,
+                                                       hi, lo == 0 ? 1 : 0, table->data, epoch, succ,
+                                                       (unsigned long long *)rows, ctx->d_ctrl);
+    }
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------
 // Links of ONE ladder spread over the G GPUs of a node (tsrate.h: ts_shard_view).
 // Every rank links the players it owns (p % G == rank):
 //   1. k_owned_stage / k_tile_scan / k_owned_gather read the whole id stream once -- the own

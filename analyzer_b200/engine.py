@@ -203,6 +203,8 @@ class Rater(object):
         self._ws = None
         self._vt = None
         self._copy_stream = None
+        self._slot_rows = self._slot_succ = None
+        self._slot_epoch = 0
 
     def close(self):
         if self._ctx:
@@ -323,6 +325,42 @@ class Rater(object):
                                              int(seq_base), int(flags), C.byref(out), int(lanes_per_match),
                                              _ptr(self._vt), self._vt.numel(), _stream_ptr()))
 
+    def rate_slots(self, table, ids, meta, outputs=None, lanes_per_match=0, window=None):
+        """Slot-indexed streaming form (ts_link_succ + ts_rate_slots) for single-pair ladders whose rows
+        do not fit L2: every match reads its rows as one contiguous piece, only the writes scatter.
+        Same bits as link_pred + rate_stream.  The ladder is rated in windows of `window` matches (about
+        60 Mi slot entries by default: the link scatter stays L2-sized); the table carries the state from
+        one window to the next, the rows buffer (32 bytes per slot of a window) is reused under a new
+        epoch each time and never cleared."""
+        n, p = ids.shape
+        if window is None:
+            window = max(1, (60 << 20) // p)
+        window = min(window, max(n, 1))
+        rows_bytes = L.check(self._lib.ts_slot_rows_bytes(window, p))
+        if self._slot_rows is None or self._slot_rows.numel() < rows_bytes:
+            self._slot_rows = None
+            self._slot_rows = torch.zeros(max(rows_bytes, 256), dtype=torch.uint8, device=self.device)
+        if self._slot_succ is None or self._slot_succ.numel() < window * p:
+            self._slot_succ = None
+            self._slot_succ = torch.empty(window * p, dtype=torch.int32, device=self.device)
+        ws = self._workspace(L.check(self._lib.ts_link_workspace_bytes(window, p)))
+        desc = table.desc()
+        with torch.cuda.device(table.data.device):
+            for lo in range(0, n, window):
+                hi = min(n, lo + window)
+                self._slot_epoch = self._slot_epoch + 1 if self._slot_epoch < 0xFFFFFFF0 else 1
+                out = L.TsOutputs()
+                if outputs:
+                    for k in ("quality", "out_queue", "status"):
+                        t = outputs.get(k)
+                        setattr(out, k, t[lo:hi].data_ptr() if t is not None else None)
+                a, b = ids[lo:hi], meta[lo:hi]
+                L.check(self._lib.ts_link_succ(self._ctx, _ptr(a), _ptr(b), hi - lo, p, C.byref(desc), self._slot_epoch,
+                                               _ptr(self._slot_succ), _ptr(self._slot_rows), _ptr(ws), ws.numel(), _stream_ptr()))
+                L.check(self._lib.ts_rate_slots(self._ctx, C.byref(desc), _ptr(a), _ptr(b), _ptr(self._slot_succ), hi - lo, p,
+                                                self._slot_epoch, C.byref(out), int(lanes_per_match), _ptr(self._slot_rows),
+                                                _stream_ptr()))
+
     def rate_stream_windows(self, table, ids, meta, window, lanes_per_match=0):
         """The whole ladder in windows of `window` matches (worker.py:18-20's
         micro-batches): link + rate per window, chain tails and versioned rows
@@ -357,6 +395,8 @@ class Rater(object):
         device so that the batch can raise the right one without the status column."""
         if L.check(self._lib.ts_stream_stalled(self._ctx, _stream_ptr())):
             raise L.TsError("ts_rate_stream gave up: the links (pred) do not belong to the stream they were given with")
+        if L.check(self._lib.ts_shard_status(self._ctx, _stream_ptr())) & L.SHARD_DUPLICATE:
+            raise L.TsError("a player is listed twice in one match: not supported by the slot-indexed / sharded paths")
         fp, val = C.c_int64(0), C.c_int64(0)
         L.check(self._lib.ts_error_counts(self._ctx, C.byref(fp), C.byref(val), _stream_ptr()))
         return int(fp.value), int(val.value)

@@ -216,6 +216,27 @@ int ts_rate_stream(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, cons
                    const ts_outputs *outputs, int32_t lanes_per_match, void *workspace, int64_t workspace_bytes,
                    void *stream);
 
+/* The streaming form for ladders whose rows do not fit L2 (single-pair ladders only): a row
+ * lives where it will be READ -- rows[m * slots + s] is the rating the player in slot s of match
+ * m brings to that match -- so a match reads its rows as one contiguous piece and only the
+ * writes scatter.  ts_link_succ sorts like ts_link_pred and writes succ[N][P] (the slot index
+ * m' * slots + s' of the same player's next rated match, TS_NONE after the last) and every
+ * player's first row (taken from the table); ts_rate_slots rates in stream order, a match waiting
+ * until its own rows carry `epoch`, and stores every new row at succ, or into the table after the
+ * player's last match.  Results are bit-identical to ts_rate_stream.  rows: ts_slot_rows_bytes
+ * (32 bytes per slot of the window), 32-byte aligned, zeroed once when allocated; `epoch` (not 0,
+ * not TS_NONE) must differ from the one of the buffer's previous use -- it is what validates a row,
+ * so the buffer is never cleared.  Windows need no carried state: the table holds it between them.
+ * A player listed twice in one match is not supported (ts_shard_status reports TS_SHARD_DUPLICATE).
+ * No counterpart in the reference. */
+int64_t ts_slot_rows_bytes(int64_t n_matches, int32_t slots);
+int ts_link_succ(ts_ctx *ctx, const uint32_t *ids, const uint32_t *meta, int64_t n_matches, int32_t slots,
+                 const ts_table *table, uint32_t epoch, uint32_t *succ, void *rows, void *workspace,
+                 int64_t workspace_bytes, void *stream);
+int ts_rate_slots(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const uint32_t *meta, const uint32_t *succ,
+                  int64_t n_matches, int32_t slots, uint32_t epoch, const ts_outputs *outputs, int32_t lanes_per_match,
+                  void *rows, void *stream);
+
 /* One ladder over the G GPUs of a node (BASELINE.json configs[4]), one
  * process per GPU, G a power of two <= 16.  No counterpart in the reference (single
  * process, single thread: worker.py:176-192 is the one sequential order this reproduces).
