@@ -534,6 +534,30 @@ def config_block(rater_of, engine, name, n, u, p, zipf, p_draw, layout, lanes, p
                         "frac": achieved / peak, "traffic": traffic, "algorithmic_bytes_per_match": b,
                         "traffic_over_algorithmic": (traffic / (b * n)) if traffic else None},
            "l2": "table %d MB, versioned rows %d MB (L2 is 126 MB)" % ((u * 16 * k) >> 20, (u * 32 * k) >> 20)}
+    if layout == "ladder":
+        # the slot-indexed form (ts_link_succ + ts_rate_slots: rows live where they are read), link and rate
+        # interleaved window by window; same bits as the stream path
+        try:
+            ref = tab.clone()
+            t_best = None
+            for it in range(3):
+                tab.copy_(tab0)
+                e0, e1 = ev(), ev()
+                e0.record()
+                rater.rate_slots(pt, ids_d, meta_d, None, lanes)
+                e1.record()
+                torch.cuda.synchronize()
+                if it and (t_best is None or e0.elapsed_time(e1) < t_best):
+                    t_best = e0.elapsed_time(e1)
+            assert rater.error_count() == 0
+            out["slots_path"] = {"total_ms": t_best, "matches_per_s": n / (t_best * 1e-3),
+                                 "bit_equal_to_stream_path": bool(torch.equal(tab, ref)),
+                                 "note": "rows indexed by the consuming slot (sequential reads, scattered writes); link + rate "
+                                         "per window of ~60 Mi slot entries"}
+            del ref
+            rater._slot_rows = rater._slot_succ = None
+        except Exception as exc:
+            out["slots_path"] = {"error": repr(exc)}
     if want_rounds:
         try:
             tab.copy_(tab0)

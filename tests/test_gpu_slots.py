@@ -49,7 +49,7 @@ def test_slots_equal_stream_and_oracle(eng, c_oracle, slots, zipf, p_draw, windo
     r.close()
 
 
-def test_slots_seeds_ragged_errors_and_duplicates(eng, c_oracle):
+def test_slots_seeds_ragged_errors_and_duplicates(eng, c_oracle, monkeypatch):
     """NULL ratings seeded on first touch, ragged teams, a sigma == 0 player (the match fails, its rows
     move on unchanged), an id outside the table; a player listed twice is reported."""
     from analyzer_b200 import _lib
@@ -90,6 +90,7 @@ def test_slots_seeds_ragged_errors_and_duplicates(eng, c_oracle):
     bad[10, 1] = bad[10, 0]
     t = dev_t(table)
     pt = eng.PlayerTable(t, -1, [-1, 0], dev_t(seeds))
+    monkeypatch.setenv("TSRATE_STREAM_MAX_SPINS", "20000")
     r.rate_slots(pt, dev_t(bad), dev_t(meta))       # may stall on the self-link: the watchdog ends it
     with pytest.raises(_lib.TsError):
         r.error_count()
