@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 # TSRATE_LIB: another build of the same library (tuning variants, scripts/build_variants.sh)
 LIB_PATH = os.environ.get("TSRATE_LIB") or os.path.join(_HERE, "libtsrate.so")
-SOURCES = ["api.cu", "gen.cu", "sched.cu", "rate.cu", "stream.cu", "stream_pair.cu", "slots.cu", "shard.cu", "static_sched.cu"]
+SOURCES = ["api.cu", "gen.cu", "ingest.cu", "sched.cu", "rate.cu", "stream.cu", "stream_pair.cu", "slots.cu", "shard.cu", "static_sched.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "--extended-lambda", "-shared", "-Xcompiler", "-fPIC"]
 
@@ -29,7 +29,7 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_schedule_static", "ts_schedule_static_max_slot_entries",
            "ts_link_workspace_bytes", "ts_link_pred", "ts_rate_stream_workspace_bytes", "ts_rate_stream",
            "ts_stream_stalled", "ts_rate_stream_table_workspace_bytes",
-           "ts_seed_table", "ts_widen_meta", "ts_unpack_ids", "ts_error_counts", "ts_slot_rows_bytes", "ts_link_succ", "ts_rate_slots",
+           "ts_seed_table", "ts_widen_meta", "ts_unpack_ids", "ts_error_counts", "ts_slot_rows_bytes", "ts_link_succ", "ts_rate_slots", "ts_ingest_rows",
            "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_shard_local_matches",
            "ts_shard_link_workspace_bytes", "ts_shard_inbox_cap", "ts_shard_reset", "ts_shard_link", "ts_shard_rate", "ts_shard_status"]
 SHARD_BLOCK, SHARD_MAX = 32, 16
@@ -63,6 +63,13 @@ class TsShardView(C.Structure):
                 ("rows", C.c_void_p * 16), ("table", C.c_void_p * 16), ("inbox", C.c_void_p * 16),
                 ("inbox_count", C.c_void_p * 16), ("inbox_cap", C.c_int64), ("ring", C.c_void_p * 16),
                 ("ring_final", C.c_void_p * 16), ("ring_tail", C.c_void_p * 16), ("ring_cap", C.c_int64), ("ring_epoch", C.c_int64)]
+
+
+class TsRowColumns(C.Structure):
+    _fields_ = [("n_rows", C.c_int64), ("match", C.c_void_p), ("player", C.c_void_p), ("game_mode", C.c_void_p),
+                ("n_rosters", C.c_void_p), ("roster", C.c_void_p), ("skill_tier", C.c_void_p), ("winner", C.c_void_p),
+                ("went_afk", C.c_void_p), ("rank_points_ranked", C.c_void_p), ("rank_points_blitz", C.c_void_p),
+                ("trueskill_mu", C.c_void_p), ("trueskill_sigma", C.c_void_p), ("queue", C.c_void_p)]
 
 
 class TsGen(C.Structure):
@@ -158,6 +165,8 @@ def lib():
                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         L.ts_rate_slots.argtypes = [C.c_void_p, C.POINTER(TsTable), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int32,
                                     C.c_uint32, C.POINTER(TsOutputs), C.c_int32, C.c_void_p, C.c_void_p]
+        L.ts_ingest_rows.argtypes = [C.POINTER(TsRowColumns), C.c_double, C.POINTER(C.c_double)] + [C.c_void_p] * 9 + \
+            [C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32)]
         L.ts_stream_stalled.argtypes = [C.c_void_p, C.c_void_p]
         L.ts_seed_table.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_double,
                                     C.POINTER(C.c_double), C.c_void_p, C.c_void_p, C.c_void_p]

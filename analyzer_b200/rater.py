@@ -25,6 +25,7 @@ without the library or a CUDA device these functions raise.
 """
 from __future__ import annotations
 
+import ctypes as C
 import logging
 import os
 import sys
@@ -261,6 +262,7 @@ class RowBatch(object):
 
 
 _VST = np.array([vst_points[t] for t in range(-1, 30)])
+_VST_C = (C.c_double * 31)(*[float(x) for x in _VST])
 
 
 def _seed_columns(ranked, blitz, tier):
@@ -288,6 +290,42 @@ def _first_appearance(keys):
 
 
 def ingest_rows(rows):
+    """Participant rows -> columns, by the native host routine (ts_ingest_rows, csrc/ingest.cu); same
+    contract and same result as ingest_rows_numpy below, whose docstring lists the columns."""
+    lib = L.lib()
+    col = lambda k, dt: np.ascontiguousarray(rows[k], dtype=dt)
+    keep = [col("match", np.int64), col("player", np.int64), col("game_mode", np.int32), col("n_rosters", np.int32),
+            col("roster", np.int32), col("skill_tier", np.int32), col("winner", np.uint8), col("went_afk", np.uint8),
+            col("rank_points_ranked", np.float64), col("rank_points_blitz", np.float64), col("trueskill_mu", np.float64),
+            col("trueskill_sigma", np.float64), col("queue", np.float64)]
+    n = keep[0].shape[0]
+    rc_ = L.TsRowColumns()
+    rc_.n_rows = n
+    for name, arr in zip(("match", "player", "game_mode", "n_rosters", "roster", "skill_tier", "winner", "went_afk",
+                          "rank_points_ranked", "rank_points_blitz", "trueskill_mu", "trueskill_sigma", "queue"), keep):
+        setattr(rc_, name, arr.ctypes.data)
+    cap = max(n, 1)
+    match_keys, player_keys = np.empty(cap, np.int64), np.empty(cap, np.int64)
+    row_match, row_slot, row_player = np.empty(cap, np.int32), np.empty(cap, np.int32), np.empty(cap, np.int32)
+    ids, meta = np.empty(cap * 10, np.uint32), np.empty(cap, np.uint32)
+    table, seed = np.full(cap * 16, np.nan), np.full(cap * 2, np.nan)
+    nm, npl, slots = C.c_int64(0), C.c_int64(0), C.c_int32(6)
+    ptr = lambda a: C.c_void_p(a.ctypes.data)
+    L.check(lib.ts_ingest_rows(C.byref(rc_), float(UNKNOWN_PLAYER_SIGMA), _VST_C, ptr(match_keys), ptr(player_keys),
+                               ptr(row_match), ptr(row_slot), ptr(row_player), ptr(ids), ptr(meta), ptr(table), ptr(seed),
+                               C.byref(nm), C.byref(npl), C.byref(slots)))
+    nm, npl, slots = nm.value, npl.value, slots.value
+    b = RowBatch()
+    b.n_rows, b.slots = n, slots
+    b.match_keys, b.player_keys = match_keys[:nm], player_keys[:npl]
+    b.row_match, b.row_slot, b.row_player = row_match[:n], row_slot[:n], row_player[:n]
+    b.ids, b.meta = ids[:nm * slots].reshape(nm, slots), meta[:nm]
+    u = max(npl, 1)
+    b.table, b.seed = table[:u * 16].reshape(u, 8, 2), seed[:u * 2].reshape(u, 2)
+    return b
+
+
+def ingest_rows_numpy(rows):
     """Participant rows -> columns.  `rows`: a mapping (or numpy structured array) of equally long
     columns, one entry per participant in the order the query yields them (matches by created_at,
     worker.py:177):

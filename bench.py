@@ -61,6 +61,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=15.0)
     ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--host-numa", dest="numa", default="local", choices=["none", "local", "interleave"],
+                    help="memory policy for the pinned host buffers of the e2e leg when several ranks run (see numa_policy)")
     ap.add_argument("--no-configs", action="store_true", help="skip the configs block (configs 3 and 4 at full size) at N = 1")
     ap.add_argument("--no-sharded", action="store_true", help="skip the one-ladder-over-all-ranks block at N > 1")
     ap.add_argument("--sharded-matches", type=int, default=100_000_000)
@@ -691,6 +693,36 @@ def sharded_block(a, rater, engine, dist, rank, world, dev, n, u, p, steps=5, wa
     return out
 
 
+def numa_policy(local, mode):
+    """Memory policy for this process's pinned host buffers (set before they are allocated): 'local' =
+    prefer the NUMA node of this rank's GPU, 'interleave' = spread pages over all nodes.  With several
+    ranks copying at once the host side of the H2D copies is what bounds e2e.  Returns what was done."""
+    import ctypes
+    import glob
+    import torch
+    try:
+        nodes = sorted(int(p.rsplit("node", 1)[1]) for p in glob.glob("/sys/devices/system/node/node[0-9]*"))
+        pr = torch.cuda.get_device_properties(local)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        try:
+            gpu_node = int(open("/sys/bus/pci/devices/%s/numa_node" % bdf).read())
+        except Exception:
+            gpu_node = -1
+        info = {"nodes": nodes, "gpu_node": gpu_node, "mode": mode}
+        if mode == "none" or len(nodes) < 2:
+            return info
+        libc = ctypes.CDLL("libc.so.6", use_errno=True)
+        if mode == "local" and gpu_node >= 0:
+            mask, pol = ctypes.c_ulong(1 << gpu_node), 1          # MPOL_PREFERRED
+        else:
+            mask, pol = ctypes.c_ulong(sum(1 << n for n in nodes)), 3     # MPOL_INTERLEAVE
+        rc = libc.syscall(238, pol, ctypes.byref(mask), ctypes.c_ulong(64))   # set_mempolicy (x86_64)
+        info["rc"] = rc if rc == 0 else -ctypes.get_errno()
+        return info
+    except Exception as exc:
+        return {"error": repr(exc)}
+
+
 # ---------------------------------------------------------------------------
 def run_b200(a):
     import numpy as np
@@ -791,6 +823,7 @@ def run_b200(a):
     # ---- e2e: the reference-facing call with pinned host buffers -----------
     e2e = None
     if not a.skip_e2e:
+        numa = numa_policy(local, a.numa) if world > 1 else None
         # the id column at the width it needs (ceil(log2(U + 1)) bits per id, widened on the device) ...
         ids_h = engine.pack_ids(ids_d.cpu().numpy().view(np.uint32), u, pin=True)
         meta_h = meta_d.cpu().to(torch.uint8).pin_memory()    # the meta word uses 8 bits: shipped as bytes
@@ -815,6 +848,7 @@ def run_b200(a):
         h2d = ids_h.nbytes + meta_h.numel() * meta_h.element_size() + tab_h.numel() * 8
         e2e = {"value": n * world / dt, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": out_h.numel() * 8 + 8 + 16, "ms_per_step": dt * 1e3, "steps": k_e2e,
+               "numa": numa,
                "ingest": "ids packed at %d bits each (ts_unpack_ids), meta as bytes (ts_widen_meta), table float64; "
                          "copies pipelined with link + rate over windows" % ids_h.bits}
 

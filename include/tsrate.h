@@ -349,6 +349,27 @@ int ts_widen_meta(const uint8_t *meta8, int64_t n_matches, uint32_t *meta, void 
  * of the column that bounds the end-to-end call.  No counterpart in the reference. */
 int ts_unpack_ids(const uint8_t *packed, int32_t bits, int64_t count, uint32_t *ids, void *stream);
 
+/* Columnar ingest on the host (no device work): the participant rows the query of
+ * worker.py:176-191 yields -- one row per participant, matches in created_at order -- become the
+ * columns above.  game_mode 0..5 in rater.py:70-82's order (anything else: unsupported), roster 0 / 1,
+ * NaN = None / NULL for the doubles, queue = the player's six trueskill_<mode> pairs [n_rows][6][2].
+ * Outputs, all caller-allocated for n_rows entries (ids: 10 * n_rows, table: 16 * n_rows doubles as
+ * [players][8][2] with col 0 shared and 1..6 the queues, seed: 2 * n_rows): matches and players in
+ * order of first appearance with their keys, every row's match / slot (-1: not on roster 0 or 1) /
+ * player index, ids [n_matches][slots] (slots = 6 or 10 by the widest roster), meta, table, seed
+ * (get_trueskill_seed, rater.py:42-62; NaN where the reference raises KeyError). */
+typedef struct ts_row_columns {
+    int64_t n_rows;
+    const int64_t *match, *player;
+    const int32_t *game_mode, *n_rosters, *roster, *skill_tier;
+    const uint8_t *winner, *went_afk;
+    const double *rank_points_ranked, *rank_points_blitz, *trueskill_mu, *trueskill_sigma, *queue;
+} ts_row_columns;
+int ts_ingest_rows(const ts_row_columns *rows, double unknown_player_sigma, const double vst_points[31],
+                   int64_t *match_keys, int64_t *player_keys, int32_t *row_match, int32_t *row_slot, int32_t *row_player,
+                   uint32_t *ids, uint32_t *meta, double *table, double *seed, int64_t *n_matches, int64_t *n_players,
+                   int32_t *slots);
+
 /* Synthetic ladders of BASELINE.json's configs (SURVEY.md 8d "Generator"):
  * counter-based, so any window [first, first+count) can be produced on its
  * own.  No counterpart in the reference (it has no benchmark input). */

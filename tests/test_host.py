@@ -136,7 +136,13 @@ def test_ingest_rows_equals_object_ingest():
     matches = H.run_objects(lambda m: None, ids, meta, table, tier, ranked, blitz)["matches"]
     a = rater.ingest(matches)
     rows, _ = H.rows_from_matches(matches)
-    b = rater.ingest_rows(rows)
+    b = rater.ingest_rows(rows)                      # the native routine ...
+    c = rater.ingest_rows_numpy(rows)                # ... and its numpy twin: the same columns
+    assert b.slots == c.slots and np.array_equal(b.ids, c.ids) and np.array_equal(b.meta, c.meta)
+    assert np.array_equal(b.table, c.table, equal_nan=True) and np.array_equal(b.seed, c.seed, equal_nan=True)
+    assert np.array_equal(b.player_keys, c.player_keys) and np.array_equal(b.match_keys, c.match_keys)
+    assert np.array_equal(b.row_match, c.row_match) and np.array_equal(b.row_slot, c.row_slot)
+    assert np.array_equal(b.row_player, c.row_player)
     assert b.slots == a.slots and np.array_equal(a.meta, b.meta)
     key_of_a = np.array([id(p) for p in a.players] + [0], dtype=np.int64)
     key_of_b = np.r_[b.player_keys, 0]
