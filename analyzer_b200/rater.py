@@ -308,7 +308,7 @@ def ingest_rows(rows):
     match_keys, player_keys = np.empty(cap, np.int64), np.empty(cap, np.int64)
     row_match, row_slot, row_player = np.empty(cap, np.int32), np.empty(cap, np.int32), np.empty(cap, np.int32)
     ids, meta = np.empty(cap * 10, np.uint32), np.empty(cap, np.uint32)
-    table, seed = np.full(cap * 16, np.nan), np.full(cap * 2, np.nan)
+    table, seed = np.empty(cap * 16), np.empty(cap * 2)          # every used row is written in full by the routine
     nm, npl, slots = C.c_int64(0), C.c_int64(0), C.c_int32(6)
     ptr = lambda a: C.c_void_p(a.ctypes.data)
     L.check(lib.ts_ingest_rows(C.byref(rc_), float(UNKNOWN_PLAYER_SIGMA), _VST_C, ptr(match_keys), ptr(player_keys),
@@ -321,6 +321,8 @@ def ingest_rows(rows):
     b.row_match, b.row_slot, b.row_player = row_match[:n], row_slot[:n], row_player[:n]
     b.ids, b.meta = ids[:nm * slots].reshape(nm, slots), meta[:nm]
     u = max(npl, 1)
+    if npl == 0:
+        table[:16], seed[:2] = np.nan, np.nan
     b.table, b.seed = table[:u * 16].reshape(u, 8, 2), seed[:u * 2].reshape(u, 2)
     return b
 
