@@ -64,8 +64,9 @@ extern "C" int ts_ingest_rows(const ts_row_columns *rows, double unknown_sigma, 
     std::vector<uint8_t> flags;            // per match: bit 0/1 a winner flag on roster 0/1, bit 2 an AFK participant
     int widest = 1;
     for (int64_t i = 0; i < n; ++i) {
-        bool fresh;
-        const int32_t m = matches.get(rows->match[i], &fresh);
+        bool fresh = false;
+        // the rows of a match usually follow each other: no lookup then
+        const int32_t m = (i > 0 && rows->match[i] == rows->match[i - 1]) ? row_match[i - 1] : matches.get(rows->match[i], &fresh);
         if (fresh) { match_keys[m] = rows->match[i]; first_row_of_match.push_back((int32_t)i); count.push_back(0); count.push_back(0); flags.push_back(0); }
         const int32_t p = players.get(rows->player[i], &fresh);
         if (fresh) { player_keys[p] = rows->player[i]; first_row_of_player.push_back((int32_t)i); }
