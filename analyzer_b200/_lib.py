@@ -31,7 +31,8 @@ EXPORTS = ["ts_ctx_create", "ts_ctx_destroy", "ts_last_error", "ts_sm_count",
            "ts_stream_stalled", "ts_rate_stream_table_workspace_bytes",
            "ts_seed_table", "ts_widen_meta", "ts_unpack_ids", "ts_error_counts", "ts_slot_rows_bytes", "ts_link_succ", "ts_rate_slots", "ts_ingest_rows",
            "ts_shard_alloc", "ts_shard_open", "ts_shard_close", "ts_shard_free", "ts_shard_local_matches",
-           "ts_shard_link_workspace_bytes", "ts_shard_inbox_cap", "ts_shard_reset", "ts_shard_link", "ts_shard_rate", "ts_shard_status"]
+           "ts_shard_link_workspace_bytes", "ts_shard_inbox_cap", "ts_shard_reset", "ts_shard_link", "ts_shard_rate", "ts_shard_status",
+           "ts_shard_exchange_workspace_bytes", "ts_shard_count", "ts_shard_send"]
 SHARD_BLOCK, SHARD_MAX = 32, 16
 SHARD_STALLED, SHARD_OVERFLOW, SHARD_DUPLICATE = 1, 2, 4
 
@@ -62,7 +63,9 @@ class TsShardView(C.Structure):
                 ("ids", C.c_void_p * 16), ("meta", C.c_void_p * 16), ("succ", C.c_void_p * 16),
                 ("rows", C.c_void_p * 16), ("table", C.c_void_p * 16), ("inbox", C.c_void_p * 16),
                 ("inbox_count", C.c_void_p * 16), ("inbox_cap", C.c_int64), ("ring", C.c_void_p * 16),
-                ("ring_final", C.c_void_p * 16), ("ring_tail", C.c_void_p * 16), ("ring_cap", C.c_int64), ("ring_epoch", C.c_int64)]
+                ("ring_final", C.c_void_p * 16), ("ring_tail", C.c_void_p * 16), ("ring_cap", C.c_int64), ("ring_epoch", C.c_int64),
+                ("link_counts", C.c_void_p * 16), ("in_keys", C.c_void_p * 16), ("in_vals", C.c_void_p * 16),
+                ("in_count", C.c_void_p * 16), ("in_cap", C.c_int64), ("link_blocks_cap", C.c_int64)]
 
 
 class TsRowColumns(C.Structure):
@@ -158,6 +161,11 @@ def lib():
         L.ts_shard_rate.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_int32, C.c_int64, C.c_int8,
                                     C.c_int64, C.POINTER(TsOutputs), C.c_int32, C.c_int32, C.c_void_p]
         L.ts_shard_status.argtypes = [C.c_void_p, C.c_void_p]
+        L.ts_shard_exchange_workspace_bytes.restype = C.c_int64
+        L.ts_shard_exchange_workspace_bytes.argtypes = [C.c_int64, C.c_int32]
+        L.ts_shard_count.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_int32, C.c_int64, C.c_int8, C.c_void_p]
+        L.ts_shard_send.argtypes = [C.c_void_p, C.POINTER(TsShardView), C.c_int64, C.c_int32, C.c_int64, C.c_int8,
+                                    C.c_void_p, C.c_int64, C.c_void_p]
         L.ts_error_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.c_void_p]
         L.ts_slot_rows_bytes.restype = C.c_int64
         L.ts_slot_rows_bytes.argtypes = [C.c_int64, C.c_int32]

@@ -921,11 +921,13 @@ int radix_onesweep_enabled()
 // Returns the index of the buffer holding the result (or <0).
 // staged: the pairs already stand in w.keys[0] / w.vals[0] and their number in *n_dev
 // (n is then only an upper bound that sizes the grids): the owned slots of a sharded ladder.
+// ext_vals (staged only): the pairs stand in src0.keys / ext_vals instead (memory the peers wrote).
 int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStream_t stream, int sm_count,
-               const uint32_t *n_dev = nullptr, const uint32_t *key_bound = nullptr)
+               const uint32_t *n_dev = nullptr, const uint32_t *key_bound = nullptr, const uint32_t *ext_vals = nullptr)
 {
     const int passes = (bits + 7) / 8;
     const bool staged = n_dev != nullptr;
+    if (ext_vals && (!staged || passes < 1)) return TS_E_ARG;
     if (n >= (1u << 30) || passes > kMaxPasses || !radix_onesweep_enabled()) {
         if (key_bound) return TS_E_UNSUPPORTED;      // the caller sizes the sort on the host instead
         if (staged) {
@@ -946,8 +948,9 @@ int radix_sort(const KeySrc &src0, uint32_t n, int bits, Workspace &w, cudaStrea
     for (int p = 0; p < passes; ++p) {
         KeySrc src = src0;
         const uint32_t *vals_in = nullptr;
-        if (cur >= 0) { src.keys = w.keys[cur]; src.from_ids = 0; vals_in = w.vals[cur]; }
         int dst = cur < 0 ? 0 : ((cur + 1) & 1);
+        if (ext_vals && p == 0) { vals_in = ext_vals; dst = 0; }
+        else if (cur >= 0) { src.keys = w.keys[cur]; src.from_ids = 0; vals_in = w.vals[cur]; }
         if (cudaMemsetAsync(w.hist, 0, (size_t)n_tiles * 256 * 4, stream) != cudaSuccess ||
             cudaMemsetAsync(ticket, 0, 4, stream) != cudaSuccess)
             return ts_cuda_fail(cudaGetLastError(), "memset");
@@ -1613,6 +1616,221 @@ void shard_ranges(uint64_t entries, int n_shards, uint32_t *n_ranges, uint32_t *
     *n_ranges = (uint32_t)std::max<uint64_t>(1, (entries + (1ull << sh) - 1) >> sh);
 }
 
+// ---------------------------------------------------------------------------
+// The owned (player, slot) pairs WITHOUT every rank reading the whole id stream: every rank looks
+// at its own slice only and sends each pair to the player's owner, to the exact place it has in
+// stream order there.  Per block of 32 matches and owner the number of pairs is counted
+// (k_block_owned<false>), the counts of all ranks are exchanged (host: one small all-gather), an
+// exclusive scan over the blocks in GLOBAL order (k_chunk_sums / k_chunk_scan / k_block_offsets)
+// gives every (block, owner) its offset in the owner's input, and k_block_owned<true> stores the
+// pairs there -- consecutive pairs of a block to consecutive addresses of the owner's memory, a
+// few hundred bytes at a time over NVLink.  Link work per rank ~ 1/G of the stream.
+// ---------------------------------------------------------------------------
+struct ExchSrc {
+    const uint32_t *ids, *meta;     // own slice
+    uint32_t n_local;               // matches in it
+    uint32_t g_mask, g_shift, me;
+    uint32_t slots, rated_mask, n_players;
+    uint32_t nb_cap;                // blocks per rank the count / offset arrays are laid out for
+};
+struct ExchDst {
+    uint32_t *in_keys[TS_SHARD_MAX], *in_vals[TS_SHARD_MAX];
+    uint32_t in_cap;
+};
+struct ExchPeers {
+    uint4 *counts[TS_SHARD_MAX];    // every rank's link_counts at sender = me
+};
+
+// one CUDA block = one block of 32 matches of the own slice, one thread per slot (32 * slots threads).
+// SEND: the block's pairs are first grouped by owner in shared memory, so that the pairs for one
+// owner leave as one run of consecutive 4-byte stores (about 32 * slots / G of them).
+template <bool SEND>
+__global__ void k_block_owned(ExchSrc src, uint16_t *cnt_local, const uint32_t *off_mine, ExchDst dst, unsigned long long *ctrl)
+{
+    __shared__ uint16_t wcnt[TS_MAX_SLOTS][TS_SHARD_MAX];    // per warp, per owner
+    __shared__ uint32_t seg[TS_SHARD_MAX + 1];               // start of every owner's run inside the block
+    __shared__ uint32_t skey[32 * TS_MAX_SLOTS], sval[32 * TS_MAX_SLOTS];
+    const uint32_t lb = blockIdx.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, n_warps = blockDim.x >> 5;
+    const uint32_t G = src.g_mask + 1u;
+    const uint32_t lm = lb * 32u + t / src.slots, sl = t % src.slots;
+    uint32_t owner = 0xFFu, key = 0;
+    if (lm < src.n_local) {
+        const uint32_t k = src.ids[(size_t)lm * src.slots + sl];
+        if (k != TS_EMPTY_SLOT && k < src.n_players) {
+            const uint32_t mt = src.meta[lm];
+            const bool gated = ((src.rated_mask >> ((mt >> TS_META_MODE_SHIFT) & 15u)) & 1u) == 0u ||
+                               (mt & (TS_META_AFK | TS_META_INVALID)) != 0u;
+            if (!gated) { owner = k & src.g_mask; key = k >> src.g_shift; }
+        }
+    }
+    // place among the slots of the same owner inside this warp, in slot order
+    uint32_t before_in_warp = 0;
+    for (uint32_t o = 0; o < G; ++o) {
+        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, owner == o);
+        if (owner == o) before_in_warp = __popc(bal & ((1u << lane) - 1u));
+        if (lane == 0) wcnt[warp][o] = (uint16_t)__popc(bal);
+    }
+    __syncthreads();
+    if (!SEND) {
+        if (t < G) {
+            uint32_t c = 0;
+            for (uint32_t w = 0; w < n_warps; ++w) c += wcnt[w][t];
+            cnt_local[(size_t)t * src.nb_cap + lb] = (uint16_t)c;
+        }
+        return;
+    }
+    if (t == 0) {
+        uint32_t run = 0;
+        for (uint32_t o = 0; o < G; ++o) {
+            seg[o] = run;
+            for (uint32_t w = 0; w < n_warps; ++w) run += wcnt[w][o];
+        }
+        seg[G] = run;
+    }
+    __syncthreads();
+    if (owner != 0xFFu) {
+        uint32_t lp = seg[owner] + before_in_warp;
+        for (uint32_t w = 0; w < warp; ++w) lp += wcnt[w][owner];
+        // slot index of the window: the stream-wide number of local match lm of this rank
+        const uint32_t m = ((((lm >> 5) << src.g_shift) | src.me) << 5) | (lm & 31u);
+        skey[lp] = key;
+        sval[lp] = m * src.slots + sl;
+    }
+    __syncthreads();
+    if (t < seg[G]) {
+        uint32_t o = 0;
+        while (t >= seg[o + 1]) ++o;
+        const uint32_t pos = __ldg(off_mine + (size_t)o * src.nb_cap + lb) + (t - seg[o]);
+        if (pos < dst.in_cap) { dst.in_keys[o][pos] = skey[t]; dst.in_vals[o][pos] = sval[t]; }
+    }
+}
+
+// own counts [G owners][nb_cap] -> the same place (sender = me) in every peer's link_counts
+__global__ void __launch_bounds__(256) k_push_counts(const uint4 *own, ExchPeers peers, uint32_t me, uint32_t G, size_t n16)
+{
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n16; i += (size_t)gridDim.x * 256) {
+        const uint4 v = own[i];
+        for (uint32_t g = 0; g < G; ++g)
+            if (g != me) peers.counts[g][i] = v;
+    }
+}
+
+// cnt_all[sender][owner][nb_cap] (16-bit); global block b = lb * G + sender.  A chunk = 4096 global blocks.
+constexpr uint32_t kExchChunk = 4096;
+
+__device__ __forceinline__ uint32_t exch_count(const uint16_t *cnt_all, uint32_t b, uint32_t owner, uint32_t g_mask,
+                                               uint32_t g_shift, uint32_t nb_cap, uint32_t n_blocks)
+{
+    if (b >= n_blocks) return 0u;
+    const uint32_t sender = b & g_mask, lb = b >> g_shift;
+    return cnt_all[((size_t)sender * (g_mask + 1u) + owner) * nb_cap + lb];
+}
+
+__global__ void __launch_bounds__(256)
+k_chunk_sums(const uint16_t *cnt_all, uint32_t g_mask, uint32_t g_shift, uint32_t nb_cap, uint32_t n_blocks, uint32_t n_chunks,
+             uint32_t *partial)
+{
+    __shared__ uint32_t red[8];
+    const uint32_t owner = blockIdx.y, chunk = blockIdx.x;
+    uint32_t sum = 0;
+    for (uint32_t i = threadIdx.x; i < kExchChunk; i += 256)
+        sum += exch_count(cnt_all, chunk * kExchChunk + i, owner, g_mask, g_shift, nb_cap, n_blocks);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xFFFFFFFFu, sum, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sum;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tot = 0;
+        for (int w = 0; w < 8; ++w) tot += red[w];
+        partial[(size_t)owner * n_chunks + chunk] = tot;
+    }
+}
+
+// one block per owner: exclusive scan of its chunk sums in place; the owner's total to totals[owner]
+// (rank `me` also stores its total, clamped to in_cap, as the number of pairs it receives)
+__global__ void __launch_bounds__(1024) k_chunk_scan(uint32_t *partial, uint32_t n_chunks, uint32_t *totals, uint32_t me,
+                                                     uint32_t in_cap, uint32_t *in_count, unsigned long long *ctrl)
+{
+    __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry;
+    uint32_t *row = partial + (size_t)blockIdx.x * n_chunks;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_chunks; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t x = i < n_chunks ? row[i] : 0u;
+        uint32_t incl = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if ((threadIdx.x & 31) >= o) incl += y;
+        }
+        if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = incl;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            const uint32_t w = warp_sums[threadIdx.x];
+            uint32_t wi = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, wi, o);
+                if (threadIdx.x >= o) wi += y;
+            }
+            warp_sums[threadIdx.x] = wi - w;
+        }
+        __syncthreads();
+        const uint32_t excl = carry + warp_sums[threadIdx.x >> 5] + incl - x;
+        if (i < n_chunks) row[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + x;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        totals[blockIdx.x] = carry;
+        if (blockIdx.x == me) {
+            *in_count = min(carry, in_cap);
+            if (carry > in_cap) atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
+        }
+    }
+}
+
+// offsets of this rank's own blocks: off_mine[owner][lb] = pairs for `owner` in all global blocks before (lb, me)
+__global__ void __launch_bounds__(256)
+k_block_offsets(const uint16_t *cnt_all, const uint32_t *partial, uint32_t g_mask, uint32_t g_shift, uint32_t me,
+                uint32_t nb_cap, uint32_t n_blocks, uint32_t n_chunks, uint32_t *off_mine)
+{
+    __shared__ uint32_t warp_sums[8];
+    const uint32_t owner = blockIdx.y, chunk = blockIdx.x;
+    constexpr uint32_t per = kExchChunk / 256;             // consecutive global blocks per thread
+    const uint32_t b0 = chunk * kExchChunk + threadIdx.x * per;
+    uint32_t c[per], sum = 0;
+#pragma unroll
+    for (uint32_t j = 0; j < per; ++j) { c[j] = exch_count(cnt_all, b0 + j, owner, g_mask, g_shift, nb_cap, n_blocks); sum += c[j]; }
+    uint32_t incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if ((threadIdx.x & 31) >= (unsigned)o) incl += y;
+    }
+    if ((threadIdx.x & 31) == 31) warp_sums[threadIdx.x >> 5] = incl;
+    __syncthreads();
+    uint32_t run = partial[(size_t)owner * n_chunks + chunk] + incl - sum;
+    for (uint32_t w = 0; w < (threadIdx.x >> 5); ++w) run += warp_sums[w];
+#pragma unroll
+    for (uint32_t j = 0; j < per; ++j) {
+        const uint32_t b = b0 + j;
+        if (b < n_blocks && (b & g_mask) == me) off_mine[(size_t)owner * nb_cap + (b >> g_shift)] = run;
+        run += c[j];
+    }
+}
+
+// the number of pairs ts_shard_send left for this rank, bounded by what the sort's buffers hold
+__global__ void k_take_count(const uint32_t *in_count, uint32_t cap, uint32_t *n_out, unsigned long long *ctrl)
+{
+    const uint32_t n = *in_count;
+    *n_out = min(n, cap);
+    if (n > cap) atomicOr(&ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
+}
+
 int check_view(const ts_shard_view *v, const char *who)
 {
     if (!v || v->n_shards < 1 || v->n_shards > TS_SHARD_MAX || (v->n_shards & (v->n_shards - 1)) || v->rank < 0 ||
@@ -1672,6 +1890,122 @@ extern "C" int64_t ts_shard_link_workspace_bytes(int64_t n_slot_entries, int64_t
            (int64_t)align_up((size_t)(tiles + 1) * 4);
 }
 
+namespace {
+
+uint32_t exch_blocks(int64_t n_matches) { return (uint32_t)((n_matches + TS_SHARD_BLOCK - 1) / TS_SHARD_BLOCK); }
+
+int check_exchange(const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players, int mode, const char *who)
+{
+    if (int rc = check_view(view, who)) return rc;
+    const int G = view->n_shards;
+    if (n_matches < 0 || slots < 2 || slots > TS_MAX_SLOTS || (slots & 1) || n_players < 1 || n_players >= 0xFFFFFFFFll ||
+        (uint64_t)n_matches * (uint64_t)slots >= 0xFFFF0000ull || mode < 0 || mode > 5) {
+        ts_set_error("%s: bad sizes (n_matches * slots must stay below 2^32 - 2^16, mode 0..5)", who);
+        return TS_E_ARG;
+    }
+    if (view->link_blocks_cap < 8 || (view->link_blocks_cap & 7) || view->in_cap < 1 || view->in_cap >= 0xFFFF0000ll ||
+        (int64_t)(exch_blocks(n_matches) + G - 1) / G > view->link_blocks_cap) {
+        ts_set_error("%s: link_blocks_cap (a multiple of 8) or in_cap too small for the window", who);
+        return TS_E_ARG;
+    }
+    for (int g = 0; g < G; ++g)
+        if (!view->link_counts[g] || !view->in_keys[g] || !view->in_vals[g] || !view->ids[view->rank] || !view->meta[view->rank] ||
+            !view->in_count[view->rank]) {
+            ts_set_error("%s: shard %d's link exchange arrays not mapped", who, g);
+            return TS_E_ARG;
+        }
+    return 0;
+}
+
+ExchSrc exchange_src(const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players, int mode)
+{
+    const int G = view->n_shards, rank = view->rank;
+    int shift = 0;
+    while ((1 << shift) < G) ++shift;
+    ExchSrc src;
+    src.ids = view->ids[rank];
+    src.meta = view->meta[rank];
+    src.n_local = (uint32_t)ts_shard_local_matches(n_matches, rank, G);
+    src.g_mask = (uint32_t)G - 1u;
+    src.g_shift = (uint32_t)shift;
+    src.me = (uint32_t)rank;
+    src.slots = (uint32_t)slots;
+    src.rated_mask = 1u << mode;
+    src.n_players = (uint32_t)n_players;
+    src.nb_cap = (uint32_t)view->link_blocks_cap;
+    return src;
+}
+
+}  // namespace
+
+extern "C" int64_t ts_shard_exchange_workspace_bytes(int64_t n_matches, int32_t n_shards)
+{
+    if (n_matches < 0 || n_shards < 1 || n_shards > TS_SHARD_MAX) return TS_E_ARG;
+    const int64_t n_blocks = exch_blocks(n_matches), n_chunks = (n_blocks + kExchChunk - 1) / kExchChunk;
+    const int64_t nb_cap = ((n_blocks + n_shards - 1) / n_shards + 7) & ~7ll;
+    return (int64_t)align_up((size_t)n_shards * (size_t)(n_chunks + 1) * 4) + 256 + (int64_t)align_up((size_t)n_shards * (size_t)nb_cap * 4);
+}
+
+extern "C" int ts_shard_count(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
+                              int8_t mode, void *stream)
+{
+    if (!ctx) return TS_E_ARG;
+    if (int rc = check_exchange(view, n_matches, slots, n_players, mode, "ts_shard_count")) return rc;
+    if (n_matches == 0) return 0;
+    TS_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    const int G = view->n_shards, rank = view->rank;
+    const ExchSrc src = exchange_src(view, n_matches, slots, n_players, mode);
+    const size_t per_sender = (size_t)G * src.nb_cap;               // 16-bit counts of one sender
+    uint16_t *own = view->link_counts[rank] + (size_t)rank * per_sender;
+    const uint32_t nb_local = (src.n_local + 31u) / 32u;
+    if (nb_local) k_block_owned<false><<<nb_local, 32 * slots, 0, s>>>(src, own, nullptr, ExchDst(), ctx->d_ctrl);
+    if (G > 1) {
+        ExchPeers peers;
+        for (int g = 0; g < TS_SHARD_MAX; ++g)
+            peers.counts[g] = g < G ? reinterpret_cast<uint4 *>(view->link_counts[g] + (size_t)rank * per_sender) : nullptr;
+        const size_t n16 = per_sender * 2 / 16;
+        k_push_counts<<<(unsigned)std::min<size_t>((n16 + 255) / 256, (size_t)ctx->sm_count * 4), 256, 0, s>>>(
+            reinterpret_cast<const uint4 *>(own), peers, (uint32_t)rank, (uint32_t)G, n16);
+    }
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int ts_shard_send(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
+                             int8_t mode, void *workspace, int64_t workspace_bytes, void *stream)
+{
+    if (!ctx) return TS_E_ARG;
+    if (int rc = check_exchange(view, n_matches, slots, n_players, mode, "ts_shard_send")) return rc;
+    if (n_matches == 0) return 0;
+    const int G = view->n_shards, rank = view->rank;
+    const uint32_t n_blocks = exch_blocks(n_matches), n_chunks = (n_blocks + kExchChunk - 1) / kExchChunk;
+    const ExchSrc src = exchange_src(view, n_matches, slots, n_players, mode);
+    const size_t partial_bytes = align_up((size_t)G * (n_chunks + 1) * 4), off_bytes = align_up((size_t)G * src.nb_cap * 4);
+    if (!workspace || ((uintptr_t)workspace & 15u) || (int64_t)(partial_bytes + 256 + off_bytes) > workspace_bytes) {
+        ts_set_error("ts_shard_send: workspace too small (ts_shard_exchange_workspace_bytes) or not 16-byte aligned");
+        return TS_E_WORKSPACE;
+    }
+    TS_CUDA(cudaSetDevice(ctx->device));
+    cudaStream_t s = (cudaStream_t)stream;
+    uint32_t *partial = (uint32_t *)workspace;
+    uint32_t *totals = (uint32_t *)((char *)workspace + partial_bytes);
+    uint32_t *off_mine = (uint32_t *)((char *)workspace + partial_bytes + 256);
+    const uint16_t *cnt_all = view->link_counts[rank];
+    k_chunk_sums<<<dim3(n_chunks, (unsigned)G), 256, 0, s>>>(cnt_all, src.g_mask, src.g_shift, src.nb_cap, n_blocks, n_chunks, partial);
+    k_chunk_scan<<<(unsigned)G, 1024, 0, s>>>(partial, n_chunks, totals, (uint32_t)rank, (uint32_t)view->in_cap, view->in_count[rank],
+                                              ctx->d_ctrl);
+    k_block_offsets<<<dim3(n_chunks, (unsigned)G), 256, 0, s>>>(cnt_all, partial, src.g_mask, src.g_shift, (uint32_t)rank, src.nb_cap,
+                                                                n_blocks, n_chunks, off_mine);
+    ExchDst dst;
+    for (int g = 0; g < TS_SHARD_MAX; ++g) { dst.in_keys[g] = g < G ? view->in_keys[g] : nullptr; dst.in_vals[g] = g < G ? view->in_vals[g] : nullptr; }
+    dst.in_cap = (uint32_t)view->in_cap;
+    const uint32_t nb_local = (src.n_local + 31u) / 32u;
+    if (nb_local) k_block_owned<true><<<nb_local, 32 * slots, 0, s>>>(src, nullptr, off_mine, dst, ctx->d_ctrl);
+    TS_CUDA(cudaGetLastError());
+    return 0;
+}
+
 extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
                              int8_t mode, int64_t seq_base, void *workspace, int64_t workspace_bytes, void *stream)
 {
@@ -1698,10 +2032,16 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     }
     // workspace: the sort's buffers for `cap` owned pairs (ts_link_workspace_bytes), then the staging
     // array of the compaction (8 bytes per slot of the window) and its tile counts
+    // (link exchange, view->in_keys set: the pairs were sent here by ts_shard_send -- no staging)
+    const bool exchanged = view->in_keys[rank] != nullptr;
+    if (exchanged && (!view->in_vals[rank] || !view->in_count[rank] || view->in_cap < 1)) {
+        ts_set_error("ts_shard_link: in_keys without in_vals / in_count / in_cap");
+        return TS_E_ARG;
+    }
     const uint32_t np = (uint32_t)n_matches * (uint32_t)slots;
-    const int64_t compact_tiles = ((int64_t)np + kSortTile - 1) / kSortTile;
+    const int64_t compact_tiles = exchanged ? 0 : ((int64_t)np + kSortTile - 1) / kSortTile;
     const int64_t stage_bytes = (int64_t)align_up((size_t)compact_tiles * kSortTile * 8) + (int64_t)align_up((size_t)(compact_tiles + 1) * 4);
-    int64_t cap = np;
+    int64_t cap = exchanged ? std::min<int64_t>(np, view->in_cap) : np;
     while (cap > 0 && ts_link_workspace_bytes(cap / 2 + 1, 2) + stage_bytes > workspace_bytes) cap -= (cap + 15) / 16;
     if (cap < 1 || !workspace) {
         ts_set_error("ts_shard_link: workspace too small");
@@ -1729,13 +2069,17 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     src.rated_mask = 1u << mode;
     src.n_players = (uint32_t)n_players;
     TS_CUDA(cudaMemsetAsync(w.totals, 0, kTotalsWords * 4, s));
-    k_owned_stage<<<(unsigned)compact_tiles, kSortBlock, 0, s>>>(src, np, staging, tile_counts);
-    k_tile_scan<<<1, 1024, 0, s>>>(tile_counts, (uint32_t)compact_tiles, (uint32_t)cap, n_dev, ctx->d_ctrl);
-    k_owned_gather<<<(unsigned)compact_tiles, kSortBlock, 0, s>>>(staging, tile_counts, (uint32_t)cap, w.keys[0], w.vals[0]);
+    if (exchanged) {
+        k_take_count<<<1, 1, 0, s>>>(view->in_count[rank], (uint32_t)cap, n_dev, ctx->d_ctrl);
+    } else {
+        k_owned_stage<<<(unsigned)compact_tiles, kSortBlock, 0, s>>>(src, np, staging, tile_counts);
+        k_tile_scan<<<1, 1024, 0, s>>>(tile_counts, (uint32_t)compact_tiles, (uint32_t)cap, n_dev, ctx->d_ctrl);
+        k_owned_gather<<<(unsigned)compact_tiles, kSortBlock, 0, s>>>(staging, tile_counts, (uint32_t)cap, w.keys[0], w.vals[0]);
+    }
     if (timing) cudaEventRecord(tev[1], s);
     const int64_t local_players = (n_players - rank + G - 1) / G;
     KeySrc ks;
-    ks.keys = w.keys[0];
+    ks.keys = exchanged ? view->in_keys[rank] : w.keys[0];
     ks.meta = nullptr;
     for (int i = 0; i < 16; ++i) ks.modes.col[i] = (int8_t)-1;
     ks.slots = 1;
@@ -1743,8 +2087,8 @@ extern "C" int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     ks.from_ids = 0;
     ks.slots_magic = 0ull;
     ks.rated_mask = 0;
-    int buf = radix_sort(ks, (uint32_t)cap, bits_for((uint64_t)(local_players > 0 ? local_players - 1 : 0)), w, s,
-                         ctx->sm_count, n_dev);
+    int buf = radix_sort(ks, (uint32_t)cap, std::max(1, bits_for((uint64_t)(local_players > 0 ? local_players - 1 : 0))), w, s,
+                         ctx->sm_count, n_dev, nullptr, exchanged ? view->in_vals[rank] : nullptr);
     if (buf < 0) return buf;
     if (timing) cudaEventRecord(tev[2], s);
     ShardDst dst;

@@ -120,15 +120,30 @@ def ring_capacity(n_players, n_total, slots, world):
     return int((n_total * slots + n_players) / (world * world) * 1.3) + (1 << 16)
 
 
-def arena_layout(n_players, n_matches_cap, slots, rank, world, n_total=None):
+def link_blocks_capacity(n_matches_cap, world):
+    """Blocks of 32 matches per rank that the link exchange's count arrays are laid out for."""
+    blocks = (n_matches_cap + BLOCK - 1) // BLOCK
+    return max(8, ((blocks + world - 1) // world + 7) & ~7)
+
+
+def owned_capacity(n_matches_cap, slots, world):
+    """(player, slot) pairs one rank can be sent in a window: its share of the slots, with room
+    for uneven ownership (all of them on one GPU)."""
+    np_ = n_matches_cap * slots
+    return max(1, np_) if world == 1 else min(max(1, np_), int(np_ / world * 1.25) + (1 << 16))
+
+
+def arena_layout(n_players, n_matches_cap, slots, rank, world, n_total=None, exchange=True):
     """Byte offsets of (rows, table, ids, meta, succ, inbox, inbox counts, ring, ring finals, ring
-    tails) in rank's arena, and its size.  Every rank computes every rank's layout: peers'
-    pointers are base + offset."""
+    tails, link counts, received keys, received slot indices, received count) in rank's arena,
+    and its size.  Every rank computes every rank's layout: peers' pointers are base + offset."""
     nl = local_matches(n_matches_cap, rank, world)
     ring = ring_capacity(n_players, n_total if n_total is not None else n_matches_cap, slots, world)
+    owned = owned_capacity(n_matches_cap, slots, world) if exchange else 1
+    counts = world * world * link_blocks_capacity(n_matches_cap, world) * 2 if exchange else 1
     sizes = (n_players * ROW_BYTES, max(1, shard_rows(n_players, rank, world)) * 16, max(1, nl) * slots * 4,
              max(1, nl) * 4, max(1, nl) * slots * 4, world * inbox_capacity(n_matches_cap, slots, world) * 8, 1024,
-             world * ring * 32, 128, 256)
+             world * ring * 32, 128, 256, counts, owned * 4, owned * 4, 256)
     offs, o = [], 0
     for sz in sizes:
         offs.append(o)
@@ -144,9 +159,12 @@ class _Raw(object):
 
 
 class ShardedLadder(object):
-    def __init__(self, rater, n_players, n_matches_cap, slots, rank=0, world=1, group=None, emulate=False, n_total=None):
+    def __init__(self, rater, n_players, n_matches_cap, slots, rank=0, world=1, group=None, emulate=False, n_total=None,
+                 exchange=True):
         """n_matches_cap: the largest window; n_total: matches of the whole ladder when it is rated in
-        several windows (the message rings are sized for the run; default: one window)."""
+        several windows (the message rings are sized for the run; default: one window).
+        exchange: links through ts_shard_count / ts_shard_send (every rank reads its own slice only);
+        False: every rank reads the whole stream (ts_shard_link alone)."""
         if world & (world - 1) or not 1 <= world <= L.SHARD_MAX:
             raise ValueError("world size must be a power of two <= %d" % L.SHARD_MAX)
         if n_matches_cap * slots >= 0xFFFF0000:
@@ -157,7 +175,8 @@ class ShardedLadder(object):
         self.device = rater.device.index or 0
         dev = torch.device("cuda", self.device)
         self.n_total = n_total if n_total is not None else n_matches_cap
-        self.layouts = [arena_layout(n_players, n_matches_cap, slots, g, world, self.n_total) for g in range(world)]
+        self.exchange = bool(exchange) and world > 1
+        self.layouts = [arena_layout(n_players, n_matches_cap, slots, g, world, self.n_total, self.exchange) for g in range(world)]
         self.bases = [0] * world
         self.opened, self.own = [], None
         self._keep = []
@@ -211,6 +230,13 @@ class ShardedLadder(object):
         v.inbox_cap = inbox_capacity(self.cap, self.slots, self.world)
         v.ring_cap = ring_capacity(self.n_players, self.n_total, self.slots, self.world)
         v.ring_epoch = self.epoch
+        if self.exchange:
+            for g in range(self.world):
+                offs, _ = self.layouts[g]
+                v.link_counts[g], v.in_keys[g], v.in_vals[g] = self.bases[g] + offs[10], self.bases[g] + offs[11], self.bases[g] + offs[12]
+                v.in_count[g] = self.bases[g] + offs[13]
+            v.in_cap = owned_capacity(self.cap, self.slots, self.world)
+            v.link_blocks_cap = link_blocks_capacity(self.cap, self.world)
         return v
 
     def _stream(self):
@@ -242,13 +268,12 @@ class ShardedLadder(object):
 
     def link(self, n_matches, mode=1, seq_base=0, owned_cap=None, gather=True):
         """succ slices and first rows of the window, for the players this rank owns."""
+        if self.exchange:
+            return self._link_exchange(n_matches, mode, seq_base)
         np_ = n_matches * self.slots
         if owned_cap is None:       # a rank owns ~1/world of the slots; skewed ladders may need more
-            owned_cap = np_ if self.world == 1 else min(np_, int(np_ / self.world * 1.25) + (1 << 16))
-        nbytes = L.check(self.lib.ts_shard_link_workspace_bytes(np_, owned_cap))
-        if self._ws is None or self._ws.numel() < nbytes:
-            self._ws = None
-            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", self.device))
+            owned_cap = owned_capacity(n_matches, self.slots, self.world)
+        self._workspace(L.check(self.lib.ts_shard_link_workspace_bytes(np_, owned_cap)))
         gathered = self._gather_stream(n_matches) if gather else None
         with torch.cuda.device(self.device):
             for g in self.played:
@@ -259,6 +284,35 @@ class ShardedLadder(object):
                         v.ids[r], v.meta[r] = all_ids[r].data_ptr(), all_meta[r].data_ptr()
                 L.check(self.lib.ts_shard_link(self.rater._ctx, C.byref(v), n_matches, self.slots, self.n_players, mode,
                                                seq_base, C.c_void_p(self._ws.data_ptr()), self._ws.numel(), self._stream()))
+
+    def _workspace(self, nbytes):
+        if self._ws is None or self._ws.numel() < nbytes:
+            self._ws = None
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=torch.device("cuda", self.device))
+
+    def _link_exchange(self, n_matches, mode, seq_base):
+        """count | send | link: every rank reads its own slice, counts per block of 32 matches the
+        live slots of every owner's players, and -- once all counts are known everywhere -- stores
+        each (player, slot) pair at its stream-ordered place in the owner's memory; the owner sorts
+        what it received.  A barrier across the ranks at every '|'."""
+        in_cap = owned_capacity(self.cap, self.slots, self.world)
+        self._workspace(max(L.check(self.lib.ts_shard_link_workspace_bytes(0, min(in_cap, n_matches * self.slots))),
+                            L.check(self.lib.ts_shard_exchange_workspace_bytes(n_matches, self.world))))
+        ws, nws = C.c_void_p(self._ws.data_ptr()), self._ws.numel()
+        ctx = self.rater._ctx
+        with torch.cuda.device(self.device):
+            for g in self.played:
+                v = self.view(g)
+                L.check(self.lib.ts_shard_count(ctx, C.byref(v), n_matches, self.slots, self.n_players, mode, self._stream()))
+            self.barrier()
+            for g in self.played:
+                v = self.view(g)
+                L.check(self.lib.ts_shard_send(ctx, C.byref(v), n_matches, self.slots, self.n_players, mode, ws, nws, self._stream()))
+            self.barrier()
+            for g in self.played:
+                v = self.view(g)
+                L.check(self.lib.ts_shard_link(ctx, C.byref(v), n_matches, self.slots, self.n_players, mode, seq_base, ws, nws,
+                                               self._stream()))
 
     def _gather_stream(self, n_matches):
         """The id stream is the one thing every rank must see whole (it keeps the slots of its own

@@ -69,6 +69,8 @@ def parse():
     ap.add_argument("--sharded-players", type=int, default=10_000_000)
     ap.add_argument("--sharded-deadline", type=int, default=300)
     ap.add_argument("--emulate", type=int, default=0, help="with --sharded on one GPU: play this many ranks in one process")
+    ap.add_argument("--shard-exchange", type=int, default=1,
+                    help="sharded ladder links: 1 = pairs sent to their owners (ts_shard_count / ts_shard_send), 0 = every rank reads the whole stream")
     return ap.parse_args()
 
 
@@ -631,7 +633,7 @@ def sharded_block(a, rater, engine, dist, rank, world, dev, n, u, p, steps=5, wa
     rater._ws = rater._vt = None
     torch.cuda.empty_cache()
 
-    ladder = sharded.ShardedLadder(rater, u, n, p, 0 if emulate else rank, G, emulate=bool(emulate))
+    ladder = sharded.ShardedLadder(rater, u, n, p, 0 if emulate else rank, G, emulate=bool(emulate), exchange=bool(a.shard_exchange))
     prefix_diff = oracle_prefix_check(rater, engine, {"seed": seed, "slots": p, "p_draw": a.p_draw, "zipf": a.zipf},
                                       a.p_draw, u, "ladder", min(n_prefix, n), a.lanes, sharded_ladder=ladder)
     ladder.set_stream(ids_d, meta_d)
@@ -666,11 +668,15 @@ def sharded_block(a, rater, engine, dist, rank, world, dev, n, u, p, steps=5, wa
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_wall, ms_link, ms_rate, one_link, one_rate, unequal, maxdiff, prefix_diff = (float(x) for x in t.cpu())
+    ladder_exchange = ladder.exchange
     ladder.close()
     assert rater.error_count() == 0
     remote = (G - 1) / G
     rate_nv = remote * p * 32 * n / G                       # rows pushed to other GPUs, per GPU
-    link_nv = remote * (n * p * 4 + n * 4) + remote * (n * p * 4) / G      # id stream read from peers + succ stored to peers
+    if ladder_exchange:      # (player, slot) pairs and block counts stored to peers + succ stored to peers
+        link_nv = remote * (n * p * 8) / G + remote * (n / 32) * 2 * G + remote * (n * p * 8) / G
+    else:                    # id stream read from peers + succ stored to peers
+        link_nv = remote * (n * p * 4 + n * 4) + remote * (n * p * 8) / G
     out = {"workload": "%s synthetic %s matches over %s players, ONE ladder, table hash-sharded over %d GPUs%s" % (
                _si(n), "3v3" if p == 6 else "5v5", _si(u), G, " (all ranks played by one GPU)" if emulate else ""),
            "n_gpus": G, "scaling": "strong", "ms_per_step": ms_wall, "link_ms": ms_link, "rate_ms": ms_rate,
@@ -683,8 +689,12 @@ def sharded_block(a, rater, engine, dist, rank, world, dev, n, u, p, steps=5, wa
            "nvlink": {"rate_bytes_per_gpu": rate_nv, "rate_gbs_per_gpu": rate_nv / (ms_rate * 1e-3) / 1e9,
                       "link_bytes_per_gpu": link_nv, "link_gbs_per_gpu": link_nv / (ms_link * 1e-3) / 1e9,
                       "peak_gbs_per_direction": 770.0,
-                      "note": "rows pushed to other GPUs (32 B each); id stream read from peers + succ stored to peers; "
+                      "note": "rows pushed to other GPUs (32 B each); links: " +
+                              ("(player, slot) pairs and per-block counts stored to the owners, succ messages stored to the raters; "
+                               if ladder_exchange else "id stream read from peers + succ messages stored to peers; ") +
                               "770 GB/s = measured peer copy per direction (B200_PROFILING.md)"},
+           "link_path": "exchange (every rank reads its own slice and sends each pair to its owner)" if ladder_exchange
+                        else "every rank reads the whole id stream",
            "bit_equal_to_one_gpu": unequal == 0.0, "max_abs_diff_vs_one_gpu": maxdiff,
            "check_max_abs_diff": prefix_diff,
            "check": "first %d matches through the sharded path vs the sequential __float128 oracle; full ladder "

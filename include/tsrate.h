@@ -289,6 +289,13 @@ typedef struct ts_shard_view {
     uint32_t *ring_tail[TS_SHARD_MAX];       /* [48], own rank only: places reserved, blocks done, consumed   */
     int64_t ring_cap;                        /* per sender: about (n_matches * slots + n_players) / G^2 + skew */
     int64_t ring_epoch;                      /* 1..255, the same on all ranks: +1 for every ts_shard_reset, 1 again after 255 */
+    /* link exchange (ts_shard_count / ts_shard_send); all NULL / 0: ts_shard_link reads the whole stream itself */
+    uint16_t *link_counts[TS_SHARD_MAX];     /* [G senders][G owners][link_blocks_cap]: owned live slots per block of 32 matches */
+    uint32_t *in_keys[TS_SHARD_MAX];         /* [in_cap] local index of the owned player of every pair sent to rank g, stream order */
+    uint32_t *in_vals[TS_SHARD_MAX];         /* [in_cap] its slot index m * slots + s in the window                              */
+    uint32_t *in_count[TS_SHARD_MAX];        /* [1] pairs rank g received (own rank only)                                        */
+    int64_t in_cap;                          /* pairs a rank can receive: about n_matches * slots / G, with room for skew        */
+    int64_t link_blocks_cap;                 /* a multiple of 8, >= ceil(ceil(n_matches / 32) / G)                               */
 } ts_shard_view;
 /* ts_shard_status bits */
 #define TS_SHARD_STALLED 1    /* a match's rows never arrived (watchdog): tables unusable      */
@@ -308,6 +315,22 @@ int ts_shard_free(void *ptr);
 int ts_shard_reset(ts_ctx *ctx, const ts_shard_view *view, int64_t n_players, void *stream);
 int ts_shard_link(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
                   int8_t mode, int64_t seq_base, void *workspace, int64_t workspace_bytes, void *stream);
+/* Link exchange: the same links with every rank reading only its OWN slice of the stream (link
+ * work per rank ~ 1/G of the window instead of all of it).  ts_shard_count counts, per block of 32
+ * matches of the own slice and per owner, the live slots of that owner's players and copies the
+ * counts to every rank's link_counts; after a barrier ts_shard_send scans the counts of all ranks in
+ * stream order and stores every (local player index, slot index) pair at its stream-ordered place
+ * in its owner's in_keys / in_vals (consecutive pairs of a block to consecutive addresses); after
+ * another barrier ts_shard_link, finding in_keys set in the view, sorts those pairs instead of
+ * reading the stream (pass n_slot_entries = 0 to ts_shard_link_workspace_bytes then).  Call order:
+ *   ts_shard_count | ts_shard_send | ts_shard_link | ts_shard_rate |
+ * TS_SHARD_OVERFLOW: a rank was sent more than in_cap pairs.  Results are identical to the
+ * links ts_shard_link makes on its own. */
+int64_t ts_shard_exchange_workspace_bytes(int64_t n_matches, int32_t n_shards);
+int ts_shard_count(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
+                   int8_t mode, void *stream);
+int ts_shard_send(ts_ctx *ctx, const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players,
+                  int8_t mode, void *workspace, int64_t workspace_bytes, void *stream);
 /* outputs: indexed by the LOCAL match index of this rank.  emulate_all = 1: this one
  * launch plays every rank of the view on one GPU (all pointers local; testing and
  * single-GPU runs of the sharded code path); outputs are then indexed by the window's

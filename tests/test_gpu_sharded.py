@@ -26,11 +26,14 @@ def _single(engine, r, ids, meta, full, u, outputs=None):
     return single.reshape(u, 2), pred
 
 
-@pytest.mark.parametrize("world,direct", [(1, "1"), (2, "1"), (2, "0"), (4, "0"), (8, "1"), (8, "0")])
+@pytest.mark.parametrize("world,direct,exchange", [(1, "1", True), (2, "1", True), (2, "0", False), (4, "0", True), (4, "1", False),
+                                                   (8, "1", False), (8, "0", True), (16, "0", True)])
 @pytest.mark.parametrize("slots,zipf,p_draw", CASES)
-def test_emulated_ranks_equal_single_gpu_and_oracle(c_oracle, monkeypatch, world, direct, slots, zipf, p_draw):
+def test_emulated_ranks_equal_single_gpu_and_oracle(c_oracle, monkeypatch, world, direct, exchange, slots, zipf, p_draw):
     """direct = "1": rows stored straight into the receiver's mailbox; "0": as messages through the
-    rings and the receiver's router blocks (what larger ladders on more GPUs use)."""
+    rings and the receiver's router blocks (what larger ladders on more GPUs use).
+    exchange: the links' (player, slot) pairs are sent to the owners by the ranks that hold the
+    matches (ts_shard_count / ts_shard_send); False: every rank reads the whole stream."""
     from analyzer_b200 import engine, sharded
     monkeypatch.setenv("TSRATE_SHARD_DIRECT", direct)
     co = c_oracle
@@ -42,7 +45,7 @@ def test_emulated_ranks_equal_single_gpu_and_oracle(c_oracle, monkeypatch, world
     full = engine.gen_table(seed, 0, u, dev).reshape(u, 2)
     outs1 = r.alloc_outputs(n, slots)
     want, pred = _single(engine, r, ids, meta, full, u, outs1)
-    ladder = sharded.ShardedLadder(r, u, n, slots, 0, world, emulate=True)
+    ladder = sharded.ShardedLadder(r, u, n, slots, 0, world, emulate=True, exchange=exchange)
     ladder.set_stream(ids, meta)
     ladder.set_table(full)
     outs = r.alloc_outputs(n, slots)
@@ -160,23 +163,24 @@ def _worker(rank, world, port, results):
         ids, meta = engine.gen_matches(gen, 0, n, dev)
         full = engine.gen_table(seed, 0, u, dev).reshape(u, 2)
         want, _ = _single(engine, r, ids, meta, full, u)
-        ladder = sharded.ShardedLadder(r, u, n, slots, rank, world)
-        ladder.set_stream(ids, meta)
-        for direct in ("1", "0"):           # rows straight into the peer's mailbox / as ring messages
-            os.environ["TSRATE_SHARD_DIRECT"] = direct
-            ladder.set_table(full)
-            ladder.run(n, mode=1)
-            errs = r.error_count()
-            mine = ladder.table[rank]
-            same = torch.equal(mine, want[rank::world]) and errs == 0        # bit for bit
-            if not same:
-                diff = (mine - want[rank::world]).abs()
-                print("sharded mismatch: rank", rank, "slots", slots, "direct", direct, "errs", errs, "rows differing",
-                      int((diff > 0).any(dim=1).sum()), "max", float(diff.max()), flush=True)
-            ok = ok and same
-            dist.barrier()
-        os.environ.pop("TSRATE_SHARD_DIRECT", None)
-        ladder.close()
+        for exchange in (True, False):      # links by pairs sent to the owners / by every rank reading the whole stream
+            ladder = sharded.ShardedLadder(r, u, n, slots, rank, world, exchange=exchange)
+            ladder.set_stream(ids, meta)
+            for direct in ("1", "0"):       # rows straight into the peer's mailbox / as ring messages
+                os.environ["TSRATE_SHARD_DIRECT"] = direct
+                ladder.set_table(full)
+                ladder.run(n, mode=1)
+                errs = r.error_count()
+                mine = ladder.table[rank]
+                same = torch.equal(mine, want[rank::world]) and errs == 0        # bit for bit
+                if not same:
+                    diff = (mine - want[rank::world]).abs()
+                    print("sharded mismatch: rank", rank, "slots", slots, "direct", direct, "exchange", exchange, "errs", errs,
+                          "rows differing", int((diff > 0).any(dim=1).sum()), "max", float(diff.max()), flush=True)
+                ok = ok and same
+                dist.barrier()
+            os.environ.pop("TSRATE_SHARD_DIRECT", None)
+            ladder.close()
         r.close()
     results[rank] = ok
     dist.destroy_process_group()
