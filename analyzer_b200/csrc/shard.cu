@@ -57,6 +57,7 @@ struct PushArgs {
     uint32_t epoch;               // 1..255: the marker byte of this run's messages
     uint32_t direct;              // 1: rows go straight into the receiver's mailbox (no rings, no routers)
     uint32_t ring_cap;            // messages one sender may leave in one receiver's ring
+    uint32_t stage_msgs;          // 1: a pass's messages are grouped by receiver in shared memory first (MsgStage)
     ts_outputs out;
     unsigned long long *ctrl;
 };
@@ -76,18 +77,41 @@ __device__ __forceinline__ void st_pair_sys(double *p, double mu, double sigma)
 // is never taken for this window's.
 constexpr int kTailDone = TS_SHARD_MAX, kTailConsumed = 2 * TS_SHARD_MAX;
 
-__device__ __forceinline__ void st_message(unsigned long long *slot, uint32_t pid, uint32_t tag, double mu, double sigma,
-                                           unsigned long long kMsgMarker)
+__device__ __forceinline__ void pack_message(uint32_t pid, uint32_t tag, double mu, double sigma, unsigned long long kMsgMarker,
+                                             unsigned long long w[4])
 {
     const unsigned long long m = (unsigned long long)__double_as_longlong(mu);
     const unsigned long long s = (unsigned long long)__double_as_longlong(sigma);
     const unsigned long long x0 = pid & 0xFFFFFFu, x1 = (pid >> 24) | ((tag & 0xFFFFu) << 8), x2 = tag >> 16;
-    const unsigned long long w0 = (kMsgMarker << 56) | (x0 << 32) | (m & 0xFFFFFFFFull);
-    const unsigned long long w1 = (kMsgMarker << 56) | (x1 << 32) | (m >> 32);
-    const unsigned long long w2 = (kMsgMarker << 56) | (x2 << 32) | (s & 0xFFFFFFFFull);
-    const unsigned long long w3 = (kMsgMarker << 56) | (s >> 32);
-    asm volatile("st.relaxed.sys.global.v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(slot), "l"(w0), "l"(w1), "l"(w2), "l"(w3) : "memory");
+    w[0] = (kMsgMarker << 56) | (x0 << 32) | (m & 0xFFFFFFFFull);
+    w[1] = (kMsgMarker << 56) | (x1 << 32) | (m >> 32);
+    w[2] = (kMsgMarker << 56) | (x2 << 32) | (s & 0xFFFFFFFFull);
+    w[3] = (kMsgMarker << 56) | (s >> 32);
 }
+
+__device__ __forceinline__ void st_words_sys(unsigned long long *slot, const unsigned long long w[4])
+{
+    asm volatile("st.relaxed.sys.global.v4.u64 [%0], {%1, %2, %3, %4};" ::"l"(slot), "l"(w[0]), "l"(w[1]), "l"(w[2]), "l"(w[3]) : "memory");
+}
+
+__device__ __forceinline__ void st_message(unsigned long long *slot, uint32_t pid, uint32_t tag, double mu, double sigma,
+                                           unsigned long long kMsgMarker)
+{
+    unsigned long long w[4];
+    pack_message(pid, tag, mu, sigma, kMsgMarker, w);
+    st_words_sys(slot, w);
+}
+
+// The messages of one pass of a warp, grouped by receiver before they leave: a warp's pass makes
+// 32 * SPL rows for up to G receivers, and a run of messages for one receiver stored by
+// neighbouring lanes crosses NVLink in fewer, larger packets than the same messages stored
+// four at a time (the lanes of one store instruction that happen to share a receiver).
+template <int N>
+struct alignas(16) MsgStage {
+    unsigned long long w[N][4];
+    uint32_t at[N];
+    uint8_t to[N];
+};
 
 // Router warp: drains one sender's ring in this rank's memory.  The warps that share a ring take its
 // chunks of 32 * kRouteUnroll messages round-robin; a lane delivers each of its messages as soon as
@@ -173,6 +197,9 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
     constexpr int SPL = (P + L - 1) / L;
     constexpr int kWarps = kBlock / 32;
     __shared__ __align__(16) WarpStage<P, W> stage_all[kWarps];
+    // grouping of the outgoing messages where it fits beside the record staging (static shared memory, 48 KB)
+    constexpr bool kCanStage = (sizeof(WarpStage<P, W>) + sizeof(MsgStage<32 * SPL>)) * kWarps <= 48 * 1024 - 64;
+    __shared__ __align__(16) MsgStage<kCanStage ? 32 * SPL : 1> msgs_all[kCanStage ? kWarps : 1];
 
     const int wl = threadIdx.x & 31;
     const int lane = wl % L;
@@ -297,23 +324,70 @@ __global__ void __launch_bounds__(kBlock, 2) k_rate_push(const PushArgs a)
                     else st_pair_sys(a.view.table[to[k]] + (size_t)(pid[k] >> a.g_shift) * 2, mu2[k], sg2[k]);
                     to[k] = 0xFFu;
                 }
-                grp_mask[k] = __match_any_sync(0xFFFFFFFFu, to[k]);
-                place[k] = 0;
-                if (to[k] != 0xFFu && wl == __ffs(grp_mask[k]) - 1)
-                    place[k] = atomicAdd(a.view.ring_tail[me] + to[k], (uint32_t)__popc(grp_mask[k]));
             }
+            if (kCanStage && a.stage_msgs) {
+                if (!a.direct && a.g_mask != 0u) {
+                    // lane d counts receiver d's messages of this pass and reserves their places with one atomic
+                    auto &msgs = msgs_all[kCanStage ? (threadIdx.x >> 5) : 0];
+                    const uint32_t lt = (1u << wl) - 1u;
+                    uint32_t idx[SPL], my_cnt = 0, my_seg = 0, total = 0;
+                    for (uint32_t d = 0; d <= a.g_mask; ++d) {
+                        uint32_t c = 0;
 #pragma unroll
-            for (int k = 0; k < SPL; ++k) {
-                const int s = lane + k * L;
-                const uint32_t at = __shfl_sync(0xFFFFFFFFu, place[k], __ffs(grp_mask[k]) - 1) +
-                                    __popc(grp_mask[k] & ((1u << wl) - 1u));
-                if (to[k] != 0xFFu) {
-                    if (at < a.ring_cap)
-                        st_message(a.view.ring[to[k]] + ((size_t)me * a.ring_cap + at) * 4, pid[k], next[k], mu2[k], sg2[k], a.epoch);
-                    else atomicOr(&a.ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
+                        for (int k = 0; k < SPL; ++k) {
+                            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, to[k] == d);
+                            if (to[k] == d) idx[k] = c + __popc(bal & lt);
+                            c += __popc(bal);
+                        }
+                        if ((uint32_t)wl == d) { my_cnt = c; my_seg = total; }
+                        total += c;
+                    }
+                    uint32_t my_base = 0;
+                    if (my_cnt) my_base = atomicAdd(a.view.ring_tail[me] + wl, my_cnt);
+#pragma unroll
+                    for (int k = 0; k < SPL; ++k) {
+                        const uint32_t base = __shfl_sync(0xFFFFFFFFu, my_base, to[k] & 31u);
+                        const uint32_t seg = __shfl_sync(0xFFFFFFFFu, my_seg, to[k] & 31u);
+                        if (to[k] != 0xFFu) {
+                            const uint32_t sp = seg + idx[k];
+                            pack_message(pid[k], next[k], mu2[k], sg2[k], a.epoch, msgs.w[sp]);
+                            msgs.at[sp] = base + idx[k];
+                            msgs.to[sp] = (uint8_t)to[k];
+                        }
+                    }
+                    __syncwarp();
+                    for (uint32_t j = wl; j < total; j += 32u) {
+                        const uint32_t at = msgs.at[j], r = msgs.to[j];
+                        if (at < a.ring_cap) st_words_sys(a.view.ring[r] + ((size_t)me * a.ring_cap + at) * 4, msgs.w[j]);
+                        else atomicOr(&a.ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
+                    }
+                    __syncwarp();
                 }
-                if (go && used[k] && ok && a.out.out_queue)
-                    st_pair_stream(a.out.out_queue + ((size_t)om * P + s) * 2, mu2[k], sg2[k], pol);
+#pragma unroll
+                for (int k = 0; k < SPL; ++k)
+                    if (go && used[k] && ok && a.out.out_queue)
+                        st_pair_stream(a.out.out_queue + ((size_t)om * P + lane + k * L) * 2, mu2[k], sg2[k], pol);
+            } else {
+#pragma unroll
+                for (int k = 0; k < SPL; ++k) {
+                    grp_mask[k] = __match_any_sync(0xFFFFFFFFu, to[k]);
+                    place[k] = 0;
+                    if (to[k] != 0xFFu && wl == __ffs(grp_mask[k]) - 1)
+                        place[k] = atomicAdd(a.view.ring_tail[me] + to[k], (uint32_t)__popc(grp_mask[k]));
+                }
+#pragma unroll
+                for (int k = 0; k < SPL; ++k) {
+                    const int s = lane + k * L;
+                    const uint32_t at = __shfl_sync(0xFFFFFFFFu, place[k], __ffs(grp_mask[k]) - 1) +
+                                        __popc(grp_mask[k] & ((1u << wl) - 1u));
+                    if (to[k] != 0xFFu) {
+                        if (at < a.ring_cap)
+                            st_message(a.view.ring[to[k]] + ((size_t)me * a.ring_cap + at) * 4, pid[k], next[k], mu2[k], sg2[k], a.epoch);
+                        else atomicOr(&a.ctrl[CTRL_SHARD], (unsigned long long)TS_SHARD_OVERFLOW);
+                    }
+                    if (go && used[k] && ok && a.out.out_queue)
+                        st_pair_stream(a.out.out_queue + ((size_t)om * P + s) * 2, mu2[k], sg2[k], pol);
+                }
             }
             if (go) {
                 if (lane == 0) {
@@ -518,6 +592,9 @@ extern "C" int ts_shard_rate(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     // 0.14 G/s into 2.2 GB of seven); beyond that, messages in rings.  TSRATE_SHARD_DIRECT=0/1 overrides.
     const char *ed = getenv("TSRATE_SHARD_DIRECT");
     a.direct = ed ? (atoi(ed) != 0) : ((int64_t)(G - 1) * n_players * 32 <= (512ll << 20));
+    // ring messages grouped by receiver in shared memory before they leave (TSRATE_SHARD_STAGE=0: as they come)
+    const char *es = getenv("TSRATE_SHARD_STAGE");
+    a.stage_msgs = es ? (atoi(es) != 0) : 1u;
     if (G > 1 && !a.direct && (a.epoch < 1u || a.epoch > 255u)) {
         ts_set_error("ts_shard_rate: ring_epoch must be 1..255 (ts_shard_reset hands it out)");
         return TS_E_ARG;
