@@ -1631,6 +1631,7 @@ struct ExchSrc {
     uint32_t n_local;               // matches in it
     uint32_t g_mask, g_shift, me;
     uint32_t slots, rated_mask, n_players;
+    unsigned long long slots_magic; // floor(2^64 / slots) + 1
     uint32_t nb_cap;                // blocks per rank the count / offset arrays are laid out for
 };
 struct ExchDst {
@@ -1641,67 +1642,79 @@ struct ExchPeers {
     uint4 *counts[TS_SHARD_MAX];    // every rank's link_counts at sender = me
 };
 
-// one CUDA block = one block of 32 matches of the own slice, one thread per slot (32 * slots threads).
-// SEND: the block's pairs are first grouped by owner in shared memory, so that the pairs for one
-// owner leave as one run of consecutive 4-byte stores (about 32 * slots / G of them).
-template <bool SEND>
-__global__ void k_block_owned(ExchSrc src, uint16_t *cnt_local, const uint32_t *off_mine, ExchDst dst, unsigned long long *ctrl)
+// owner (and local index) of the player in entry e = match * slots + slot of block lb of the own slice; 0xFF: takes no part
+__device__ __forceinline__ uint32_t exch_owner(const ExchSrc &src, uint32_t lb, uint32_t e, uint32_t &key, uint32_t &val)
 {
-    __shared__ uint16_t wcnt[TS_MAX_SLOTS][TS_SHARD_MAX];    // per warp, per owner
-    __shared__ uint32_t seg[TS_SHARD_MAX + 1];               // start of every owner's run inside the block
-    __shared__ uint32_t skey[32 * TS_MAX_SLOTS], sval[32 * TS_MAX_SLOTS];
-    const uint32_t lb = blockIdx.x, t = threadIdx.x, warp = t >> 5, lane = t & 31, n_warps = blockDim.x >> 5;
+    const uint32_t mi = (uint32_t)__umul64hi((unsigned long long)e, src.slots_magic), sl = e - mi * src.slots;
+    const uint32_t lm = lb * 32u + mi;
+    if (lm >= src.n_local) return 0xFFu;
+    const uint32_t k = __ldg(src.ids + (size_t)lm * src.slots + sl);
+    if (k == TS_EMPTY_SLOT || k >= src.n_players) return 0xFFu;
+    const uint32_t mt = __ldg(src.meta + lm);
+    const bool gated = ((src.rated_mask >> ((mt >> TS_META_MODE_SHIFT) & 15u)) & 1u) == 0u ||
+                       (mt & (TS_META_AFK | TS_META_INVALID)) != 0u;
+    if (gated) return 0xFFu;
+    key = k >> src.g_shift;
+    // slot index of the window: the stream-wide number of local match lm of this rank
+    val = (((((lm >> 5) << src.g_shift) | src.me) << 5) | (lm & 31u)) * src.slots + sl;
+    return k & src.g_mask;
+}
+
+// One WARP = one block of 32 matches of the own slice (32 * slots entries, 32 at a time); lane o keeps
+// owner o's count.  No block-wide step.  SEND: a second sweep puts the block's pairs, grouped by owner,
+// into the warp's piece of shared memory, so that the pairs for one owner leave as one run of
+// consecutive 4-byte stores (about 32 * slots / G of them) to that owner's memory.
+constexpr int kExchWarps = 4;
+template <bool SEND>
+__global__ void __launch_bounds__(kExchWarps * 32)
+k_block_owned(ExchSrc src, uint32_t nb_local, uint16_t *cnt_local, const uint32_t *off_mine, ExchDst dst)
+{
+    extern __shared__ uint4 exch_smem[];                    // SEND: [kExchWarps][32 * slots] of (key, val, place, owner)
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31, lt = (1u << lane) - 1u;
+    const uint32_t lb = blockIdx.x * kExchWarps + warp;
+    if (lb >= nb_local) return;
     const uint32_t G = src.g_mask + 1u;
-    const uint32_t lm = lb * 32u + t / src.slots, sl = t % src.slots;
-    uint32_t owner = 0xFFu, key = 0;
-    if (lm < src.n_local) {
-        const uint32_t k = src.ids[(size_t)lm * src.slots + sl];
-        if (k != TS_EMPTY_SLOT && k < src.n_players) {
-            const uint32_t mt = src.meta[lm];
-            const bool gated = ((src.rated_mask >> ((mt >> TS_META_MODE_SHIFT) & 15u)) & 1u) == 0u ||
-                               (mt & (TS_META_AFK | TS_META_INVALID)) != 0u;
-            if (!gated) { owner = k & src.g_mask; key = k >> src.g_shift; }
+    // (loading all 32 * slots entries before the counting, unrolled over TS_MAX_SLOTS, measured slower:
+    // 80 registers, send 0.21 -> 0.28 ms for 2.5M matches)
+    uint32_t tot = 0;                                       // lane o: pairs of this block for owner o
+    for (uint32_t c = 0; c < src.slots; ++c) {
+        uint32_t key, val;
+        const uint32_t owner = exch_owner(src, lb, c * 32u + lane, key, val);
+        for (uint32_t o = 0; o < G; ++o) {
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, owner == o);
+            if (lane == o) tot += __popc(bal);
         }
     }
-    // place among the slots of the same owner inside this warp, in slot order
-    uint32_t before_in_warp = 0;
-    for (uint32_t o = 0; o < G; ++o) {
-        const uint32_t bal = __ballot_sync(0xFFFFFFFFu, owner == o);
-        if (owner == o) before_in_warp = __popc(bal & ((1u << lane) - 1u));
-        if (lane == 0) wcnt[warp][o] = (uint16_t)__popc(bal);
-    }
-    __syncthreads();
     if (!SEND) {
-        if (t < G) {
-            uint32_t c = 0;
-            for (uint32_t w = 0; w < n_warps; ++w) c += wcnt[w][t];
-            cnt_local[(size_t)t * src.nb_cap + lb] = (uint16_t)c;
-        }
+        if (lane < G) cnt_local[(size_t)lane * src.nb_cap + lb] = (uint16_t)tot;
         return;
     }
-    if (t == 0) {
-        uint32_t run = 0;
+    uint32_t incl = tot;                                    // start of every owner's run in the warp's piece
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+        if (lane >= (uint32_t)o) incl += y;
+    }
+    const uint32_t seg = incl - tot, total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    const uint32_t my_off = lane < G ? __ldg(off_mine + (size_t)lane * src.nb_cap + lb) : 0u;
+    uint4 *piece = exch_smem + (size_t)warp * 32u * src.slots;
+    uint32_t run = 0;                                       // lane o: owner o's pairs in the entries before
+    for (uint32_t c = 0; c < src.slots; ++c) {
+        uint32_t key = 0, val = 0, idx = 0;
+        const uint32_t owner = exch_owner(src, lb, c * 32u + lane, key, val);
         for (uint32_t o = 0; o < G; ++o) {
-            seg[o] = run;
-            for (uint32_t w = 0; w < n_warps; ++w) run += wcnt[w][o];
+            const uint32_t bal = __ballot_sync(0xFFFFFFFFu, owner == o);
+            const uint32_t before = __shfl_sync(0xFFFFFFFFu, run, o);
+            if (owner == o) idx = before + __popc(bal & lt);
+            if (lane == o) run += __popc(bal);
         }
-        seg[G] = run;
+        const uint32_t sg = __shfl_sync(0xFFFFFFFFu, seg, owner & 31u), off = __shfl_sync(0xFFFFFFFFu, my_off, owner & 31u);
+        if (owner != 0xFFu) piece[sg + idx] = make_uint4(key, val, off + idx, owner);
     }
-    __syncthreads();
-    if (owner != 0xFFu) {
-        uint32_t lp = seg[owner] + before_in_warp;
-        for (uint32_t w = 0; w < warp; ++w) lp += wcnt[w][owner];
-        // slot index of the window: the stream-wide number of local match lm of this rank
-        const uint32_t m = ((((lm >> 5) << src.g_shift) | src.me) << 5) | (lm & 31u);
-        skey[lp] = key;
-        sval[lp] = m * src.slots + sl;
-    }
-    __syncthreads();
-    if (t < seg[G]) {
-        uint32_t o = 0;
-        while (t >= seg[o + 1]) ++o;
-        const uint32_t pos = __ldg(off_mine + (size_t)o * src.nb_cap + lb) + (t - seg[o]);
-        if (pos < dst.in_cap) { dst.in_keys[o][pos] = skey[t]; dst.in_vals[o][pos] = sval[t]; }
+    __syncwarp();
+    for (uint32_t j = lane; j < total; j += 32u) {
+        const uint4 e = piece[j];
+        if (e.z < dst.in_cap) { dst.in_keys[e.w][e.z] = e.x; dst.in_vals[e.w][e.z] = e.y; }
     }
 }
 
@@ -1892,6 +1905,30 @@ extern "C" int64_t ts_shard_link_workspace_bytes(int64_t n_slot_entries, int64_t
 
 namespace {
 
+// TSRATE_SHARD_TIMING=1: the time of one entry point's launches (synchronises; diagnosis only)
+struct StageTimer {
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    cudaStream_t s;
+    const char *what;
+    int rank, G;
+    StageTimer(const char *w, int r, int g, cudaStream_t st) : s(st), what(w), rank(r), G(g)
+    {
+        const char *e = getenv("TSRATE_SHARD_TIMING");
+        if (e && atoi(e)) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, s); }
+    }
+    ~StageTimer()
+    {
+        if (!e0) return;
+        cudaEventRecord(e1, s);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        fprintf(stderr, "%s rank %d/%d: %.3f ms\n", what, rank, G, ms);
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+    }
+};
+
 uint32_t exch_blocks(int64_t n_matches) { return (uint32_t)((n_matches + TS_SHARD_BLOCK - 1) / TS_SHARD_BLOCK); }
 
 int check_exchange(const ts_shard_view *view, int64_t n_matches, int32_t slots, int64_t n_players, int mode, const char *who)
@@ -1930,6 +1967,7 @@ ExchSrc exchange_src(const ts_shard_view *view, int64_t n_matches, int32_t slots
     src.g_shift = (uint32_t)shift;
     src.me = (uint32_t)rank;
     src.slots = (uint32_t)slots;
+    src.slots_magic = (~0ull / (unsigned long long)slots) + 1ull;
     src.rated_mask = 1u << mode;
     src.n_players = (uint32_t)n_players;
     src.nb_cap = (uint32_t)view->link_blocks_cap;
@@ -1956,10 +1994,11 @@ extern "C" int ts_shard_count(ts_ctx *ctx, const ts_shard_view *view, int64_t n_
     cudaStream_t s = (cudaStream_t)stream;
     const int G = view->n_shards, rank = view->rank;
     const ExchSrc src = exchange_src(view, n_matches, slots, n_players, mode);
+    StageTimer timer("ts_shard_count", rank, G, s);
     const size_t per_sender = (size_t)G * src.nb_cap;               // 16-bit counts of one sender
     uint16_t *own = view->link_counts[rank] + (size_t)rank * per_sender;
     const uint32_t nb_local = (src.n_local + 31u) / 32u;
-    if (nb_local) k_block_owned<false><<<nb_local, 32 * slots, 0, s>>>(src, own, nullptr, ExchDst(), ctx->d_ctrl);
+    if (nb_local) k_block_owned<false><<<(nb_local + kExchWarps - 1) / kExchWarps, kExchWarps * 32, 0, s>>>(src, nb_local, own, nullptr, ExchDst());
     if (G > 1) {
         ExchPeers peers;
         for (int g = 0; g < TS_SHARD_MAX; ++g)
@@ -1988,6 +2027,7 @@ extern "C" int ts_shard_send(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     }
     TS_CUDA(cudaSetDevice(ctx->device));
     cudaStream_t s = (cudaStream_t)stream;
+    StageTimer timer("ts_shard_send", rank, G, s);
     uint32_t *partial = (uint32_t *)workspace;
     uint32_t *totals = (uint32_t *)((char *)workspace + partial_bytes);
     uint32_t *off_mine = (uint32_t *)((char *)workspace + partial_bytes + 256);
@@ -2001,7 +2041,9 @@ extern "C" int ts_shard_send(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     for (int g = 0; g < TS_SHARD_MAX; ++g) { dst.in_keys[g] = g < G ? view->in_keys[g] : nullptr; dst.in_vals[g] = g < G ? view->in_vals[g] : nullptr; }
     dst.in_cap = (uint32_t)view->in_cap;
     const uint32_t nb_local = (src.n_local + 31u) / 32u;
-    if (nb_local) k_block_owned<true><<<nb_local, 32 * slots, 0, s>>>(src, nullptr, off_mine, dst, ctx->d_ctrl);
+    if (nb_local)
+        k_block_owned<true><<<(nb_local + kExchWarps - 1) / kExchWarps, kExchWarps * 32, (size_t)kExchWarps * 32 * slots * sizeof(uint4), s>>>(
+            src, nb_local, nullptr, off_mine, dst);
     TS_CUDA(cudaGetLastError());
     return 0;
 }
