@@ -215,6 +215,7 @@ class ShardedLadder(object):
             self.succ[g] = arena[offs[4]:offs[4] + nl * slots * 4].view(torch.int32).view(nl, slots)
         self._ws = None
         self._gbuf = None
+        self._flag = None
         self.epoch = 0
 
     def view(self, rank=None):
@@ -242,10 +243,21 @@ class ShardedLadder(object):
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
-    def barrier(self):
+    def barrier(self, host=True):
+        """All ranks' earlier work on their streams is done before any rank's later work starts.
+        host=False with an NCCL group: a one-word all-reduce queued on the stream -- the GPUs wait for
+        each other, the hosts do not (no synchronize, the next launches are queued behind it)."""
+        if self.emulate or self.world == 1:
+            if host:
+                torch.cuda.synchronize(self.device)
+            return
+        if not host and dist.get_backend(self.group) == "nccl":
+            if self._flag is None:
+                self._flag = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", self.device))
+            dist.all_reduce(self._flag, group=self.group)
+            return
         torch.cuda.synchronize(self.device)
-        if not self.emulate and self.world > 1:
-            dist.barrier(group=self.group)
+        dist.barrier(group=self.group)
 
     def set_stream(self, ids_full, meta_full):
         """Take this rank's blocks (all ranks' when emulating) out of a full stream on this GPU."""
@@ -304,11 +316,11 @@ class ShardedLadder(object):
             for g in self.played:
                 v = self.view(g)
                 L.check(self.lib.ts_shard_count(ctx, C.byref(v), n_matches, self.slots, self.n_players, mode, self._stream()))
-            self.barrier()
+            self.barrier(host=False)
             for g in self.played:
                 v = self.view(g)
                 L.check(self.lib.ts_shard_send(ctx, C.byref(v), n_matches, self.slots, self.n_players, mode, ws, nws, self._stream()))
-            self.barrier()
+            self.barrier(host=False)
             for g in self.played:
                 v = self.view(g)
                 L.check(self.lib.ts_shard_link(ctx, C.byref(v), n_matches, self.slots, self.n_players, mode, seq_base, ws, nws,

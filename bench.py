@@ -647,14 +647,14 @@ def sharded_block(a, rater, engine, dist, rank, world, dev, n, u, p, steps=5, wa
         e0, e1, e2, e3 = ev(), ev(), ev(), ev()
         e0.record()
         ladder.reset()
-        ladder.barrier()
+        ladder.barrier(host=False)     # the GPUs wait for each other on their streams; the host queues on
         ladder.link(n, 1)
         e1.record()
-        ladder.barrier()
+        ladder.barrier(host=False)
         e2.record()
         ladder.rate(n, 1, 0, None, a.lanes)
         e3.record()
-        ladder.barrier()
+        ladder.barrier()               # host: everything done on every rank
         dt = time.perf_counter() - t0
         ladder.check()
         if it >= warmup:
@@ -681,8 +681,9 @@ def sharded_block(a, rater, engine, dist, rank, world, dev, n, u, p, steps=5, wa
                _si(n), "3v3" if p == 6 else "5v5", _si(u), G, " (all ranks played by one GPU)" if emulate else ""),
            "n_gpus": G, "scaling": "strong", "ms_per_step": ms_wall, "link_ms": ms_link, "rate_ms": ms_rate,
            "matches_per_s": n / (ms_wall * 1e-3),
-           "timing": "ms_per_step = wall clock from before the mailbox reset to after the last barrier (host barriers "
-                     "included), max over ranks; link_ms / rate_ms = CUDA events around each rank's own launches, max over ranks",
+           "timing": "ms_per_step = wall clock from before the mailbox reset to after the last (host) barrier, the "
+                     "barriers between the phases included (one-word NCCL all-reduces on the streams), max over ranks; "
+                     "link_ms / rate_ms = CUDA events around each rank's own launches, max over ranks",
            "one_gpu": {"link_ms": one_link, "rate_ms": one_rate, "matches_per_s": n / ((one_link + one_rate) * 1e-3)},
            "speedup_vs_one_gpu": (one_link + one_rate) / ms_wall,
            "strong_scaling_efficiency": (one_link + one_rate) / ms_wall / G,
