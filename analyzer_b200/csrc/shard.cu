@@ -587,11 +587,13 @@ extern "C" int ts_shard_rate(ts_ctx *ctx, const ts_shard_view *view, int64_t n_m
     a.ring_cap = (uint32_t)(G > 1 ? view->ring_cap : 0);
     a.window_gen = (uint32_t)(seq_base / TS_SHARD_BLOCK) + 1u;
     a.epoch = (uint32_t)view->ring_epoch;
-    // Rows straight into the receivers' mailboxes while the peers' mailboxes together stay small enough
-    // for scattered stores (measured: 8.4 G stores/s into 320 MB of one peer, 5.7 G/s into 960 MB of three,
-    // 0.14 G/s into 2.2 GB of seven); beyond that, messages in rings.  TSRATE_SHARD_DIRECT=0/1 overrides.
+    // Rows straight into the receivers' mailboxes while the peers' mailboxes together are small (scattered
+    // stores over NVLink: 8.4 G stores/s into 320 MB of one peer, 5.7 G/s into 960 MB of three, 0.14 G/s into
+    // 2.2 GB of seven); beyond 256 MB, messages in rings -- with the messages of a pass grouped by receiver
+    // the rings are also the faster way into ONE peer's 320 MB (2 GPUs, 100M matches over 10M players: rating
+    // 19.8 ms against 22.5 direct).  TSRATE_SHARD_DIRECT=0/1 overrides.
     const char *ed = getenv("TSRATE_SHARD_DIRECT");
-    a.direct = ed ? (atoi(ed) != 0) : ((int64_t)(G - 1) * n_players * 32 <= (512ll << 20));
+    a.direct = ed ? (atoi(ed) != 0) : ((int64_t)(G - 1) * n_players * 32 <= (256ll << 20));
     // ring messages grouped by receiver in shared memory before they leave (TSRATE_SHARD_STAGE=0: as they come)
     const char *es = getenv("TSRATE_SHARD_STAGE");
     a.stage_msgs = es ? (atoi(es) != 0) : 1u;
