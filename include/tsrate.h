@@ -257,8 +257,10 @@ int ts_rate_slots(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const
  * owner's table shard the same way.  No inter-GPU barrier and no collective while
  * rating.  ts_shard_reset clears mailbox, rings and counts before a ladder's first window;
  * every window's messages are appended behind the earlier ones (size ring_cap for the run).
- * Links: ts_shard_link reads the whole id stream once (its peers' slices over NVLink),
- * keeps the slots of the players it owns, sorts them, and sends succ[m][s] (the
+ * Links: ts_shard_link takes the slots of the players it owns -- sent to it by the ranks that
+ * hold the matches (ts_shard_count / ts_shard_send below: every rank reads its own slice only),
+ * or, without those two calls, by reading the whole id stream once itself (its peers' slices
+ * over NVLink) -- sorts them, and sends succ[m][s] (the
  * stream-wide number of that player's next rated match, TS_NONE if none) to the rank
  * that rates m -- as messages appended to that rank's inbox in large coalesced pieces,
  * which ts_shard_rate scatters into the succ slice locally before it rates (scattered
@@ -269,7 +271,7 @@ int ts_rate_slots(ts_ctx *ctx, const ts_table *table, const uint32_t *ids, const
  * All arrays of a ts_shard_view are device pointers valid on THIS GPU: index rank =
  * own allocations, the others peer mappings (ts_shard_alloc / ts_shard_open).
  * Call order per window, with a barrier across the ranks at every "|":
- *   slices and table shards in place, ts_shard_reset | ts_shard_link | ts_shard_rate |
+ *   slices and table shards in place, ts_shard_reset | [ts_shard_count | ts_shard_send |] ts_shard_link | ts_shard_rate |
  * Windows (seq_base > 0) continue a ladder: seq_base must be a multiple of 32 * G and
  * stream-wide match numbers stay below 2^32 - 1; ts_shard_reset is for the first only. */
 #define TS_SHARD_BLOCK 32
