@@ -95,3 +95,42 @@ def test_shard_entry_points_refuse_bad_views():
     assert lib.ts_shard_rate(None, C.byref(v), 10, 6, 10, 1, 0, None, 0, 0, None) == -1
     assert lib.ts_shard_local_matches(-1, 0, 2) < 0
     assert lib.ts_shard_link_workspace_bytes(1 << 22, 1 << 20) > (1 << 20) * 16 + (1 << 22) * 8
+
+
+def test_link_exchange_sizes_and_argument_checks():
+    """The link exchange's host-side sizes agree between Python and the C ABI, and its entry points
+    refuse views that do not fit the window before they touch a GPU."""
+    from analyzer_b200 import _lib, sharded
+    lib = _lib.lib()
+    for n, world in ((1, 1), (31, 2), (32 * 8 + 1, 8), (100_000_000, 8), (500_000_000, 16)):
+        nb = sharded.link_blocks_capacity(n, world)
+        blocks = (n + 31) // 32
+        assert nb % 8 == 0 and nb * world >= blocks
+        # scratch of ts_shard_send: chunk sums per owner, totals, offsets of the own blocks
+        need = lib.ts_shard_exchange_workspace_bytes(n, world)
+        assert need >= world * nb * 4 and need < world * nb * 4 + world * (blocks // 4096 + 2) * 4 + 4096
+        # the staging-free link workspace only holds the sort's buffers
+        cap = sharded.owned_capacity(n, 6, world)
+        assert cap <= max(1, n * 6) and (world > 1 or cap == n * 6)
+        assert lib.ts_shard_link_workspace_bytes(0, min(cap, n * 6)) < lib.ts_shard_link_workspace_bytes(n * 6, min(cap, n * 6)) \
+            or n * 6 < 4096
+    assert lib.ts_shard_exchange_workspace_bytes(-1, 2) < 0 and lib.ts_shard_exchange_workspace_bytes(10, 17) < 0
+    # arenas: the exchange adds its four pieces at the end; without it they shrink to place holders
+    with_x, size_x = sharded.arena_layout(1000, 5000, 6, 1, 4)
+    without, size_0 = sharded.arena_layout(1000, 5000, 6, 1, 4, exchange=False)
+    assert with_x[:10] == without[:10] and len(with_x) == 14 and size_x > size_0
+    v = _lib.TsShardView()
+    v.rank, v.n_shards = 0, 2
+    assert lib.ts_shard_count(None, C.byref(v), 100, 6, 10, 1, None) == -1            # no context
+    ctx_stub = C.c_void_p(1)              # never dereferenced: the view is checked first
+    v.link_blocks_cap, v.in_cap = 8, 600
+    assert lib.ts_shard_count(ctx_stub, C.byref(v), 32 * 2 * 8 + 1, 6, 10, 1, None) == -1   # 9 blocks per rank > 8
+    assert b"link_blocks_cap" in lib.ts_last_error()
+    v.link_blocks_cap = 12                # not a multiple of 8
+    assert lib.ts_shard_send(ctx_stub, C.byref(v), 100, 6, 10, 1, None, 0, None) == -1
+    v.link_blocks_cap = 16
+    assert lib.ts_shard_send(ctx_stub, C.byref(v), 100, 6, 10, 1, None, 0, None) == -1      # arrays not mapped
+    assert b"not mapped" in lib.ts_last_error()
+    v.n_shards = 3
+    assert lib.ts_shard_count(ctx_stub, C.byref(v), 100, 6, 10, 1, None) == -1
+    assert b"power of two" in lib.ts_last_error()
