@@ -148,6 +148,45 @@ def test_duplicate_player_and_bad_id_are_reported():
     ladder.close()
 
 
+@pytest.mark.parametrize("exchange", [True, False])
+def test_skewed_ownership_overflows_loudly_and_fits_with_more_room(exchange):
+    """Every player owned by rank 0 (all ids even, 2 ranks): rank 0 is sent twice its share of the slots.
+    The default capacity (1.25 shares) must report TS_SHARD_OVERFLOW, not rate with missing links; a
+    ladder laid out for a window twice as large has the room and equals one GPU bit for bit."""
+    from analyzer_b200 import _lib, engine, sharded
+    dev = torch.device("cuda", 0)
+    world, slots, n, u = 2, 6, 40_000, 3_000
+    r = engine.Rater(engine.Env(), 0)
+    ids, meta = engine.gen_matches(engine.make_gen(11, u // 2, slots=slots, mode=1), 0, n, dev)
+    ids = ids * 2
+    full = engine.gen_table(11, 0, u, dev).reshape(u, 2)
+    want, _ = _single(engine, r, ids, meta, full, u)
+    tight = sharded.ShardedLadder(r, u, n, slots, 0, world, emulate=True, exchange=exchange)
+    tight.set_stream(ids, meta)
+    tight.set_table(full)
+    with pytest.raises(_lib.TsError, match="too small"):
+        tight.run(n, mode=1)
+    tight.close()
+    r.reset_errors()
+    roomy = sharded.ShardedLadder(r, u, 2 * n, slots, 0, world, emulate=True, exchange=exchange)
+    roomy.set_stream(ids, meta)
+    roomy.set_table(full)
+    if exchange:
+        roomy.run(n, mode=1)
+    else:           # the whole-stream form sizes its workspace per call
+        roomy.reset()
+        roomy.barrier()
+        roomy.link(n, 1, owned_cap=n * slots)
+        roomy.check()
+        roomy.rate(n, 1)
+        roomy.barrier()
+        roomy.check()
+    got = sharded.merge_tables([roomy.table[g] for g in range(world)])
+    assert torch.equal(got, want)
+    assert r.error_count() == 0
+    roomy.close()
+
+
 def _worker(rank, world, port, results):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
