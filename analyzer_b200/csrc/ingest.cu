@@ -13,27 +13,51 @@
 
 namespace {
 
-// int64 key -> dense index in order of first appearance (open addressing, power-of-two table)
+// int64 key -> dense index in order of first appearance (open addressing, power-of-two table that doubles
+// at half load: its size follows the number of distinct keys, not the number of rows -- a table laid out for
+// as many keys as rows cost more to clear than the whole batch to ingest; key and index share a 16-byte
+// entry, and the caller prefetches the entry of a row a few rows ahead)
 struct FirstSeen {
-    std::vector<int64_t> key;
-    std::vector<int32_t> val;
+    struct Entry { int64_t key; int32_t val; int32_t pad; };
+    std::vector<Entry> tab;
     uint64_t mask;
     int32_t count = 0;
-    explicit FirstSeen(int64_t expected)
+    explicit FirstSeen(int64_t rows)          // small batches never grow; large ones start at 64k entries
     {
-        uint64_t cap = 16;
-        while (cap < (uint64_t)expected * 2 + 2) cap <<= 1;
-        key.assign(cap, 0);
-        val.assign(cap, -1);
+        uint64_t cap = 1024;
+        while (cap < (uint64_t)rows * 2 + 2 && cap < (1u << 16)) cap <<= 1;
+        tab.assign(cap, Entry{0, -1, 0});
         mask = cap - 1;
+    }
+    static uint64_t hash(int64_t k)
+    {
+        uint64_t h = (uint64_t)k * 0x9E3779B97F4A7C15ull;
+        return h ^ (h >> 29);
+    }
+    void prefetch(int64_t k) const { __builtin_prefetch(&tab[hash(k) & mask]); }
+    void grow()
+    {
+        std::vector<Entry> old(tab.size() * 2, Entry{0, -1, 0});
+        old.swap(tab);
+        mask = tab.size() - 1;
+        for (const Entry &e : old) {
+            if (e.val < 0) continue;
+            uint64_t i = hash(e.key) & mask;
+            while (tab[i].val >= 0) i = (i + 1) & mask;
+            tab[i] = e;
+        }
     }
     int32_t get(int64_t k, bool *fresh)
     {
-        uint64_t h = (uint64_t)k * 0x9E3779B97F4A7C15ull;
-        h ^= h >> 29;
-        for (uint64_t i = h & mask;; i = (i + 1) & mask) {
-            if (val[i] < 0) { key[i] = k; val[i] = count; *fresh = true; return count++; }
-            if (key[i] == k) { *fresh = false; return val[i]; }
+        for (uint64_t i = hash(k) & mask;; i = (i + 1) & mask) {
+            Entry &e = tab[i];
+            if (e.key == k && e.val >= 0) { *fresh = false; return e.val; }
+            if (e.val < 0) {
+                e.key = k; e.val = count; *fresh = true;
+                const int32_t idx = count++;
+                if ((uint64_t)count * 2 > mask) grow();
+                return idx;
+            }
         }
     }
 };
@@ -58,13 +82,18 @@ extern "C" int ts_ingest_rows(const ts_row_columns *rows, double unknown_sigma, 
         ts_set_error("ts_ingest_rows: null column");
         return TS_E_ARG;
     }
-    FirstSeen matches(n), players(n);
+    FirstSeen matches(n / 2), players(n);
     std::vector<int32_t> first_row_of_match, first_row_of_player, pos(n);
     std::vector<uint32_t> count;           // per match: participants seen so far on roster 0 / 1
     std::vector<uint8_t> flags;            // per match: bit 0/1 a winner flag on roster 0/1, bit 2 an AFK participant
     int widest = 1;
+    constexpr int64_t kAhead = 12;
     for (int64_t i = 0; i < n; ++i) {
         bool fresh = false;
+        if (i + kAhead < n) {
+            players.prefetch(rows->player[i + kAhead]);
+            if (rows->match[i + kAhead] != rows->match[i + kAhead - 1]) matches.prefetch(rows->match[i + kAhead]);
+        }
         // the rows of a match usually follow each other: no lookup then
         const int32_t m = (i > 0 && rows->match[i] == rows->match[i - 1]) ? row_match[i - 1] : matches.get(rows->match[i], &fresh);
         if (fresh) { match_keys[m] = rows->match[i]; first_row_of_match.push_back((int32_t)i); count.push_back(0); count.push_back(0); flags.push_back(0); }
