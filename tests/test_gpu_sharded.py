@@ -149,6 +149,29 @@ def test_duplicate_player_and_bad_id_are_reported():
 
 
 @pytest.mark.parametrize("exchange", [True, False])
+def test_windows_smaller_than_a_round_of_blocks(exchange):
+    """Windows of fewer than 32 * G matches: some ranks hold no match at all (they still own players,
+    link them and take their rows back), blocks are ragged."""
+    from analyzer_b200 import engine, sharded
+    dev = torch.device("cuda", 0)
+    slots, u = 6, 101
+    r = engine.Rater(engine.Env(), 0)
+    for world in (2, 4, 8):
+        for n in (1, 31, 33, 40, 257):
+            ids, meta = engine.gen_matches(engine.make_gen(100 + n, u, slots=slots, mode=1, p_afk=0.05), 0, n, dev)
+            full = engine.gen_table(100 + n, 0, u, dev).reshape(u, 2)
+            want, _ = _single(engine, r, ids, meta, full, u)
+            ladder = sharded.ShardedLadder(r, u, n, slots, 0, world, emulate=True, exchange=exchange)
+            ladder.set_stream(ids, meta)
+            ladder.set_table(full)
+            ladder.run(n, mode=1)
+            got = sharded.merge_tables([ladder.table[g] for g in range(world)])
+            assert torch.equal(got, want), (world, n)
+            assert r.error_count() == 0
+            ladder.close()
+
+
+@pytest.mark.parametrize("exchange", [True, False])
 def test_skewed_ownership_overflows_loudly_and_fits_with_more_room(exchange):
     """Every player owned by rank 0 (all ids even, 2 ranks): rank 0 is sent twice its share of the slots.
     The default capacity (1.25 shares) must report TS_SHARD_OVERFLOW, not rate with missing links; a
